@@ -1,0 +1,267 @@
+// rd_traverse.h -- ray / wide-BVH traversal and ray/triangle intersection (one ray per thread).
+//
+// Replaces radiance/shader/radiance.cl:41-251 (intersectBot, intersectTop, intersectAABB,
+// intersectTriangle). Same observable semantics:
+//   * a candidate is accepted iff the triangle test passes and  Tmin < t < Tmax  and  t < best
+//     (all strict, radiance.cl:90-91); two-sided triangles, inclusive edges, det == 0 rejected,
+//     t > 0 (radiance.cl:221-240)
+//   * the triangle test evaluates the same Moeller-Trumbore expressions in the same order with
+//     separately rounded IEEE multiplies and adds, so t / barycentrics are bit-identical to the
+//     reference compiled without contraction
+//   * instance rays are transformed with w = 1 / w = 0 and NOT renormalised, so t is shared
+//     between world and object space (radiance.cl:161-169)
+//   * the candidate callback runs after the hit is committed and may only stop the traversal
+//     (any-hit, radiance.cl:93-101)
+// Different by design: 8-wide quantised nodes, front-to-back order by ray octant, boxes culled
+// against the current best t, precomputed instance inverse, two-level walk on one stack.
+//
+// The file compiles in three places: nvcc (library kernels), NVRTC (inlined into user programs)
+// and g++ (tests/hostemu only, never the product).
+#ifndef RD_TRAVERSE_H
+#define RD_TRAVERSE_H
+#include "rd_types.h"
+
+#ifdef __CUDA_ARCH__
+#define RD_MUL(a, b) __fmul_rn((a), (b))
+#define RD_ADD(a, b) __fadd_rn((a), (b))
+#define RD_SUB(a, b) __fsub_rn((a), (b))
+#define RD_RCP(a) __frcp_rn(a)
+#define RD_FMA(a, b, c) __fmaf_rn((a), (b), (c))
+#define RD_FMIN(a, b) fminf((a), (b))
+#define RD_FMAX(a, b) fmaxf((a), (b))
+#define RD_POPC(x) __popc(x)
+#define RD_CLZ(x) __clz((int)(x))
+#define RD_FFS(x) __ffs((int)(x))
+#define RD_F2U(f) __float_as_uint(f)
+#define RD_U2F(u) __uint_as_float(u)
+#define RD_LDG4(p) __ldg((const uint4*)(p))
+#else
+#include <math.h>
+#include <string.h>
+// host build (unit tests): compiled with -ffp-contract=off so these stay separately rounded
+#define RD_MUL(a, b) ((a) * (b))
+#define RD_ADD(a, b) ((a) + (b))
+#define RD_SUB(a, b) ((a) - (b))
+#define RD_RCP(a) (1.0f / (a))
+#define RD_FMA(a, b, c) fmaf((a), (b), (c))
+#define RD_FMIN(a, b) fminf((a), (b))
+#define RD_FMAX(a, b) fmaxf((a), (b))
+#define RD_POPC(x) __builtin_popcount(x)
+#define RD_CLZ(x) ((x) ? __builtin_clz(x) : 32)
+#define RD_FFS(x) __builtin_ffs((int)(x))
+static inline rd_u32 rd_f2u_(float f) { rd_u32 u; memcpy(&u, &f, 4); return u; }
+static inline float rd_u2f_(rd_u32 u) { float f; memcpy(&f, &u, 4); return f; }
+#define RD_F2U(f) rd_f2u_(f)
+#define RD_U2F(u) rd_u2f_(u)
+#endif
+
+#ifndef RD_STACK_ENTRIES
+#define RD_STACK_ENTRIES 48
+#endif
+
+struct RdHitRec {
+    float t, b1, b2;     // t = RD_MISS_T when nothing was accepted
+    rd_u32 prim, inst;   // primitive index inside the mesh, instanceID (caller order)
+};
+
+// Moeller-Trumbore with the reference's expression order (radiance/shader/radiance.cl:211-251).
+RD_HD bool rd_intersect_triangle(float ox, float oy, float oz, float dx, float dy, float dz,
+                                 float ax, float ay, float az, float bx, float by, float bz,
+                                 float cx, float cy, float cz, float* t, float* b1, float* b2)
+{
+    const float e1x = RD_SUB(bx, ax), e1y = RD_SUB(by, ay), e1z = RD_SUB(bz, az);
+    const float e2x = RD_SUB(cx, ax), e2y = RD_SUB(cy, ay), e2z = RD_SUB(cz, az);
+    // p = d x e2
+    const float px = RD_SUB(RD_MUL(dy, e2z), RD_MUL(dz, e2y));
+    const float py = RD_SUB(RD_MUL(dz, e2x), RD_MUL(dx, e2z));
+    const float pz = RD_SUB(RD_MUL(dx, e2y), RD_MUL(dy, e2x));
+    const float det = RD_ADD(RD_ADD(RD_MUL(e1x, px), RD_MUL(e1y, py)), RD_MUL(e1z, pz));
+    if (det == 0.0f) return false;
+    const float inv = RD_RCP(det);
+    const float sx = RD_SUB(ox, ax), sy = RD_SUB(oy, ay), sz = RD_SUB(oz, az);
+    const float u = RD_MUL(inv, RD_ADD(RD_ADD(RD_MUL(sx, px), RD_MUL(sy, py)), RD_MUL(sz, pz)));
+    // q = s x e1
+    const float qx = RD_SUB(RD_MUL(sy, e1z), RD_MUL(sz, e1y));
+    const float qy = RD_SUB(RD_MUL(sz, e1x), RD_MUL(sx, e1z));
+    const float qz = RD_SUB(RD_MUL(sx, e1y), RD_MUL(sy, e1x));
+    const float v = RD_MUL(inv, RD_ADD(RD_ADD(RD_MUL(dx, qx), RD_MUL(dy, qy)), RD_MUL(dz, qz)));
+    const float tt = RD_MUL(inv, RD_ADD(RD_ADD(RD_MUL(e2x, qx), RD_MUL(e2y, qy)), RD_MUL(e2z, qz)));
+    if (u < 0.0f || u > 1.0f) return false;
+    if (v < 0.0f || RD_ADD(u, v) > 1.0f) return false;
+    if (!(tt > 0.0f)) return false;
+    *t = tt; *b1 = u; *b2 = v;
+    return true;
+}
+
+// row-major 3x4 times (x,y,z,w) with the reference's left-to-right sum (math.cl:25-31)
+RD_HD float rd_row_dot(const float* r, float x, float y, float z, float w)
+{
+    return RD_ADD(RD_ADD(RD_ADD(RD_MUL(r[0], x), RD_MUL(r[1], y)), RD_MUL(r[2], z)), RD_MUL(r[3], w));
+}
+
+struct RdRayFrame {   // per-space ray constants for the quantised box test
+    float ox, oy, oz, dx, dy, dz;
+    float ix, iy, iz;   // 1/d with |d| clamped away from zero
+    rd_u32 octinv4;     // (7 - octant) replicated to 4 bytes; octant bit2=x<0, bit1=y<0, bit0=z<0
+};
+
+RD_HD float rd_safe_rcp(float d)
+{
+    const float tiny = 1e-30f;
+    float a = fabsf(d) > tiny ? d : (RD_F2U(d) >> 31 ? -tiny : tiny);
+    return 1.0f / a;
+}
+
+RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, float dy, float dz)
+{
+    f.ox = ox; f.oy = oy; f.oz = oz; f.dx = dx; f.dy = dy; f.dz = dz;
+    f.ix = rd_safe_rcp(dx); f.iy = rd_safe_rcp(dy); f.iz = rd_safe_rcp(dz);
+    rd_u32 oct = (f.ix < 0.0f ? 4u : 0u) | (f.iy < 0.0f ? 2u : 0u) | (f.iz < 0.0f ? 1u : 0u);
+    f.octinv4 = (7u - oct) * 0x01010101u;
+}
+
+// Tests the 8 quantised child boxes of one node against the ray interval [tmin, tbest].
+// Returns the hit mask: bits 24..31 = inner children keyed by visiting priority (highest first),
+// bits 0..23 = leaf records (one bit per primitive record relative to primBase).
+RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const RdU4& n3, const RdU4& n4,
+                          const RdRayFrame& f, float tmin, float tbest)
+{
+    const float sx = RD_U2F((n0.w & 0xffu) << 23), sy = RD_U2F(((n0.w >> 8) & 0xffu) << 23),
+                sz = RD_U2F(((n0.w >> 16) & 0xffu) << 23);
+    const float ax = sx * f.ix, ay = sy * f.iy, az = sz * f.iz;
+    const float bx = (RD_U2F(n0.x) - f.ox) * f.ix, by = (RD_U2F(n0.y) - f.oy) * f.iy,
+                bz = (RD_U2F(n0.z) - f.oz) * f.iz;
+    rd_u32 hitmask = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int h = 0; h < 2; ++h) {
+        const rd_u32 meta4 = h ? n1.w : n1.z;
+        const rd_u32 inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const rd_u32 innerMask4 = (inner4 >> 4) * 0xffu;
+        const rd_u32 bitIndex4 = (meta4 ^ (f.octinv4 & innerMask4)) & 0x1f1f1f1fu;
+        const rd_u32 childBits4 = (meta4 >> 5) & 0x07070707u;
+        const rd_u32 qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
+        const rd_u32 qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
+        const rd_u32 nx = f.ix < 0.0f ? qhx : qlx, fx = f.ix < 0.0f ? qlx : qhx;
+        const rd_u32 ny = f.iy < 0.0f ? qhy : qly, fy = f.iy < 0.0f ? qly : qhy;
+        const rd_u32 nz = f.iz < 0.0f ? qhz : qlz, fz = f.iz < 0.0f ? qlz : qhz;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int j = 0; j < 4; ++j) {
+            const int sh = 8 * j;
+            const float t0x = RD_FMA((float)((nx >> sh) & 0xffu), ax, bx);
+            const float t0y = RD_FMA((float)((ny >> sh) & 0xffu), ay, by);
+            const float t0z = RD_FMA((float)((nz >> sh) & 0xffu), az, bz);
+            const float t1x = RD_FMA((float)((fx >> sh) & 0xffu), ax, bx);
+            const float t1y = RD_FMA((float)((fy >> sh) & 0xffu), ay, by);
+            const float t1z = RD_FMA((float)((fz >> sh) & 0xffu), az, bz);
+            const float tn = RD_FMAX(RD_FMAX(t0x, t0y), RD_FMAX(t0z, tmin));
+            const float tf = RD_FMIN(RD_FMIN(t1x, t1y), RD_FMIN(t1z, tbest));
+            if (tn <= tf) hitmask |= ((childBits4 >> sh) & 0xffu) << ((bitIndex4 >> sh) & 0xffu);
+        }
+    }
+    return hitmask;
+}
+
+#ifdef __CUDA_ARCH__
+#define RD_LOAD_U4(dst, ptr) { uint4 _v = __ldg((const uint4*)(ptr)); dst.x = _v.x; dst.y = _v.y; dst.z = _v.z; dst.w = _v.w; }
+#define RD_LOAD_F4(dst, ptr) { float4 _v = __ldg((const float4*)(ptr)); dst.x = _v.x; dst.y = _v.y; dst.z = _v.z; dst.w = _v.w; }
+#else
+#define RD_LOAD_U4(dst, ptr) { dst = *(const RdU4*)(ptr); }
+#define RD_LOAD_F4(dst, ptr) { dst = *(const RdF4*)(ptr); }
+#endif
+
+// Walks the two-level structure for one ray. `onCandidate(hit)` is invoked after every accepted
+// closer candidate (hit already committed) and returns false to stop (any-hit semantics).
+// Returns true iff something was accepted; `hit` holds the closest accepted candidate so far.
+template <class OnCandidate>
+RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz,
+                       float tmin, float tmax, RdHitRec& hit, OnCandidate& onCandidate)
+{
+    struct Entry { rd_u32 x, y; };
+    Entry stack[RD_STACK_ENTRIES];
+    int sp = 0, blasSp = -1;          // blasSp >= 0 while inside a bottom-level structure
+    const RdNode8* nodes = scene->nodes;
+    const RdTri* tris = 0;
+    const RdInstance* curInst = 0;
+    RdRayFrame f;
+    rd_frame_set(f, ox, oy, oz, dx, dy, dz);
+    // The interval is open at tmax in the reference (t < Tmax); boxes are culled with <= so use
+    // tmax itself as the first "best" bound and keep strictness in the triangle accept test.
+    float tbest = tmax;
+    bool any = false;
+    hit.t = RD_MISS_T; hit.b1 = 0.0f; hit.b2 = 0.0f; hit.prim = RD_INVALID; hit.inst = RD_INVALID;
+    Entry ng, tg;
+    ng.x = 0; ng.y = 0x80000000u; tg.x = 0; tg.y = 0;
+    for (;;) {
+        if (ng.y > 0x00ffffffu) {
+            const rd_u32 bit = 31u - (rd_u32)RD_CLZ(ng.y);
+            const rd_u32 imask = ng.y & 0xffu;   // low byte of an inner group = imask
+            ng.y &= ~(1u << bit);
+            if (ng.y > 0x00ffffffu) {
+                if (sp < RD_STACK_ENTRIES) stack[sp++] = ng;
+                else if (scene->status) scene->status[0] = 1u;
+            }
+            const rd_u32 slot = (bit - 24u) ^ (f.octinv4 & 0xffu);
+            const rd_u32 rel = (rd_u32)RD_POPC(imask & ~(0xffffffffu << slot));
+            const RdNode8* n = nodes + (ng.x + rel);
+            RdU4 n0, n1, n2, n3, n4;
+            RD_LOAD_U4(n0, &n->w[0]); RD_LOAD_U4(n1, &n->w[1]); RD_LOAD_U4(n2, &n->w[2]);
+            RD_LOAD_U4(n3, &n->w[3]); RD_LOAD_U4(n4, &n->w[4]);
+            const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
+            ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
+            tg.x = n1.y; tg.y = hm & 0x00ffffffu;
+        } else {
+            tg = ng; ng.x = 0; ng.y = 0;
+        }
+        while (tg.y) {
+            const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
+            tg.y &= tg.y - 1u;
+            if (blasSp < 0) {
+                // top level: record k is an instance -> descend into its bottom-level structure
+                const rd_u32 ii = scene->leafInstances[tg.x + k];
+                if (tg.y) { if (sp < RD_STACK_ENTRIES) stack[sp++] = tg; else if (scene->status) scene->status[0] = 1u; }
+                if (ng.y > 0x00ffffffu) { if (sp < RD_STACK_ENTRIES) stack[sp++] = ng; else if (scene->status) scene->status[0] = 1u; }
+                blasSp = sp;
+                curInst = scene->instances + ii;
+                const float* m = curInst->inv;
+                const float lox = rd_row_dot(m + 0, ox, oy, oz, 1.0f), loy = rd_row_dot(m + 4, ox, oy, oz, 1.0f),
+                            loz = rd_row_dot(m + 8, ox, oy, oz, 1.0f);
+                const float ldx = rd_row_dot(m + 0, dx, dy, dz, 0.0f), ldy = rd_row_dot(m + 4, dx, dy, dz, 0.0f),
+                            ldz = rd_row_dot(m + 8, dx, dy, dz, 0.0f);
+                rd_frame_set(f, lox, loy, loz, ldx, ldy, ldz);
+                nodes = curInst->nodes; tris = curInst->tris;
+                ng.x = 0; ng.y = 0x80000000u; tg.y = 0;
+                break;
+            }
+            const RdTri* tr = tris + (tg.x + k);
+            RdF4 a, b, c;
+            RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
+            float t, b1, b2;
+            if (rd_intersect_triangle(f.ox, f.oy, f.oz, f.dx, f.dy, f.dz, a.x, a.y, a.z, b.x, b.y, b.z,
+                                      c.x, c.y, c.z, &t, &b1, &b2) &&
+                t < hit.t && t > tmin && t < tmax) {
+                hit.t = t; hit.b1 = b1; hit.b2 = b2; hit.prim = RD_F2U(a.w); hit.inst = curInst->instanceID;
+                tbest = t; any = true;
+                if (!onCandidate(hit)) return true;
+            }
+        }
+        if (ng.y <= 0x00ffffffu) {
+            if (blasSp >= 0 && sp == blasSp) {
+                // bottom-level structure exhausted: back to world space
+                blasSp = -1; nodes = scene->nodes;
+                rd_frame_set(f, ox, oy, oz, dx, dy, dz);
+            }
+            if (sp == 0) break;
+            ng = stack[--sp];
+        }
+    }
+    return any;
+}
+
+struct RdNoAnyHit { RD_HD bool operator()(const RdHitRec&) const { return true; } };
+struct RdFirstHit { RD_HD bool operator()(const RdHitRec&) const { return false; } };
+
+#endif

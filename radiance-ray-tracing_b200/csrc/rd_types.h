@@ -1,0 +1,81 @@
+// rd_types.h -- device data layout of the B200 tracer (shared by nvcc, NVRTC and the host-side
+// unit-test build). Everything here is plain data; see DESIGN.md "Data layout in HBM".
+//
+// Replaces the reference's single-blob binary BVH (radiance/src/core.h:34-101,
+// radiance/shader/data.cl:4-99): 48-byte binary nodes + indexed 16-byte faces + 16-byte vertices
+// addressed by 32-bit byte offsets become
+//   * RdNode8   80 B  8-wide node, child boxes quantised to 8 bits on a per-node power-of-two grid
+//   * RdTri     48 B  pre-gathered triangle (3 x float4, primID in v0.w), stored in leaf order
+//   * RdInstance 144 B world->object 3x4 (precomputed once, the reference inverts a 4x4 per ray per
+//                     instance visit: radiance/shader/radiance.cl:166-167), object->world 4x4, ids,
+//                     64-bit pointers to the bottom-level arrays (no 4 GiB ceiling)
+#ifndef RD_TYPES_H
+#define RD_TYPES_H
+
+#if defined(__CUDACC_RTC__)
+typedef unsigned int rd_u32;
+typedef unsigned long long rd_u64;
+typedef unsigned char rd_u8;
+#else
+#include <stdint.h>
+typedef uint32_t rd_u32;
+typedef uint64_t rd_u64;
+typedef uint8_t rd_u8;
+#endif
+
+#if defined(__CUDACC__) || defined(__CUDACC_RTC__)
+#define RD_HD __host__ __device__ __forceinline__
+#define RD_ALIGN(n) __align__(n)
+#else
+#define RD_HD inline
+#define RD_ALIGN(n) __attribute__((aligned(n)))
+#endif
+
+struct RD_ALIGN(16) RdU4 { rd_u32 x, y, z, w; };
+struct RD_ALIGN(16) RdF4 { float x, y, z, w; };
+
+// 8-wide BVH node, 5 x 16 B.
+//  w[0] = { p.x, p.y, p.z (float bits),  ex | ey<<8 | ez<<16 | imask<<24 }
+//         p = lower corner of the node box, e* = biased float exponents of the grid step per axis,
+//         imask bit s set <=> slot s holds an inner child
+//  w[1] = { childBase, primBase, meta[0..3], meta[4..7] }
+//         inner child in slot s lives at node index childBase + popc(imask & ((1<<s)-1))
+//         meta byte: 0 = empty; inner = 0b001_11sss; leaf = unary(count 1..3)<<5 | first record
+//         offset (0..21) relative to primBase
+//  w[2] = { qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7] }
+//  w[3] = { qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7] }
+//  w[4] = { qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7] }
+struct RD_ALIGN(16) RdNode8 { RdU4 w[5]; };
+
+// Triangle record: v0.w carries the primitive index (bits), v1.w / v2.w are zero.
+struct RD_ALIGN(16) RdTri { RdF4 v0, v1, v2; };
+
+struct RD_ALIGN(16) RdInstance {
+    float inv[12];            // world->object, rows 0..2 of the 4x4 inverse
+    float fwd[16];            // object->world, row-major 4x4 exactly as the caller gave it
+    rd_u32 sbtOffset, instanceID, customID, flags;
+    const RdNode8* nodes;     // bottom-level node array (root = node 0)
+    const RdTri* tris;        // bottom-level triangle records
+};
+
+// Top-level acceleration structure header; lives in HBM, its address is the descriptor that a
+// user program passes to traceRay as `topLevel` (reference: `__global struct AccelStruct*`).
+struct RD_ALIGN(16) RdScene {
+    const RdNode8* nodes;         // top-level nodes over instance boxes (root = node 0)
+    const rd_u32* leafInstances;  // instance indices in top-level leaf order
+    const RdInstance* instances;  // caller order: instanceID == array index
+    rd_u32 instanceCount, nodeCount, flags, pad;
+    rd_u32* status;               // [0] = traversal-stack overflow counter (must stay 0)
+    rd_u64 pad2;
+};
+
+// Ray / hit records of the wavefront queues (structure of arrays, 16-byte vector loads):
+//   rayA[i] = { o.x, o.y, o.z, tmin }   rayB[i] = { d.x, d.y, d.z, tmax }
+//   hitA[i] = { t, b1, b2, primID(bits) } (t = FLT_MAX: miss)   hitB[i] = instanceID
+#define RD_MISS_T 3.402823466e+38f
+#define RD_INVALID 0xffffffffu
+
+// rd_trace flags
+#define RD_TRACE_TERMINATE_ON_FIRST_HIT 1u
+
+#endif
