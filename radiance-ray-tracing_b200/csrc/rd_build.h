@@ -343,4 +343,26 @@ RD_HD bool rd_inverse4x4(const float* m, float* out)
     return true;
 }
 
+// World-space box of an instance: transform the 8 corners of the bottom-level root box
+// (reference: radiance/src/bvh.cpp:370-401).
+RD_HD void rd_instance_world_box(const float* fwd, RdF4 blo, RdF4 bhi, RdF4* lo, RdF4* hi)
+{
+    RdF4 l, h;
+    l.x = l.y = l.z = 3.402823466e+38f; h.x = h.y = h.z = -3.402823466e+38f; l.w = h.w = 0.0f;
+    for (int c = 0; c < 8; ++c) {
+        const float x = (c & 1) ? bhi.x : blo.x, y = (c & 2) ? bhi.y : blo.y, z = (c & 4) ? bhi.z : blo.z;
+        const float wx = fwd[0] * x + fwd[1] * y + fwd[2] * z + fwd[3];
+        const float wy = fwd[4] * x + fwd[5] * y + fwd[6] * z + fwd[7];
+        const float wz = fwd[8] * x + fwd[9] * y + fwd[10] * z + fwd[11];
+        l.x = fminf(l.x, wx); l.y = fminf(l.y, wy); l.z = fminf(l.z, wz);
+        h.x = fmaxf(h.x, wx); h.y = fmaxf(h.y, wy); h.z = fmaxf(h.z, wz);
+    }
+    // pad by a few ulps of the magnitude: the instance-space traversal re-derives the ray with
+    // rounded arithmetic, the world box must stay conservative
+    const float px = 4e-7f * fmaxf(fabsf(l.x), fabsf(h.x)), py = 4e-7f * fmaxf(fabsf(l.y), fabsf(h.y)),
+                pz = 4e-7f * fmaxf(fabsf(l.z), fabsf(h.z));
+    l.x -= px; l.y -= py; l.z -= pz; h.x += px; h.y += py; h.z += pz;
+    *lo = l; *hi = h;
+}
+
 #endif
