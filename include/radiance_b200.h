@@ -1,0 +1,128 @@
+/* radiance_b200.h -- C ABI of libradiance_b200.so, the B200 (sm_100a) backend that replaces the
+ * Radiance host library + OpenCL device runtime for the TraceRays hot path.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the reference
+ * repository, zekailin00/Radiance-Ray-Tracing). Plain pointers and sizes only; no C++/torch types.
+ * All functions return RD_OK (0) or a negative RD_E_* code; rd_last_error() holds the message of the
+ * last failure on the calling thread. The reference aborts on every error (radiance/src/clcontext.h:27-47);
+ * the C++ shim include/radiance.h converts non-zero returns into that behaviour.
+ * There is no CPU execution path: every call needs a CUDA device.
+ */
+#ifndef RADIANCE_B200_H
+#define RADIANCE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RD_OK 0
+#define RD_E_CUDA (-1)      /* CUDA runtime / driver error */
+#define RD_E_ARG (-2)       /* invalid argument */
+#define RD_E_COMPILE (-3)   /* NVRTC compile / link error, log in rd_last_error() */
+#define RD_E_STATE (-4)     /* call order (no pipeline / descriptors bound, ...) */
+#define RD_E_IO (-5)        /* file error */
+#define RD_E_OVERFLOW (-6)  /* traversal stack overflow was detected on the device */
+
+typedef struct rd_platform rd_platform;   /* RD::Platform            radiance/include/radiance.h:146-174 */
+typedef struct rd_blas rd_blas;           /* RD::BottomAccelStruct   radiance/include/radiance.h:38-45  */
+typedef struct rd_module rd_module;       /* RD::ShaderModule        radiance/include/radiance.h:60     */
+typedef void* rd_handle;                  /* RD::Handle (Buffer / Image / ImageArray / Sampler / TopAccelStruct),
+                                             radiance/include/radiance.h:12-19; one 8-byte kernel parameter each */
+
+/* RD::Instance, radiance/include/radiance.h:48-55 (row-major object->world) */
+typedef struct rd_instance_desc {
+    float transform[16];
+    uint32_t SBTOffset;
+    uint32_t customInstanceID;
+    rd_blas* bottomAccelStruct;
+} rd_instance_desc;
+
+const char* rd_last_error(void);
+
+/* RD::Platform::GetPlatform() + CLContext::GetCLContext(), radiance.h:148-158, clcontext.cpp:12-40.
+ * device < 0 selects the current CUDA device. */
+int rd_platform_create(int device, rd_platform** out);
+int rd_platform_destroy(rd_platform* p);
+/* stream used for all work of this platform (cudaStream_t as void*), for external event timing */
+void* rd_platform_stream(rd_platform* p);
+int rd_platform_sync(rd_platform* p);
+
+/* RD::CreateBuffer, radiance/src/radiance.cpp:133-140 */
+int rd_buffer_create(rd_platform* p, size_t size, rd_handle* out);
+/* RD::CreateImage (a plain W*H*4-byte buffer), radiance/src/radiance.cpp:86-93 */
+int rd_image_create(rd_platform* p, unsigned width, unsigned height, rd_handle* out);
+/* RD::CreateImageArray (layered RGBA8), radiance/src/radiance.cpp:96-118 */
+int rd_image_array_create(rd_platform* p, unsigned width, unsigned height, unsigned layers, rd_handle* out);
+/* RD::CreateSampler, radiance/src/radiance.cpp:120-131; modes are the CL_ADDRESS_* / CL_FILTER_* values */
+int rd_sampler_create(rd_platform* p, uint32_t addressingMode, uint32_t filterMode, rd_handle* out);
+/* RD::WriteBuffer / RD::ReadBuffer (blocking), radiance/src/radiance.cpp:186-199 */
+int rd_buffer_write(rd_platform* p, rd_handle h, size_t size, const void* data, size_t offset);
+int rd_buffer_read(rd_platform* p, rd_handle h, size_t size, void* data, size_t offset);
+/* RD::WriteImage / RD::ReadImage (one layer), radiance/src/radiance.cpp:202-224 */
+int rd_image_write(rd_platform* p, rd_handle h, unsigned width, unsigned height, size_t layer, const void* data);
+int rd_image_read(rd_platform* p, rd_handle h, unsigned width, unsigned height, size_t layer, void* data);
+/* no reference counterpart (the reference never frees): release a buffer/image/sampler/TLAS handle */
+int rd_handle_free(rd_platform* p, rd_handle h);
+/* raw device address behind a buffer handle (for tests and zero-copy interop) */
+void* rd_handle_device_ptr(rd_handle h);
+
+/* RD::BuildAccelStruct(Platform*, Mesh&), radiance/src/radiance.cpp:20-52 (+ bvh.cpp:288-341, 502-522).
+ * verts: nv x 3 floats (RD::Vec3), idx: nt x 3 uint32 (RD::Triangle). Host pointers. */
+int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, const uint32_t* idx, unsigned nt, rd_blas** out);
+/* same, inputs already resident in HBM (device pointers): the GPU build without the upload */
+int rd_blas_build_device(rd_platform* p, const float* dverts, unsigned nv, const uint32_t* didx, unsigned nt, rd_blas** out);
+int rd_blas_free(rd_platform* p, rd_blas* b);
+/* build statistics: [0] wide nodes, [1] triangle records, [2] collapse levels, [3] bytes in HBM */
+int rd_blas_stats(rd_blas* b, uint64_t out[4]);
+
+/* RD::BuildAccelStruct(Platform*, std::vector<Instance>&), radiance/src/radiance.cpp:54-84 */
+int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, unsigned n, rd_handle* out);
+
+/* RD::CreateShaderModule, radiance/src/radiance.cpp:152-179: compiles an OpenCL-C user program
+ * (samples/shader.cl conventions) with NVRTC for sm_100a; kernel "raygen" is extracted. `name` is
+ * accepted and ignored like in the reference. */
+int rd_shader_module_create(rd_platform* p, const char* code, unsigned size, const char* name, rd_module** out);
+int rd_module_free(rd_platform* p, rd_module* m);
+/* samples/sbt.json: rows {raygen, closestHit, anyHit, miss}; row index = dispatcher case label.
+ * When set before rd_shader_module_create and the program does not define callHit/callMiss/callAnyHit
+ * itself, the dispatchers are generated from the table (tools/genSBT.py semantics). */
+int rd_sbt_load_json(rd_platform* p, const char* json_text);
+/* RD::BindPipeline, radiance/src/radiance.cpp:226-229 (module 0 of the pipeline is the one launched,
+ * radiance.cpp:254) */
+int rd_pipeline_bind(rd_platform* p, rd_module* const* modules, unsigned n);
+/* RD::BindDescriptorSet, radiance/src/radiance.cpp:231-240: handle i becomes kernel argument i */
+int rd_descriptors_bind(rd_platform* p, const rd_handle* handles, unsigned n);
+/* RD::TraceRays, radiance/src/radiance.cpp:242-267: launches `raygen` over width*height work-items
+ * and blocks. The three group indices are accepted and ignored like in the reference. */
+int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned missGroupIndex, unsigned hitGroupIndex,
+                  unsigned width, unsigned height);
+/* same without the final host synchronisation (for device-side event timing) */
+int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height);
+
+/* Explicit ray list through the traversal kernel (wavefront building block; used for hit-ID parity
+ * against the reference's traceRay, radiance/shader/radiance.cl:254-275).
+ *   rayA[i] = {o.xyz, tmin}, rayB[i] = {d.xyz, tmax}; hitA[i] = {t, b1, b2, primID bits}, hitB[i] = instanceID.
+ * All four are buffer handles. flags: RD_TRACE_* below. Asynchronous on the platform stream. */
+#define RD_TRACE_TERMINATE_ON_FIRST_HIT 1u
+#define RD_TRACE_COUNTERS 2u   /* also count node / triangle fetches (see rd_trace_counters) */
+int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA, rd_handle rayB, rd_handle hitA,
+                      rd_handle hitB, size_t n, unsigned flags);
+/* totals of the last RD_TRACE_COUNTERS launch: [0] wide nodes fetched, [1] triangle records fetched,
+ * [2] rays */
+int rd_trace_counters(rd_platform* p, uint64_t out[3]);
+/* pinhole / thin-lens primary rays of samples/shader.cl:111-173 into rayA/rayB (width*height rays) */
+int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID, unsigned totalSamples,
+                             unsigned width, unsigned height, rd_handle rayA, rd_handle rayB);
+
+/* runtime options: "fmad" (0/1, NVRTC contraction for user code), "tile" (0/1 8x4 pixel tiles per warp),
+ * "block" (threads per block of raygen launches) */
+int rd_set_option(rd_platform* p, const char* key, long value);
+/* number of kernels this library launched since platform creation */
+uint64_t rd_launch_count(rd_platform* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

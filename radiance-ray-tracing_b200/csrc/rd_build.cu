@@ -1,0 +1,307 @@
+// rd_build.cu -- GPU acceleration-structure build: LBVH (Morton -> radix sort -> Karras -> refit)
+// followed by a level-synchronous collapse into 8-wide quantised nodes. Replaces the host SAH
+// builder of the reference (radiance/src/bvh.cpp:46-597) and its blob packers
+// (radiance/src/radiance.cpp:318-425). The per-element logic lives in rd_build.h.
+#include <cub/device/device_radix_sort.cuh>
+#include <float.h>
+#include <string.h>
+#include "rd_internal.h"
+#include "rd_build.h"
+
+#define RD_BT 256
+static inline unsigned rd_grid(size_t n) { return (unsigned)((n + RD_BT - 1) / RD_BT); }
+
+// order-preserving float <-> uint encoding for atomicMin/atomicMax
+__device__ __forceinline__ unsigned rd_f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__host__ __device__ __forceinline__ float rd_ord2f(unsigned u)
+{
+    unsigned v = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u;
+#ifdef __CUDA_ARCH__
+    return __uint_as_float(v);
+#else
+    float f; memcpy(&f, &v, 4); return f;
+#endif
+}
+
+__global__ void rd_k_tri_boxes(const float* verts, const rd_u32* idx, rd_u32 n, RdF4* lo, RdF4* hi)
+{
+    rd_u32 p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) rd_prim_box_tri(verts, idx, p, lo, hi);
+}
+
+// bounds[0..2] = min centroid (ordered uint), bounds[3..5] = max centroid
+__global__ void rd_k_centroid_bounds(const RdF4* lo, const RdF4* hi, rd_u32 n, unsigned* bounds)
+{
+    float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const RdF4 l = lo[i], h = hi[i];
+        const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { mn[a] = fminf(mn[a], c[a]); mx[a] = fmaxf(mx[a], c[a]); }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+            mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { atomicMin(&bounds[a], rd_f2ord(mn[a])); atomicMax(&bounds[3 + a], rd_f2ord(mx[a])); }
+    }
+}
+
+__global__ void rd_k_morton(const RdF4* lo, const RdF4* hi, rd_u32 n, const unsigned* bounds, rd_u64* keys, rd_u32* vals)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float cmin[3], cinv[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        cmin[a] = rd_ord2f(bounds[a]);
+        const float ext = rd_ord2f(bounds[3 + a]) - cmin[a];
+        cinv[a] = ext > 0.0f ? 1.0f / ext : 0.0f;
+    }
+    const RdF4 l = lo[i], h = hi[i];
+    keys[i] = rd_morton63(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z), cmin, cinv);
+    vals[i] = i;
+}
+
+__global__ void rd_k_leaf_boxes(RdBinTree T, const RdF4* plo, const RdF4* phi)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T.n) return;
+    const rd_u32 p = T.prim[i];
+    T.lo[T.n - 1 + i] = plo[p];
+    T.hi[T.n - 1 + i] = phi[p];
+}
+
+__global__ void rd_k_karras(RdBinTree T)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < T.n) rd_karras_node(T, (int)i);
+}
+
+__global__ void rd_k_refit(RdBinTree T)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < T.n) rd_refit_from_leaf(T, i);
+}
+
+__global__ void rd_k_collapse(RdBinTree T, RdCollapseOut O, const RdCollapseItem* items, rd_u32 count)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) rd_collapse_item(T, O, items[i]);
+}
+
+__global__ void rd_k_gather_tris(const float* verts, const rd_u32* idx, const rd_u32* leafPrim, RdTri* out, rd_u32 n)
+{
+    rd_u32 r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r < n) rd_gather_tri(verts, idx, leafPrim, out, r);
+}
+
+struct RdTmp {   // scoped device scratch
+    std::vector<void*> ptrs;
+    ~RdTmp() { for (void* q : ptrs) cudaFree(q); }
+    template <class T> cudaError_t alloc(T** out, size_t count)
+    {
+        void* q = 0;
+        cudaError_t e = cudaMalloc(&q, count * sizeof(T) ? count * sizeof(T) : 16);
+        if (e == cudaSuccess) ptrs.push_back(q);
+        *out = (T*)q;
+        return e;
+    }
+};
+
+int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out)
+{
+    cudaStream_t st = p->stream;
+    memset(out, 0, sizeof(*out));
+    if (n == 0) {
+        // empty structure: one node without children
+        RdNode8 e; memset(&e, 0, sizeof(e)); e.w[0].w = 1u | (1u << 8) | (1u << 16);
+        RD_CUDA(cudaMalloc(&out->nodes, sizeof(RdNode8)));
+        RD_CUDA(cudaMemcpyAsync(out->nodes, &e, sizeof(e), cudaMemcpyHostToDevice, st));
+        RD_CUDA(cudaMalloc(&out->leafPrim, 16));
+        RD_CUDA(cudaStreamSynchronize(st));
+        out->nodeCount = 1;
+        return RD_OK;
+    }
+    RdTmp tmp;
+    unsigned* dbounds; rd_u64 *keysA, *keysB; rd_u32 *valsA, *valsB;
+    RD_CUDA(tmp.alloc(&dbounds, 8));
+    RD_CUDA(tmp.alloc(&keysA, n)); RD_CUDA(tmp.alloc(&keysB, n));
+    RD_CUDA(tmp.alloc(&valsA, n)); RD_CUDA(tmp.alloc(&valsB, n));
+    const unsigned init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    RD_CUDA(cudaMemcpyAsync(dbounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
+    unsigned rb = rd_grid(n); if (rb > (unsigned)p->smCount * 8) rb = p->smCount * 8;
+    rd_k_centroid_bounds<<<rb, RD_BT, 0, st>>>(dlo, dhi, n, dbounds);
+    rd_k_morton<<<rd_grid(n), RD_BT, 0, st>>>(dlo, dhi, n, dbounds, keysA, valsA);
+    p->launches += 2;
+    size_t sortBytes = 0;
+    cub::DeviceRadixSort::SortPairs(0, sortBytes, keysA, keysB, valsA, valsB, (int)n, 0, 63, st);
+    char* dsort;
+    RD_CUDA(tmp.alloc(&dsort, sortBytes));
+    RD_CUDA(cub::DeviceRadixSort::SortPairs(dsort, sortBytes, keysA, keysB, valsA, valsB, (int)n, 0, 63, st));
+
+    const rd_u32 ni = n > 1 ? n - 1 : 1;
+    RdBinTree T;
+    T.n = n; T.keys = keysB; T.prim = valsB;
+    RD_CUDA(tmp.alloc(&T.left, ni)); RD_CUDA(tmp.alloc(&T.right, ni));
+    RD_CUDA(tmp.alloc(&T.first, ni)); RD_CUDA(tmp.alloc(&T.last, ni));
+    RD_CUDA(tmp.alloc(&T.parent, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.arrive, ni));
+    RD_CUDA(tmp.alloc(&T.lo, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.hi, 2 * (size_t)n));
+    RD_CUDA(cudaMemsetAsync(T.arrive, 0, ni * sizeof(rd_u32), st));
+    rd_k_leaf_boxes<<<rd_grid(n), RD_BT, 0, st>>>(T, dlo, dhi);
+    p->launches += 1;
+    RdCollapseItem rootItem; rootItem.wide = 0; rootItem.bin = (n == 1) ? (RD_BIN_LEAF | 0u) : 0u;
+    if (n > 1) {
+        rd_k_karras<<<rd_grid(n - 1), RD_BT, 0, st>>>(T);
+        rd_k_refit<<<rd_grid(n), RD_BT, 0, st>>>(T);
+        p->launches += 2;
+    }
+    // collapse, one launch per level of the wide tree
+    RdNode8* wide; rd_u32* counters; RdCollapseItem *itemsA, *itemsB;
+    const size_t maxNodes = (size_t)n / 2 + 2;   // every wide node below the root has >= 4 primitives... see DESIGN.md
+    RD_CUDA(tmp.alloc(&wide, (size_t)n + 1));
+    (void)maxNodes;
+    RD_CUDA(tmp.alloc(&counters, 4));
+    RD_CUDA(tmp.alloc(&itemsA, (size_t)n + 1)); RD_CUDA(tmp.alloc(&itemsB, (size_t)n + 1));
+    RD_CUDA(cudaMalloc(&out->leafPrim, (size_t)n * sizeof(rd_u32)));
+    const rd_u32 c0[4] = {1u, 0u, 0u, 0u};
+    RD_CUDA(cudaMemcpyAsync(counters, c0, sizeof(c0), cudaMemcpyHostToDevice, st));
+    RD_CUDA(cudaMemcpyAsync(itemsA, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
+    RdCollapseOut O; O.nodes = wide; O.leafPrim = out->leafPrim; O.counters = counters; O.next = itemsB;
+    rd_u32 count = 1, levels = 0;
+    RdCollapseItem* cur = itemsA;
+    rd_u32 hc[4];
+    while (count) {
+        RD_CUDA(cudaMemsetAsync(counters + 2, 0, sizeof(rd_u32), st));
+        rd_k_collapse<<<rd_grid(count), RD_BT, 0, st>>>(T, O, cur, count);
+        p->launches += 1;
+        RD_CUDA(cudaMemcpyAsync(hc, counters, sizeof(hc), cudaMemcpyDeviceToHost, st));
+        RD_CUDA(cudaStreamSynchronize(st));
+        count = hc[2];
+        RdCollapseItem* t = cur; cur = O.next; O.next = t;
+        if (++levels > 200) { rd_set_error("rd_build_wide_bvh: collapse did not terminate"); return RD_E_CUDA; }
+    }
+    out->nodeCount = hc[0]; out->levels = levels;
+    if (hc[1] != n) { rd_set_error("rd_build_wide_bvh: %u leaf records for %u primitives", hc[1], n); return RD_E_CUDA; }
+    RD_CUDA(cudaMalloc(&out->nodes, (size_t)out->nodeCount * sizeof(RdNode8)));
+    RD_CUDA(cudaMemcpyAsync(out->nodes, wide, (size_t)out->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, st));
+    RdF4 rl, rh;
+    const rd_u32 rootSlot = (n == 1) ? 0u : 0u;   // inner root = slot 0; single leaf = slot n-1 = 0
+    RD_CUDA(cudaMemcpyAsync(&rl, T.lo + rootSlot, sizeof(RdF4), cudaMemcpyDeviceToHost, st));
+    RD_CUDA(cudaMemcpyAsync(&rh, T.hi + rootSlot, sizeof(RdF4), cudaMemcpyDeviceToHost, st));
+    RD_CUDA(cudaStreamSynchronize(st));
+    RD_CUDA(cudaGetLastError());
+    out->lo[0] = rl.x; out->lo[1] = rl.y; out->lo[2] = rl.z;
+    out->hi[0] = rh.x; out->hi[1] = rh.y; out->hi[2] = rh.z;
+    return RD_OK;
+}
+
+extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigned nv, const uint32_t* didx, unsigned nt, rd_blas** out)
+{
+    if (!p || !out || (nt && (!dverts || !didx))) { rd_set_error("rd_blas_build: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    RdTmp tmp;
+    RdF4 *plo, *phi;
+    RD_CUDA(tmp.alloc(&plo, nt)); RD_CUDA(tmp.alloc(&phi, nt));
+    if (nt) { rd_k_tri_boxes<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, nt, plo, phi); p->launches += 1; }
+    RdBuildResult r;
+    int rc = rd_build_wide_bvh(p, plo, phi, nt, &r);
+    if (rc) return rc;
+    rd_blas* b = new rd_blas();
+    b->nodes = r.nodes; b->nodeCount = r.nodeCount; b->triCount = nt; b->levels = r.levels;
+    memcpy(b->lo, r.lo, 12); memcpy(b->hi, r.hi, 12);
+    RD_CUDA(cudaMalloc(&b->tris, nt ? (size_t)nt * sizeof(RdTri) : 48));
+    if (nt) { rd_k_gather_tris<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, r.leafPrim, b->tris, nt); p->launches += 1; }
+    RD_CUDA(cudaStreamSynchronize(st));
+    RD_CUDA(cudaGetLastError());
+    cudaFree(r.leafPrim);
+    (void)nv;
+    *out = b;
+    return RD_OK;
+}
+
+extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, const uint32_t* idx, unsigned nt, rd_blas** out)
+{
+    if (!p || !out || (nt && (!verts || !idx))) { rd_set_error("rd_blas_build: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    for (size_t k = 0; k < (size_t)nt * 3; ++k)
+        if (idx[k] >= nv) { rd_set_error("rd_blas_build: index %u out of range (nv=%u)", idx[k], nv); return RD_E_ARG; }
+    RdTmp tmp;
+    float* dv; uint32_t* di;
+    RD_CUDA(tmp.alloc(&dv, (size_t)nv * 3)); RD_CUDA(tmp.alloc(&di, (size_t)nt * 3));
+    if (nv) RD_CUDA(cudaMemcpyAsync(dv, verts, (size_t)nv * 12, cudaMemcpyHostToDevice, p->stream));
+    if (nt) RD_CUDA(cudaMemcpyAsync(di, idx, (size_t)nt * 12, cudaMemcpyHostToDevice, p->stream));
+    return rd_blas_build_device(p, dv, nv, di, nt, out);
+}
+
+extern "C" int rd_blas_free(rd_platform* p, rd_blas* b)
+{
+    if (!b) return RD_OK;
+    if (p) cudaSetDevice(p->device);
+    cudaFree(b->nodes); cudaFree(b->tris);
+    delete b;
+    return RD_OK;
+}
+
+extern "C" int rd_blas_stats(rd_blas* b, uint64_t out[4])
+{
+    if (!b || !out) { rd_set_error("rd_blas_stats: null argument"); return RD_E_ARG; }
+    out[0] = b->nodeCount; out[1] = b->triCount; out[2] = b->levels;
+    out[3] = (uint64_t)b->nodeCount * sizeof(RdNode8) + (uint64_t)b->triCount * sizeof(RdTri);
+    return RD_OK;
+}
+
+extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, unsigned n, rd_handle* out)
+{
+    if (!p || !out || (n && !instances)) { rd_set_error("rd_tlas_build: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    std::vector<RdInstance> inst(n);
+    std::vector<RdF4> lo(n), hi(n);
+    for (unsigned i = 0; i < n; ++i) {
+        const rd_blas* b = instances[i].bottomAccelStruct;
+        if (!b) { rd_set_error("rd_tlas_build: instance %u has no bottom-level structure", i); return RD_E_ARG; }
+        RdInstance& I = inst[i];
+        memcpy(I.fwd, instances[i].transform, 64);
+        float inv[16];
+        if (!rd_inverse4x4(I.fwd, inv)) { rd_set_error("rd_tlas_build: instance %u transform is singular", i); return RD_E_ARG; }
+        memcpy(I.inv, inv, 48);
+        I.sbtOffset = instances[i].SBTOffset; I.instanceID = i; I.customID = instances[i].customInstanceID; I.flags = 0;
+        I.nodes = b->nodes; I.tris = b->tris;
+        RdF4 bl, bh; bl.x = b->lo[0]; bl.y = b->lo[1]; bl.z = b->lo[2]; bl.w = 0; bh.x = b->hi[0]; bh.y = b->hi[1]; bh.z = b->hi[2]; bh.w = 0;
+        rd_instance_world_box(I.fwd, bl, bh, &lo[i], &hi[i]);
+    }
+    RdTmp tmp;
+    RdF4 *dlo, *dhi;
+    RD_CUDA(tmp.alloc(&dlo, n)); RD_CUDA(tmp.alloc(&dhi, n));
+    if (n) {
+        RD_CUDA(cudaMemcpyAsync(dlo, lo.data(), (size_t)n * sizeof(RdF4), cudaMemcpyHostToDevice, st));
+        RD_CUDA(cudaMemcpyAsync(dhi, hi.data(), (size_t)n * sizeof(RdF4), cudaMemcpyHostToDevice, st));
+    }
+    RdBuildResult r;
+    int rc = rd_build_wide_bvh(p, dlo, dhi, n, &r);
+    if (rc) return rc;
+    RdHandleObj* o = new RdHandleObj();
+    memset(o, 0, sizeof(*o));
+    o->magic = RD_HANDLE_MAGIC; o->kind = RD_H_TLAS;
+    o->dnodes = r.nodes; o->dleaf = r.leafPrim; o->instanceCount = n; o->nodeCount = r.nodeCount;
+    RD_CUDA(cudaMalloc(&o->dinst, n ? (size_t)n * sizeof(RdInstance) : 16));
+    if (n) RD_CUDA(cudaMemcpyAsync(o->dinst, inst.data(), (size_t)n * sizeof(RdInstance), cudaMemcpyHostToDevice, st));
+    RdScene S; memset(&S, 0, sizeof(S));
+    S.nodes = r.nodes; S.leafInstances = r.leafPrim; S.instances = (const RdInstance*)o->dinst;
+    S.instanceCount = n; S.nodeCount = r.nodeCount; S.status = p->dstatus;
+    RD_CUDA(cudaMalloc(&o->dptr, sizeof(RdScene)));
+    RD_CUDA(cudaMemcpyAsync(o->dptr, &S, sizeof(S), cudaMemcpyHostToDevice, st));
+    RD_CUDA(cudaStreamSynchronize(st));
+    o->size = sizeof(RdScene);
+    o->arg = (uint64_t)(uintptr_t)o->dptr;
+    *out = o;
+    return RD_OK;
+}

@@ -1,0 +1,86 @@
+// rd_internal.h -- host-side objects behind the C ABI (include/radiance_b200.h).
+#ifndef RD_INTERNAL_H
+#define RD_INTERNAL_H
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/radiance_b200.h"
+#include "rd_types.h"
+
+enum RdHandleKind { RD_H_BUFFER = 1, RD_H_IMAGE_ARRAY = 2, RD_H_SAMPLER = 3, RD_H_TLAS = 4 };
+
+// device-side image descriptor, must match rd_image_array_desc in shader/cl_compat.h
+struct RdImageArrayDesc { const unsigned char* texels; unsigned width, height, layers, pad; };
+
+struct RdHandleObj {
+    uint32_t magic;          // 'RDHO'
+    RdHandleKind kind;
+    void* dptr;              // buffer storage / texel storage / RdScene*
+    size_t size;             // bytes of dptr
+    uint64_t arg;            // the 8-byte kernel parameter this handle binds as
+    // image array
+    unsigned width, height, layers;
+    void* ddesc;             // device RdImageArrayDesc
+    // top-level structure
+    void* dnodes; void* dleaf; void* dinst;
+    unsigned instanceCount, nodeCount;
+};
+#define RD_HANDLE_MAGIC 0x4f484452u
+
+struct rd_blas {
+    RdNode8* nodes; RdTri* tris;
+    uint32_t nodeCount, triCount, levels;
+    float lo[3], hi[3];
+};
+
+struct rd_module {
+    CUmodule mod; CUfunction raygen;
+    int numRegs; int localBytes;
+    std::string ptxInfo;
+};
+
+struct rd_platform {
+    int device;
+    cudaStream_t stream;
+    uint32_t* dstatus;        // [0] stack overflow flag, [1..] spare
+    unsigned long long* dcounters;   // trace counters [nodes, tris, rays] + work counter at [4]
+    std::vector<uint64_t> boundArgs;
+    rd_module* boundModule;
+    std::string sbtJson;
+    long optFmad, optTile, optBlock;
+    uint64_t launches;
+    int smCount;
+};
+
+void rd_set_error(const char* fmt, ...);
+#define RD_CUDA(call)                                                                       \
+    do {                                                                                    \
+        cudaError_t _e = (call);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            rd_set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return RD_E_CUDA;                                                               \
+        }                                                                                   \
+    } while (0)
+#define RD_CU(call)                                                                         \
+    do {                                                                                    \
+        CUresult _e = (call);                                                               \
+        if (_e != CUDA_SUCCESS) {                                                           \
+            const char* _s = 0; cuGetErrorString(_e, &_s);                                  \
+            rd_set_error("%s failed: %s (%s:%d)", #call, _s ? _s : "?", __FILE__, __LINE__); \
+            return RD_E_CUDA;                                                               \
+        }                                                                                   \
+    } while (0)
+
+static inline RdHandleObj* rd_obj(rd_handle h)
+{
+    RdHandleObj* o = (RdHandleObj*)h;
+    return (o && o->magic == RD_HANDLE_MAGIC) ? o : 0;
+}
+
+// rd_build.cu: generic device build over primitive boxes (dlo/dhi: n float4 each, device)
+struct RdBuildResult { RdNode8* nodes; uint32_t* leafPrim; uint32_t nodeCount, levels; float lo[3], hi[3]; };
+int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out);
+
+#endif

@@ -210,6 +210,7 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
             RdU4 n0, n1, n2, n3, n4;
             RD_LOAD_U4(n0, &n->w[0]); RD_LOAD_U4(n1, &n->w[1]); RD_LOAD_U4(n2, &n->w[2]);
             RD_LOAD_U4(n3, &n->w[3]); RD_LOAD_U4(n4, &n->w[4]);
+            onCandidate.countNode();
             const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
             ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
             tg.x = n1.y; tg.y = hm & 0x00ffffffu;
@@ -239,6 +240,7 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
             const RdTri* tr = tris + (tg.x + k);
             RdF4 a, b, c;
             RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
+            onCandidate.countTri();
             float t, b1, b2;
             if (rd_intersect_triangle(f.ox, f.oy, f.oz, f.dx, f.dy, f.dz, a.x, a.y, a.z, b.x, b.y, b.z,
                                       c.x, c.y, c.z, &t, &b1, &b2) &&
@@ -261,7 +263,22 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
     return any;
 }
 
-struct RdNoAnyHit { RD_HD bool operator()(const RdHitRec&) const { return true; } };
-struct RdFirstHit { RD_HD bool operator()(const RdHitRec&) const { return false; } };
+// callback interface: operator() = any-hit; countNode / countTri = optional fetch statistics
+struct RdNoAnyHit {
+    RD_HD bool operator()(const RdHitRec&) const { return true; }
+    RD_HD void countNode() const {}
+    RD_HD void countTri() const {}
+};
+struct RdFirstHit {
+    RD_HD bool operator()(const RdHitRec&) const { return false; }
+    RD_HD void countNode() const {}
+    RD_HD void countTri() const {}
+};
+struct RdCountingHit {   // counters-on build of the same traversal (roofline bytes per ray)
+    bool terminate; rd_u32 nodes, tris;
+    RD_HD bool operator()(const RdHitRec&) const { return !terminate; }
+    RD_HD void countNode() { nodes++; }
+    RD_HD void countTri() { tris++; }
+};
 
 #endif
