@@ -85,6 +85,11 @@ int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, unsigned n,
  * accepted and ignored like in the reference. */
 int rd_shader_module_create(rd_platform* p, const char* code, unsigned size, const char* name, rd_module** out);
 int rd_module_free(rd_platform* p, rd_module* m);
+/* compile-only variant of the above (no device needed): RD_OK + cubin size, the ptxas statistics are
+ * left in rd_last_error(); on failure RD_E_COMPILE with the compiler log there */
+int rd_shader_compile_check(const char* code, unsigned size, const char* sbt_json, int fmad, size_t* cubinSize);
+/* registers per thread / local bytes of the compiled raygen kernel */
+int rd_module_info(rd_module* m, int out[2]);
 /* samples/sbt.json: rows {raygen, closestHit, anyHit, miss}; row index = dispatcher case label.
  * When set before rd_shader_module_create and the program does not define callHit/callMiss/callAnyHit
  * itself, the dispatchers are generated from the table (tools/genSBT.py semantics). */

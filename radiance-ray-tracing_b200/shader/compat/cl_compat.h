@@ -17,9 +17,14 @@
 #if defined(__CUDACC_RTC__) || defined(__CUDACC__)
 #define RD_DEVICE_BUILD 1
 #define RD_F __device__ __forceinline__
+#define RD_DEV __device__
+// the traversal core must be seen before the OpenCL spellings float4/uint4 are mapped onto the
+// rd_* classes at the end of this file (it uses the CUDA built-in vector types for its loads)
+#include "rd_traverse.h"
 #else
 #define RD_DEVICE_BUILD 0
 #define RD_F inline
+#define RD_DEV
 #include <math.h>
 #include <float.h>
 #include <stdio.h>
@@ -376,7 +381,7 @@ RD_F rd_uint4 convert_uint4(const rd_float4& a) { return rd_uint4((uint)a.x, (ui
 #if RD_DEVICE_BUILD
 // Set by the launcher before each launch: first global id of this launch, total work-items,
 // and the image width used for the optional 8x4 pixel-tile remap (0 = identity mapping).
-extern "C" __constant__ unsigned int rd_launch_info[4];
+extern "C" { __constant__ unsigned int rd_launch_info[4]; }
 RD_F size_t get_global_id(uint dim)
 {
     if (dim != 0) return 0;
@@ -495,15 +500,20 @@ RD_F rd_float4 read_imagef(image2d_array_t img, sampler_t smp, const rd_float4& 
 #define __constant const
 #define __private
 #define __local
+#if !RD_DEVICE_BUILD
+// Under CUDA `__global__` / `__constant__` are themselves macros for __attribute__((global)) /
+// __attribute__((constant)), so the bare OpenCL keywords cannot be object-like macros there; the
+// library rewrites the bare tokens `global`, `constant`, `kernel`, `local`, `private` in the user's
+// source before handing it to NVRTC (csrc/rd_program.cu, rewrite_bare_qualifiers).
 #define global
 #define constant const
+#define kernel
+#endif
 #define restrict __restrict__
 #if RD_DEVICE_BUILD
 #define __kernel extern "C" __global__
-#define kernel extern "C" __global__
 #else
 #define __kernel
-#define kernel
 #endif
 
 #define float2 rd_float2
