@@ -61,6 +61,17 @@ namespace ref_shader1 {
 }  // namespace ref_shader1
 
 // ----------------------------------------------------------------------------------------
+// our own benchmark user programs (radiance-ray-tracing_b200/programs/*.cl) compiled against the
+// REFERENCE runtime headers: same program text on both sides of every image comparison
+#undef DATA_CL
+#undef MATH_CL
+#undef PI
+namespace ref_primary {
+#include "primary.cl"
+#include "primary_dispatch.inc"
+}  // namespace ref_primary
+
+// ----------------------------------------------------------------------------------------
 template <class F>
 static void parallel_range(size_t n, int nthreads, F f)
 {
@@ -162,6 +173,25 @@ void ref_generate_ray(const void* cam48, const unsigned int* rand3, size_t index
     ref_shader1::generateRay((const ref_shader1::PhysicalCamera*)cam48,
                              rd_uint3(rand3[0], rand3[1], rand3[2]), &o, &d);
     for (int k = 0; k < 3; ++k) { o3[k] = o[k]; d3[k] = d[k]; }
+}
+
+#define RD_RAYGEN_ARGS(NS) \
+    (NS::RayTraceProperties*)args[0], (float*)args[1], (uchar*)args[2], (NS::PhysicalCamera*)args[3], \
+    (NS::SceneProperties*)args[4], (NS::MeshInfo*)args[5], (float*)args[6], (uint*)args[7], (float*)args[8], \
+    (float*)args[9], (NS::Material*)args[10], (image2d_array_t)args[11], (sampler_t)(uintptr_t)args[12], \
+    (NS::AccelStruct*)args[13]
+
+// program: 0 = samples/shader.cl, 1 = programs/primary.cl
+void ref_raygen(int program, void* const* args, size_t globalSize, size_t first, size_t count, int nthreads)
+{
+    rd_host_global_size = globalSize;
+    parallel_range(count, nthreads, [=](size_t b, size_t e) {
+        for (size_t i = first + b; i < first + e; ++i) {
+            rd_host_global_id = i;
+            if (program == 0) ref_shader1::raygen(RD_RAYGEN_ARGS(ref_shader1));
+            else if (program == 1) ref_primary::raygen(RD_RAYGEN_ARGS(ref_primary));
+        }
+    });
 }
 
 // NDRange emulation of the shader.cl `raygen` kernel: 14 positional arguments in descriptor-set

@@ -54,6 +54,7 @@ def lib():
         L.ref_intersect_triangle.argtypes = [C.c_void_p] * 4
         L.ref_generate_ray.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_raygen_shader1.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]
+        L.ref_raygen.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]
         assert C.sizeof(RefInstance) == 80
         _lib = L
     return _lib
@@ -155,3 +156,23 @@ def raygen_shader1(args, global_size, first=0, count=None, nthreads=None):
     lib().ref_raygen_shader1(ptrs, int(global_size), int(first),
                              int(global_size - first if count is None else count),
                              nthreads or os.cpu_count() or 1)
+
+
+PROGRAMS = {"shader": 0, "primary": 1}
+
+
+def raygen(program, args, global_size, first=0, count=None, nthreads=None):
+    """NDRange emulation (local size 1, as RD::TraceRays launches it: radiance/src/radiance.cpp:250-259)
+    of a user program's `raygen` built against the reference runtime. program: "shader" =
+    samples/shader.cl, "primary" = radiance-ray-tracing_b200/programs/primary.cl. args: 14 entries in
+    descriptor-set order; numpy arrays by address, ints as raw 8-byte values, None as NULL."""
+    ptrs = (C.c_void_p * 14)()
+    for i, a in enumerate(args):
+        if a is None:
+            ptrs[i] = None
+        elif isinstance(a, np.ndarray):
+            ptrs[i] = a.ctypes.data
+        else:
+            ptrs[i] = int(a)
+    lib().ref_raygen(PROGRAMS[program], ptrs, int(global_size), int(first),
+                     int(global_size - first if count is None else count), nthreads or os.cpu_count() or 1)

@@ -1,0 +1,334 @@
+"""Host-side mirror of the reference's `namespace RD` API on top of the C ABI (include/radiance_b200.h).
+
+Function names, argument order and error behaviour follow radiance/include/radiance.h:88-144 so that
+drivers and tests read like the reference's samples (samples/sample1.cpp:363-443). Everything goes
+through libradiance_b200.so with plain pointers; numpy is only used to hold host arrays. There is no
+CPU execution path: without the CUDA library / a device every call raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libradiance_b200.so")
+
+RD_ADDRESS_CLAMP_TO_EDGE, RD_ADDRESS_CLAMP, RD_ADDRESS_REPEAT, RD_ADDRESS_MIRRORED_REPEAT = 0x1131, 0x1132, 0x1133, 0x1134
+RD_FILTER_NEAREST, RD_FILTER_LINEAR = 0x1140, 0x1141
+TRACE_TERMINATE_ON_FIRST_HIT, TRACE_COUNTERS = 1, 2
+
+# every symbol include/radiance_b200.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "rd_last_error", "rd_platform_create", "rd_platform_destroy", "rd_platform_stream", "rd_platform_sync",
+    "rd_buffer_create", "rd_image_create", "rd_image_array_create", "rd_sampler_create", "rd_buffer_write",
+    "rd_buffer_read", "rd_image_write", "rd_image_read", "rd_handle_free", "rd_handle_device_ptr",
+    "rd_blas_build", "rd_blas_build_device", "rd_blas_free", "rd_blas_stats", "rd_tlas_build",
+    "rd_shader_module_create", "rd_module_free", "rd_shader_compile_check", "rd_module_info", "rd_sbt_load_json",
+    "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_ray_list",
+    "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count",
+]
+
+
+class RadianceError(RuntimeError):
+    """The reference aborts the process on any error (clcontext.h:27-47); the mirror raises."""
+
+
+class InstanceDesc(C.Structure):
+    _fields_ = [("transform", C.c_float * 16), ("SBTOffset", C.c_uint32), ("customInstanceID", C.c_uint32),
+                ("bottomAccelStruct", C.c_void_p)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RadianceError("libradiance_b200.so is not built (run __graft_entry__.build()); there is no fallback path")
+        L = C.CDLL(LIB_PATH)
+        L.rd_last_error.restype = C.c_char_p
+        L.rd_platform_stream.restype = C.c_void_p
+        L.rd_platform_stream.argtypes = [C.c_void_p]
+        L.rd_handle_device_ptr.restype = C.c_void_p
+        L.rd_handle_device_ptr.argtypes = [C.c_void_p]
+        L.rd_launch_count.restype = C.c_uint64
+        L.rd_launch_count.argtypes = [C.c_void_p]
+        vp, sz, u = C.c_void_p, C.c_size_t, C.c_uint
+        sigs = {
+            "rd_platform_create": [C.c_int, C.POINTER(vp)], "rd_platform_destroy": [vp], "rd_platform_sync": [vp],
+            "rd_buffer_create": [vp, sz, C.POINTER(vp)], "rd_image_create": [vp, u, u, C.POINTER(vp)],
+            "rd_image_array_create": [vp, u, u, u, C.POINTER(vp)], "rd_sampler_create": [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)],
+            "rd_buffer_write": [vp, vp, sz, vp, sz], "rd_buffer_read": [vp, vp, sz, vp, sz],
+            "rd_image_write": [vp, vp, u, u, sz, vp], "rd_image_read": [vp, vp, u, u, sz, vp],
+            "rd_handle_free": [vp, vp], "rd_blas_build": [vp, vp, u, vp, u, C.POINTER(vp)],
+            "rd_blas_build_device": [vp, vp, u, vp, u, C.POINTER(vp)], "rd_blas_free": [vp, vp],
+            "rd_blas_stats": [vp, C.POINTER(C.c_uint64)], "rd_tlas_build": [vp, vp, u, C.POINTER(vp)],
+            "rd_shader_module_create": [vp, C.c_char_p, u, C.c_char_p, C.POINTER(vp)], "rd_module_free": [vp, vp],
+            "rd_shader_compile_check": [C.c_char_p, u, C.c_char_p, C.c_int, C.POINTER(sz)],
+            "rd_module_info": [vp, C.POINTER(C.c_int)], "rd_sbt_load_json": [vp, C.c_char_p],
+            "rd_pipeline_bind": [vp, C.POINTER(vp), u], "rd_descriptors_bind": [vp, C.POINTER(vp), u],
+            "rd_trace_rays": [vp, u, u, u, u, u], "rd_trace_rays_async": [vp, u, u],
+            "rd_trace_ray_list": [vp, vp, vp, vp, vp, vp, sz, u], "rd_trace_counters": [vp, C.POINTER(C.c_uint64)],
+            "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
+        }
+        for name, args in sigs.items():
+            f = getattr(L, name)
+            f.argtypes, f.restype = args, C.c_int
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise RadianceError("radiance_b200 error %d: %s" % (rc, lib().rd_last_error().decode(errors="replace")))
+
+
+def last_message():
+    return lib().rd_last_error().decode(errors="replace")
+
+
+class Platform:
+    """RD::Platform (radiance.h:146-174). GetPlatform() returns a per-process singleton per device."""
+    _instances = {}
+
+    def __init__(self, device=-1):
+        self.handle = C.c_void_p()
+        _check(lib().rd_platform_create(device, C.byref(self.handle)))
+        self.activePipeline = None
+
+    @staticmethod
+    def GetPlatform(device=-1):
+        if device not in Platform._instances:
+            Platform._instances[device] = Platform(device)
+        return Platform._instances[device]
+
+    def stream(self):
+        return lib().rd_platform_stream(self.handle)
+
+    def sync(self):
+        _check(lib().rd_platform_sync(self.handle))
+
+    def launch_count(self):
+        return int(lib().rd_launch_count(self.handle))
+
+    def set_option(self, key, value):
+        _check(lib().rd_set_option(self.handle, key.encode(), int(value)))
+
+
+class Mesh:
+    """RD::Mesh (radiance.h:32-36): vertexData (nv,3) float32, indexData (nt,3) uint32."""
+
+    def __init__(self, vertexData, indexData):
+        self.vertexData = np.ascontiguousarray(vertexData, np.float32).reshape(-1, 3)
+        self.indexData = np.ascontiguousarray(indexData, np.uint32).reshape(-1, 3)
+
+
+class Instance:
+    """RD::Instance (radiance.h:48-55)."""
+
+    def __init__(self, transform, SBTOffset, customInstanceID, bottomAccelStruct):
+        self.transform = np.ascontiguousarray(transform, np.float32).reshape(4, 4)
+        self.SBTOffset, self.customInstanceID, self.bottomAccelStruct = int(SBTOffset), int(customInstanceID), bottomAccelStruct
+
+
+class BottomAccelStruct:
+    def __init__(self, plt, handle):
+        self.plt, self.handle = plt, handle
+
+    def stats(self):
+        out = (C.c_uint64 * 4)()
+        _check(lib().rd_blas_stats(self.handle, out))
+        return {"nodes": out[0], "triangles": out[1], "levels": out[2], "bytes": out[3]}
+
+
+class Handle:
+    """Buffer / Image / ImageArray / Sampler / TopAccelStruct descriptor handle."""
+
+    def __init__(self, plt, handle, size=0, keep=None):
+        self.plt, self.handle, self.size, self._keep = plt, handle, size, keep
+
+    def device_ptr(self):
+        return lib().rd_handle_device_ptr(self.handle)
+
+    def free(self):
+        if self.handle:
+            lib().rd_handle_free(self.plt.handle, self.handle)
+            self.handle = None
+
+
+def BuildAccelStruct(plt, arg):
+    """Both overloads of RD::BuildAccelStruct (radiance.cpp:20-52 for a Mesh, :54-84 for instances)."""
+    if isinstance(arg, Mesh):
+        out = C.c_void_p()
+        v, t = arg.vertexData, arg.indexData
+        _check(lib().rd_blas_build(plt.handle, v.ctypes.data, v.shape[0], t.ctypes.data, t.shape[0], C.byref(out)))
+        return BottomAccelStruct(plt, out)
+    instances = list(arg)
+    arr = (InstanceDesc * max(1, len(instances)))()
+    for k, inst in enumerate(instances):
+        arr[k].transform[:] = [float(x) for x in inst.transform.reshape(16)]
+        arr[k].SBTOffset, arr[k].customInstanceID = inst.SBTOffset, inst.customInstanceID
+        arr[k].bottomAccelStruct = inst.bottomAccelStruct.handle
+    out = C.c_void_p()
+    _check(lib().rd_tlas_build(plt.handle, arr, len(instances), C.byref(out)))
+    return Handle(plt, out, keep=[i.bottomAccelStruct for i in instances])
+
+
+def CreateBuffer(plt, size):
+    out = C.c_void_p()
+    _check(lib().rd_buffer_create(plt.handle, int(size), C.byref(out)))
+    return Handle(plt, out, int(size))
+
+
+def CreateImage(plt, width, height):
+    out = C.c_void_p()
+    _check(lib().rd_image_create(plt.handle, width, height, C.byref(out)))
+    return Handle(plt, out, width * height * 4)
+
+
+def CreateImageArray(plt, width, height, arraySize):
+    out = C.c_void_p()
+    _check(lib().rd_image_array_create(plt.handle, width, height, arraySize, C.byref(out)))
+    return Handle(plt, out, width * height * 4 * arraySize)
+
+
+def CreateSampler(plt, addressingMode, filterMode):
+    out = C.c_void_p()
+    _check(lib().rd_sampler_create(plt.handle, addressingMode, filterMode, C.byref(out)))
+    return Handle(plt, out)
+
+
+def _host_ptr(data, size):
+    if isinstance(data, np.ndarray):
+        if not data.flags["C_CONTIGUOUS"]:
+            raise RadianceError("host array must be C-contiguous")
+        if data.nbytes < size:
+            raise RadianceError("host array smaller than the requested transfer")
+        return data.ctypes.data
+    return data
+
+
+def WriteBuffer(plt, handle, size, data, offset=0):
+    _check(lib().rd_buffer_write(plt.handle, handle.handle, int(size), _host_ptr(data, size), int(offset)))
+
+
+def ReadBuffer(plt, handle, size, data, offset=0):
+    _check(lib().rd_buffer_read(plt.handle, handle.handle, int(size), _host_ptr(data, size), int(offset)))
+
+
+def WriteImage(plt, handle, width, height, arrayIndex, data):
+    _check(lib().rd_image_write(plt.handle, handle.handle, width, height, arrayIndex, _host_ptr(data, width * height * 4)))
+
+
+def ReadImage(plt, handle, width, height, arrayIndex, data):
+    _check(lib().rd_image_read(plt.handle, handle.handle, width, height, arrayIndex, _host_ptr(data, width * height * 4)))
+
+
+def CreateDescriptorSet(handles):
+    return list(handles)
+
+
+def CreatePipelineLayout(descriptorTypes):
+    return list(descriptorTypes)
+
+
+class ShaderModule:
+    def __init__(self, plt, handle):
+        self.plt, self.handle = plt, handle
+
+    def info(self):
+        out = (C.c_int * 2)()
+        _check(lib().rd_module_info(self.handle, out))
+        return {"registers": out[0], "local_bytes": out[1]}
+
+
+def LoadSBT(plt, json_text):
+    """samples/sbt.json text; dispatchers are generated when the program does not define them."""
+    _check(lib().rd_sbt_load_json(plt.handle, json_text.encode() if isinstance(json_text, str) else json_text))
+
+
+def CreateShaderModule(plt, code, size=0, name="raygen"):
+    src = code.encode() if isinstance(code, str) else bytes(code)
+    out = C.c_void_p()
+    _check(lib().rd_shader_module_create(plt.handle, src, len(src) if not size else size, name.encode(), C.byref(out)))
+    return ShaderModule(plt, out)
+
+
+def CompileCheck(code, sbt_json=None, fmad=True):
+    """NVRTC compile without a device; returns (cubin_bytes, ptxas_log)."""
+    src = code.encode() if isinstance(code, str) else bytes(code)
+    n = C.c_size_t(0)
+    sbt = None if sbt_json is None else (sbt_json.encode() if isinstance(sbt_json, str) else sbt_json)
+    _check(lib().rd_shader_compile_check(src, len(src), sbt, int(bool(fmad)), C.byref(n)))
+    return n.value, last_message()
+
+
+class PipelineCreateInfo:
+    def __init__(self, maxRayRecursionDepth=1, layout=None, modules=None, groups=None):
+        self.maxRayRecursionDepth, self.layout = maxRayRecursionDepth, layout or []
+        self.modules, self.groups = modules or [], groups or []
+
+
+def CreatePipeline(info):
+    return info
+
+
+def BindPipeline(plt, pipeline):
+    mods = (C.c_void_p * max(1, len(pipeline.modules)))(*[m.handle for m in pipeline.modules])
+    _check(lib().rd_pipeline_bind(plt.handle, mods, len(pipeline.modules)))
+    plt.activePipeline = pipeline
+
+
+def BindDescriptorSet(plt, descriptorSet):
+    arr = (C.c_void_p * max(1, len(descriptorSet)))(*[h.handle for h in descriptorSet])
+    _check(lib().rd_descriptors_bind(plt.handle, arr, len(descriptorSet)))
+    plt._descriptors = list(descriptorSet)
+
+
+def TraceRays(plt, raygenGroupIndex, missGroupIndex, hitGroupIndex, width, height):
+    _check(lib().rd_trace_rays(plt.handle, raygenGroupIndex, missGroupIndex, hitGroupIndex, width, height))
+
+
+def TraceRaysAsync(plt, width, height):
+    _check(lib().rd_trace_rays_async(plt.handle, width, height))
+
+
+# ---- wavefront building blocks (no reference counterpart) ----------------------------------------
+HIT_DTYPE = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("prim", "<u4")])
+
+
+def TraceRayList(plt, tlas, rayA, rayB, hitA, hitB, n, flags=0):
+    _check(lib().rd_trace_ray_list(plt.handle, tlas.handle, rayA.handle, rayB.handle, hitA.handle, hitB.handle, int(n), flags))
+
+
+def TraceCounters(plt):
+    out = (C.c_uint64 * 3)()
+    _check(lib().rd_trace_counters(plt.handle, out))
+    return {"nodes": out[0], "tris": out[1], "rays": out[2]}
+
+
+def GeneratePrimaryRays(plt, camera, frameID, totalSamples, width, height, rayA, rayB):
+    _check(lib().rd_generate_primary_rays(plt.handle, camera.handle, frameID, totalSamples, width, height, rayA.handle, rayB.handle))
+
+
+def trace_host_rays(plt, tlas, rays, flags=0):
+    """Convenience for tests: rays (n,8) float32 {o,tmin,d,tmax} on the host -> (hitA records, instanceIDs)."""
+    rays = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+    n = rays.shape[0]
+    a, b = np.ascontiguousarray(rays[:, 0:4]), np.ascontiguousarray(rays[:, 4:8])
+    bufs = [CreateBuffer(plt, max(16, n * 16)) for _ in range(3)] + [CreateBuffer(plt, max(16, n * 4))]
+    try:
+        if n:
+            WriteBuffer(plt, bufs[0], n * 16, a)
+            WriteBuffer(plt, bufs[1], n * 16, b)
+        TraceRayList(plt, tlas, bufs[0], bufs[1], bufs[2], bufs[3], n, flags)
+        plt.sync()
+        hitA, hitB = np.zeros(n, HIT_DTYPE), np.zeros(n, np.uint32)
+        if n:
+            ReadBuffer(plt, bufs[2], n * 16, hitA)
+            ReadBuffer(plt, bufs[3], n * 4, hitB)
+        return hitA, hitB
+    finally:
+        for h in bufs:
+            h.free()

@@ -243,3 +243,107 @@ def pinhole_rays(cam, tmin=0.001, tmax=1000.0, stride=1, jitter=None):
     rays[:, 4:7] = d.astype(np.float32)
     rays[:, 7] = tmax
     return rays
+
+
+# ---- device upload / rendering helpers (through the RD mirror; used by tests, smoke() and bench.py) ----
+import os as _os
+
+PROGRAM_DIR = _os.path.join(_os.path.dirname(_os.path.abspath(__file__)), "programs")
+
+
+def program_source(name):
+    """(source, sbt_json or None) of a user program shipped in programs/."""
+    src = open(_os.path.join(PROGRAM_DIR, name + ".cl")).read()
+    sbt_path = _os.path.join(PROGRAM_DIR, name + "_sbt.json")
+    return src, (open(sbt_path).read() if _os.path.exists(sbt_path) else None)
+
+
+def build_scene(plt, bundle):
+    """BuildAccelStruct for every mesh and for the instance list (samples/sample1.cpp-style)."""
+    from . import rd
+    blas = [rd.BuildAccelStruct(plt, rd.Mesh(v, t)) for (v, t) in bundle.meshes]
+    inst = [rd.Instance(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in bundle.instances]
+    return rd.BuildAccelStruct(plt, inst), blas
+
+
+def build_reference_scene(ref, bundle):
+    """Same scene through the reference's own host builder (oracle/_ref)."""
+    blas = [ref.RefBlas(v, t) for (v, t) in bundle.meshes]
+    return ref.RefTlas([(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in bundle.instances])
+
+
+class DeviceScene:
+    """The 14-descriptor set of samples/sample1.cpp:387-394 / tools/sceneBuilder.h:8-17 on the device."""
+
+    def __init__(self, plt, bundle, tlas, width, height, rt=None, cam=None):
+        from . import rd
+        self.plt, self.width, self.height = plt, width, height
+        self.rtprop = np.array(rt if rt is not None else rtprop(0, 1, 1, 0), RTPROP_DTYPE).reshape(())
+        self.cam = np.array(cam if cam is not None else bundle.camera, CAMERA_DTYPE).reshape(()).copy()
+        self.cam["widthPixel"], self.cam["heightPixel"] = width, height
+        n = width * height
+
+        def buf(arr):
+            arr = np.ascontiguousarray(arr)
+            h = rd.CreateBuffer(plt, max(16, arr.nbytes))
+            if arr.nbytes:
+                rd.WriteBuffer(plt, h, arr.nbytes, arr)
+            return h
+        self.rdRTProp = buf(self.rtprop.reshape(1))
+        self.rdImageScratch = rd.CreateBuffer(plt, n * 16)
+        self.rdImage = rd.CreateImage(plt, width, height)
+        self.rdCam = buf(self.cam.reshape(1))
+        self.rdScene = buf(np.array(bundle.scene).reshape(1))
+        self.rdMeshInfo, self.rdVertex, self.rdIndex = buf(bundle.meshInfoData), buf(bundle.vertexData), buf(bundle.indexData)
+        self.rdUV, self.rdNormal, self.rdMaterial = buf(bundle.uvData), buf(bundle.normalData), buf(bundle.materials)
+        self.rdTextures = rd.CreateImageArray(plt, 4, 4, 1)
+        self.rdSampler = rd.CreateSampler(plt, rd.RD_ADDRESS_REPEAT, rd.RD_FILTER_LINEAR)
+        self.tlas = tlas
+        self.descriptors = rd.CreateDescriptorSet([
+            self.rdRTProp, self.rdImageScratch, self.rdImage, self.rdCam, self.rdScene, self.rdMeshInfo, self.rdVertex,
+            self.rdIndex, self.rdUV, self.rdNormal, self.rdMaterial, self.rdTextures, self.rdSampler, tlas])
+
+    def set_rtprop(self, total, batch, depth, debug=0):
+        from . import rd
+        self.rtprop = rtprop(total, batch, depth, debug)
+        rd.WriteBuffer(self.plt, self.rdRTProp, 16, self.rtprop.reshape(1))
+
+    def read_image(self):
+        from . import rd
+        img = np.zeros((self.height, self.width, 4), np.uint8)
+        rd.ReadBuffer(self.plt, self.rdImage, img.nbytes, img)
+        return img
+
+    def read_scratch(self):
+        from . import rd
+        s = np.zeros((self.height, self.width, 4), np.float32)
+        rd.ReadBuffer(self.plt, self.rdImageScratch, s.nbytes, s)
+        return s
+
+    def host_args(self):
+        """The same 14 arguments as host arrays for the CPU oracle's raygen (None = unused descriptor)."""
+        n = self.width * self.height
+        return {"rtprop": self.rtprop.reshape(1).copy(), "scratch": np.zeros(n * 4, np.float32), "image": np.zeros(n * 4, np.uint8),
+                "cam": self.cam.reshape(1).copy()}
+
+
+def make_pipeline(plt, program="primary", source=None, sbt=None):
+    from . import rd
+    if source is None:
+        source, sbt = program_source(program)
+    if sbt is not None:
+        rd.LoadSBT(plt, sbt)
+    module = rd.CreateShaderModule(plt, source, 0, "raygen")
+    pipe = rd.CreatePipeline(rd.PipelineCreateInfo(2, [], [module], []))
+    return pipe, module
+
+
+def render_primary(plt, bundle, tlas, width, height, program="primary", batch=1, depth=1):
+    """One TraceRays call of a shipped user program; returns the RGBA8 image (H,W,4)."""
+    from . import rd
+    ds = DeviceScene(plt, bundle, tlas, width, height, rtprop(0, batch, depth, 0))
+    pipe, _ = make_pipeline(plt, program)
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, width, height)
+    return ds.read_image()

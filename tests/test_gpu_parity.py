@@ -1,0 +1,131 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the reference's own code (oracle/_ref)
+on the same seeded inputs. Bars (BASELINE.json north_star): hit / instance IDs bit-exact except a
+<= 1e-4 fraction of near-tie rays, t within 1e-5 relative, images within a stated RMSE."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ID_TIE_BUDGET = 1e-4
+T_REL_TOL = 1e-5
+IMAGE_RMSE_U8 = 1.0   # in 8-bit levels, equal sample counts and identical RNG streams
+
+
+def compare_hits(hitA, hitB, exp, id_budget=ID_TIE_BUDGET):
+    hit_g = hitA["t"] < 3e38
+    hit_r = exp["hit"] == 1
+    mism = hit_g != hit_r
+    assert mism.mean() <= id_budget, "hit/miss disagreement on %d of %d rays" % (mism.sum(), len(mism))
+    both = hit_g & hit_r
+    bad = (hitA["prim"][both] != exp["prim"][both]) | (hitB[both] != exp["inst"][both])
+    assert bad.mean() <= id_budget if both.any() else True, "ID mismatch fraction %g" % bad.mean()
+    ok = both.copy()
+    ok[both] = ~bad
+    if ok.any():
+        rel = np.abs(hitA["t"][ok] - exp["t"][ok]) / exp["t"][ok]
+        assert rel.max() <= T_REL_TOL
+        # barycentrics come from the same expressions
+        assert np.abs(hitA["b1"][ok] - exp["bary"][ok, 1]).max() <= 1e-4
+        assert np.abs(hitA["b2"][ok] - exp["bary"][ok, 2]).max() <= 1e-4
+    return both.sum()
+
+
+def offcentre_cornell(scenes):
+    b = scenes.cornell_like()
+    b.camera["x"], b.camera["y"] = 0.013, 1.037   # keeps pixel rows off the exactly shared wall edges
+    return b
+
+
+def test_cornell_ray_list_matches_reference(pkg, plt, ref):
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    rays = scenes.pinhole_rays(b.camera, stride=2, jitter=(0.37, 0.61))
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    exp = scenes.build_reference_scene(ref, b).trace(rays)
+    assert compare_hits(hitA, hitB, exp) > 50000
+
+
+def test_heightfield_ray_list_matches_reference(pkg, plt, ref):
+    rd, scenes = pkg.rd, pkg.scenes
+    b = scenes.heightfield_scene(224, 640, 360)   # 100 352 triangles
+    tlas, blas = scenes.build_scene(plt, b)
+    st = blas[0].stats()
+    assert st["triangles"] == 2 * 224 * 224 and st["nodes"] > 1000
+    rays = scenes.pinhole_rays(b.camera, jitter=(0.29, 0.71))
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    exp = scenes.build_reference_scene(ref, b).trace(rays)
+    assert compare_hits(hitA, hitB, exp) > 100000
+
+
+def test_first_hit_mode_agrees_on_occlusion(pkg, plt, ref):
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    rays = scenes.pinhole_rays(b.camera, stride=4, jitter=(0.37, 0.61))
+    hitA, _ = rd.trace_host_rays(plt, tlas, rays, rd.TRACE_TERMINATE_ON_FIRST_HIT)
+    exp = scenes.build_reference_scene(ref, b).trace(rays, terminate_on_first_hit=True)
+    assert np.array_equal(hitA["t"] < 3e38, exp["hit"] == 1)
+    assert (exp["anyhit_calls"][exp["hit"] == 1] >= 1).all()
+
+
+def test_edge_cases(pkg, plt):
+    rd, scenes = pkg.rd, pkg.scenes
+    # single triangle, many instances of it, rays that miss everything, an empty ray list
+    v = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    t = np.array([[0, 1, 2]], np.uint32)
+    blas = rd.BuildAccelStruct(plt, rd.Mesh(v, t))
+    inst = [rd.Instance(scenes.translate(2.0 * i, 0, 0), 0, i, blas) for i in range(20)]
+    tlas = rd.BuildAccelStruct(plt, inst)
+    rays = np.zeros((20, 8), np.float32)
+    rays[:, 0] = 2.0 * np.arange(20) + 0.25
+    rays[:, 1], rays[:, 2], rays[:, 3] = 0.25, 1.0, 0.001
+    rays[:, 6], rays[:, 7] = -1.0, 1000.0
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    assert np.array_equal(hitB, np.arange(20, dtype=np.uint32))
+    assert np.allclose(hitA["t"], 1.0) and (hitA["prim"] == 0).all()
+    rays[:, 6] = 1.0   # pointing away
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    assert (hitA["t"] > 3e38).all() and (hitB == 0xffffffff).all()
+    hitA, hitB = rd.trace_host_rays(plt, tlas, np.zeros((0, 8), np.float32))
+    assert len(hitA) == 0
+    # Tmin / Tmax are exclusive (radiance/shader/radiance.cl:90-91)
+    r = np.array([[0.25, 0.25, 1.0, 1.0, 0, 0, -1.0, 1000.0], [0.25, 0.25, 1.0, 0.001, 0, 0, -1.0, 1.0]], np.float32)
+    hitA, _ = rd.trace_host_rays(plt, tlas, r)
+    assert (hitA["t"] > 3e38).all()
+    # empty mesh and empty instance list build and trace as all-miss
+    eb = rd.BuildAccelStruct(plt, rd.Mesh(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.uint32)))
+    et = rd.BuildAccelStruct(plt, [rd.Instance(np.eye(4), 0, 0, eb)])
+    hitA, _ = rd.trace_host_rays(plt, et, rays)
+    assert (hitA["t"] > 3e38).all()
+    et = rd.BuildAccelStruct(plt, [])
+    hitA, _ = rd.trace_host_rays(plt, et, rays)
+    assert (hitA["t"] > 3e38).all()
+
+
+def reference_image(ref, scenes, b, program, width, height, rt):
+    cam = np.array(b.camera).reshape(()).copy()
+    cam["widthPixel"], cam["heightPixel"] = width, height
+    n = width * height
+    scratch, image = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
+    tl = scenes.build_reference_scene(ref, b)
+    args = [np.array(rt).reshape(1), scratch, image, cam.reshape(1), np.array(b.scene).reshape(1), b.meshInfoData,
+            b.vertexData, b.indexData, b.uvData, b.normalData, b.materials, None, 0, tl.blob]
+    ref.raygen(program, args, n)
+    return image.reshape(height, width, 4), scratch.reshape(height, width, 4)
+
+
+def test_primary_program_image_matches_reference(pkg, plt, ref):
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 320, 240
+    launches = plt.launch_count()
+    img = scenes.render_primary(plt, b, tlas, w, h, "primary", batch=2)
+    assert plt.launch_count() > launches
+    exp, _ = reference_image(ref, scenes, b, "primary", w, h, scenes.rtprop(0, 2, 1, 0))
+    d = img[..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+    rmse = np.sqrt((d * d).mean())
+    assert rmse <= IMAGE_RMSE_U8, "RMSE %g" % rmse
+    assert (np.abs(d).max(axis=-1) > 8).mean() <= 1e-3   # isolated edge pixels only
+    assert (img[..., 3] == 255).all()
