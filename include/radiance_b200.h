@@ -105,6 +105,10 @@ int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned missGroupI
                   unsigned width, unsigned height);
 /* same without the final host synchronisation (for device-side event timing) */
 int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height);
+/* work-items [first, first+count) of the width*height NDRange only (count 0 = to the end); with the
+ * 8x4 tile mapping a contiguous range is a contiguous run of screen tiles: the multi-GPU partition unit */
+int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
+                        unsigned long long count);
 
 /* Explicit ray list through the traversal kernel (wavefront building block; used for hit-ID parity
  * against the reference's traceRay, radiance/shader/radiance.cl:254-275).

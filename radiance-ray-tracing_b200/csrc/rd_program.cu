@@ -342,13 +342,20 @@ extern "C" int rd_descriptors_bind(rd_platform* p, const rd_handle* handles, uns
     return RD_OK;
 }
 
-extern "C" int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height)
+// Launches work-items [first, first + count) of the width*height NDRange (count == 0: all of them).
+// With the 8x4 tile mapping on, consecutive work-items of a warp cover one 8x4 pixel tile, so a
+// contiguous range is a contiguous run of screen tiles (the unit of the multi-GPU partition).
+extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
+                                   unsigned long long count)
 {
     if (!p) { rd_set_error("null platform"); return RD_E_ARG; }
     if (!p->boundModule) { rd_set_error("rd_trace_rays: no pipeline bound"); return RD_E_STATE; }
     const unsigned long long total = (unsigned long long)width * height;
     if (!total) return RD_OK;
     if (total > 0xffffffffull) { rd_set_error("rd_trace_rays: more than 2^32 work-items"); return RD_E_ARG; }
+    if (first > total || count > total - first) { rd_set_error("rd_trace_rays_range: range outside the NDRange"); return RD_E_ARG; }
+    if (!count) count = total - first;
+    if (!count) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
     rd_module* m = p->boundModule;
     CUdeviceptr dinfo; size_t infoBytes = 0;
@@ -357,20 +364,25 @@ extern "C" int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned heig
     for (size_t i = 0; i < argv.size(); ++i) argv[i] = &p->boundArgs[i];
     const unsigned block = (unsigned)p->optBlock;
     const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
-    const unsigned full = (unsigned)(total / block), tail = (unsigned)(total % block);
+    const unsigned full = (unsigned)(count / block), tail = (unsigned)(count % block);
     if (full) {
-        const unsigned info[4] = {0u, (unsigned)total, tileW, 0u};
+        const unsigned info[4] = {(unsigned)first, (unsigned)total, tileW, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         RD_CU(cuLaunchKernel(m->raygen, full, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
     if (tail) {
-        const unsigned info[4] = {full * block, (unsigned)total, tileW, 0u};
+        const unsigned info[4] = {(unsigned)first + full * block, (unsigned)total, tileW, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         RD_CU(cuLaunchKernel(m->raygen, 1, 1, 1, tail, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
     return RD_OK;
+}
+
+extern "C" int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height)
+{
+    return rd_trace_rays_range(p, width, height, 0, 0);
 }
 
 extern "C" int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned missGroupIndex, unsigned hitGroupIndex,

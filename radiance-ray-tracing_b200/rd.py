@@ -24,7 +24,7 @@ ABI_SYMBOLS = [
     "rd_buffer_read", "rd_image_write", "rd_image_read", "rd_handle_free", "rd_handle_device_ptr",
     "rd_blas_build", "rd_blas_build_device", "rd_blas_free", "rd_blas_stats", "rd_tlas_build",
     "rd_shader_module_create", "rd_module_free", "rd_shader_compile_check", "rd_module_info", "rd_sbt_load_json",
-    "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_ray_list",
+    "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count",
 ]
 
@@ -68,7 +68,7 @@ def lib():
             "rd_shader_compile_check": [C.c_char_p, u, C.c_char_p, C.c_int, C.POINTER(sz)],
             "rd_module_info": [vp, C.POINTER(C.c_int)], "rd_sbt_load_json": [vp, C.c_char_p],
             "rd_pipeline_bind": [vp, C.POINTER(vp), u], "rd_descriptors_bind": [vp, C.POINTER(vp), u],
-            "rd_trace_rays": [vp, u, u, u, u, u], "rd_trace_rays_async": [vp, u, u],
+            "rd_trace_rays": [vp, u, u, u, u, u], "rd_trace_rays_async": [vp, u, u], "rd_trace_rays_range": [vp, u, u, C.c_ulonglong, C.c_ulonglong],
             "rd_trace_ray_list": [vp, vp, vp, vp, vp, vp, sz, u], "rd_trace_counters": [vp, C.POINTER(C.c_uint64)],
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
         }
@@ -292,6 +292,11 @@ def TraceRays(plt, raygenGroupIndex, missGroupIndex, hitGroupIndex, width, heigh
 
 def TraceRaysAsync(plt, width, height):
     _check(lib().rd_trace_rays_async(plt.handle, width, height))
+
+
+def TraceRaysRange(plt, width, height, first, count):
+    """Work-items [first, first+count) of the NDRange (asynchronous): one GPU's share of the screen tiles."""
+    _check(lib().rd_trace_rays_range(plt.handle, width, height, int(first), int(count)))
 
 
 # ---- wavefront building blocks (no reference counterpart) ----------------------------------------
