@@ -51,6 +51,9 @@ int rd_platform_sync(rd_platform* p);
 
 /* RD::CreateBuffer, radiance/src/radiance.cpp:133-140 */
 int rd_buffer_create(rd_platform* p, size_t size, rd_handle* out);
+/* no reference counterpart: a buffer handle over device memory the caller owns (zero-copy interop with
+ * other CUDA libraries, e.g. the NCCL framebuffer gather); rd_handle_free does not release the memory */
+int rd_buffer_wrap(rd_platform* p, void* device_ptr, size_t size, rd_handle* out);
 /* RD::CreateImage (a plain W*H*4-byte buffer), radiance/src/radiance.cpp:86-93 */
 int rd_image_create(rd_platform* p, unsigned width, unsigned height, rd_handle* out);
 /* RD::CreateImageArray (layered RGBA8), radiance/src/radiance.cpp:96-118 */

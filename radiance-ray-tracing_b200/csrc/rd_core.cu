@@ -92,6 +92,16 @@ extern "C" int rd_buffer_create(rd_platform* p, size_t size, rd_handle* out)
     return RD_OK;
 }
 
+extern "C" int rd_buffer_wrap(rd_platform* p, void* device_ptr, size_t size, rd_handle* out)
+{
+    if (!p || !out || !device_ptr) { rd_set_error("rd_buffer_wrap: null argument"); return RD_E_ARG; }
+    RdHandleObj* o = new_handle(RD_H_BUFFER);
+    o->dptr = device_ptr; o->size = size; o->external = 1;
+    o->arg = (uint64_t)(uintptr_t)device_ptr;
+    *out = o;
+    return RD_OK;
+}
+
 extern "C" int rd_image_create(rd_platform* p, unsigned width, unsigned height, rd_handle* out)
 {
     return rd_buffer_create(p, (size_t)width * height * 4, out);
@@ -191,7 +201,7 @@ extern "C" int rd_handle_free(rd_platform* p, rd_handle h)
     if (!o) return RD_OK;
     if (p) cudaSetDevice(p->device);
     if (o->kind == RD_H_TLAS) { cudaFree(o->dnodes); cudaFree(o->dleaf); cudaFree(o->dinst); }
-    if (o->dptr) cudaFree(o->dptr);
+    if (o->dptr && !o->external) cudaFree(o->dptr);
     if (o->ddesc) cudaFree(o->ddesc);
     o->magic = 0;
     delete o;

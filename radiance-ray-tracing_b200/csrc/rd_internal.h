@@ -26,6 +26,7 @@ struct RdHandleObj {
     // top-level structure
     void* dnodes; void* dleaf; void* dinst;
     unsigned instanceCount, nodeCount;
+    int external;            // dptr is owned by the caller (rd_buffer_wrap)
 };
 #define RD_HANDLE_MAGIC 0x4f484452u
 

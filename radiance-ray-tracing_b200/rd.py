@@ -20,7 +20,7 @@ TRACE_TERMINATE_ON_FIRST_HIT, TRACE_COUNTERS = 1, 2
 # every symbol include/radiance_b200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [
     "rd_last_error", "rd_platform_create", "rd_platform_destroy", "rd_platform_stream", "rd_platform_sync",
-    "rd_buffer_create", "rd_image_create", "rd_image_array_create", "rd_sampler_create", "rd_buffer_write",
+    "rd_buffer_create", "rd_buffer_wrap", "rd_image_create", "rd_image_array_create", "rd_sampler_create", "rd_buffer_write",
     "rd_buffer_read", "rd_image_write", "rd_image_read", "rd_handle_free", "rd_handle_device_ptr",
     "rd_blas_build", "rd_blas_build_device", "rd_blas_free", "rd_blas_stats", "rd_tlas_build",
     "rd_shader_module_create", "rd_module_free", "rd_shader_compile_check", "rd_module_info", "rd_sbt_load_json",
@@ -57,7 +57,7 @@ def lib():
         vp, sz, u = C.c_void_p, C.c_size_t, C.c_uint
         sigs = {
             "rd_platform_create": [C.c_int, C.POINTER(vp)], "rd_platform_destroy": [vp], "rd_platform_sync": [vp],
-            "rd_buffer_create": [vp, sz, C.POINTER(vp)], "rd_image_create": [vp, u, u, C.POINTER(vp)],
+            "rd_buffer_create": [vp, sz, C.POINTER(vp)], "rd_buffer_wrap": [vp, vp, sz, C.POINTER(vp)], "rd_image_create": [vp, u, u, C.POINTER(vp)],
             "rd_image_array_create": [vp, u, u, u, C.POINTER(vp)], "rd_sampler_create": [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)],
             "rd_buffer_write": [vp, vp, sz, vp, sz], "rd_buffer_read": [vp, vp, sz, vp, sz],
             "rd_image_write": [vp, vp, u, u, sz, vp], "rd_image_read": [vp, vp, u, u, sz, vp],
@@ -179,6 +179,13 @@ def CreateBuffer(plt, size):
     out = C.c_void_p()
     _check(lib().rd_buffer_create(plt.handle, int(size), C.byref(out)))
     return Handle(plt, out, int(size))
+
+
+def WrapBuffer(plt, device_ptr, size, owner=None):
+    """Buffer handle over caller-owned device memory (e.g. a torch tensor's data_ptr())."""
+    out = C.c_void_p()
+    _check(lib().rd_buffer_wrap(plt.handle, C.c_void_p(int(device_ptr)), int(size), C.byref(out)))
+    return Handle(plt, out, int(size), keep=owner)
 
 
 def CreateImage(plt, width, height):
