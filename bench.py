@@ -106,3 +106,197 @@ def reference_arm(args, rank, world):
                       "config": {"workload": WORKLOAD, "sample": sample},
                       "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
                       "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+def tile_row_range(rank, world):
+    """Contiguous run of 8x4-tile rows owned by `rank`: (first work-item, count, first pixel row, rows)."""
+    tile_rows = HEIGHT // 4
+    r0, r1 = tile_rows * rank // world, tile_rows * (rank + 1) // world
+    return r0 * 4 * WIDTH, (r1 - r0) * 4 * WIDTH, r0 * 4, (r1 - r0) * 4
+
+
+def cpu_baseline_leg(pkg, ref, bundle):
+    """Reference CPU path on a bounded sample (rank 0, N=1 only): see reference_arm for the sample."""
+    scenes = pkg.scenes
+    cores = os.cpu_count() or 1
+    t0 = time.time()
+    tl = scenes.build_reference_scene(ref, bundle)
+    build_s = time.time() - t0
+    n = WIDTH * HEIGHT
+    host = [np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1), np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8),
+            np.array(bundle.camera).reshape(1), np.array(bundle.scene).reshape(1), bundle.meshInfoData, bundle.vertexData,
+            bundle.indexData, bundle.uvData, bundle.normalData, bundle.materials, None, 0, tl.blob]
+    rows = 60
+    first, count = (HEIGHT // 2 - rows // 2) * WIDTH, rows * WIDTH
+    ref.raygen("primary", host, n, first, count, cores)   # warm-up
+    best = None
+    for _ in range(3):
+        t0 = time.perf_counter()
+        ref.raygen("primary", host, n, first, count, cores)
+        dt = time.perf_counter() - t0
+        best = dt if best is None or dt < best else best
+    return {"value": count / best / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
+            "sample": "%d of %d image rows (%d rays), best of 3, all host threads; reference SAH build took %.1f s (not timed)"
+                      % (rows, HEIGHT, count, build_s)}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; this framework has no CPU path")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    pkg = entry.load_package()
+    rd, scenes = pkg.rd, pkg.scenes
+    plt = rd.Platform.GetPlatform(local)
+    stream = torch.cuda.ExternalStream(plt.stream(), device=local)
+
+    bundle = scenes.heightfield_scene(GRID_N, WIDTH, HEIGHT)
+    t0 = time.perf_counter()
+    tlas, blas = scenes.build_scene(plt, bundle)
+    build_ms = (time.perf_counter() - t0) * 1e3
+    ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, 1, 1, 0))
+    # the RGBA8 framebuffer lives in a torch tensor so NCCL can gather it in place (zero copy)
+    n = WIDTH * HEIGHT
+    image_t = torch.zeros(n * 4, dtype=torch.uint8, device="cuda")
+    ds.rdImage = rd.WrapBuffer(plt, image_t.data_ptr(), n * 4, owner=image_t)
+    ds.descriptors[2] = ds.rdImage
+    pipe, module = scenes.make_pipeline(plt, "primary")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    first, count, row0, rows = tile_row_range(rank, world)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+
+    def gather():
+        if world == 1:
+            return
+        ops = []
+        if rank == 0:
+            for r in range(1, world):
+                _, _, y0, ny = tile_row_range(r, world)
+                ops.append(dist.P2POp(dist.irecv, image_t[y0 * WIDTH * 4:(y0 + ny) * WIDTH * 4], r))
+        else:
+            ops.append(dist.P2POp(dist.isend, image_t[row0 * WIDTH * 4:(row0 + rows) * WIDTH * 4], 0))
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+
+    def step(timed):
+        with torch.cuda.stream(stream):
+            flush.fill_(rank + 1)                       # evict the scene from L2 between frames
+            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0.record(stream)
+            rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
+            e1.record(stream)
+            gather()
+            e2.record(stream)
+        return e0, e1, e2
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(3, args.warmup)):
+        step(False)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = plt.launch_count()
+    evs = [step(True) for _ in range(args.steps)]
+    barrier()
+    launches = plt.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    frame_ms = sum(e0.elapsed_time(e2) for e0, _, e2 in evs) / args.steps
+    kern_ms = sum(e0.elapsed_time(e1) for e0, e1, _ in evs) / args.steps
+    t = torch.tensor([frame_ms, kern_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    frame_ms, kern_ms = float(t[0]), float(t[1])
+
+    # ---- end to end through the public API with HOST buffers (sample1.cpp render loop :466-490):
+    # WriteBuffer(RTProp) from pinned memory, TraceRays (blocking), ReadBuffer(image) into pinned memory
+    host_rt = torch.zeros(4, dtype=torch.int32).pin_memory()
+    host_img = torch.zeros(count * 4, dtype=torch.uint8).pin_memory()
+    host_rt[1], host_rt[2] = 1, 1
+
+    def e2e_step():
+        rd.WriteBuffer(plt, ds.rdRTProp, 16, host_rt.data_ptr())
+        rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
+        with torch.cuda.stream(stream):
+            gather()
+        if rank == 0:
+            rd.ReadBuffer(plt, ds.rdImage, n * 4 if world > 1 else count * 4, host_full.data_ptr(), 0)
+        else:
+            plt.sync()
+    host_full = torch.zeros(n * 4, dtype=torch.uint8).pin_memory()
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(t[0])
+
+    if rank == 0:
+        # algorithmic bytes per ray: counters-on build of the same traversal over the same primary rays
+        ra, rb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 16)
+        ha, hb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 4)
+        rd.GeneratePrimaryRays(plt, ds.rdCam, 0, 0, WIDTH, HEIGHT, ra, rb)
+        rd.TraceRayList(plt, tlas, ra, rb, ha, hb, n, rd.TRACE_COUNTERS)
+        plt.sync()
+        c = rd.TraceCounters(plt)
+        nodes_per_ray, tris_per_ray = c["nodes"] / c["rays"], c["tris"] / c["rays"]
+        bytes_per_ray = nodes_per_ray * NODE_BYTES + tris_per_ray * TRI_BYTES + RAY_BYTES + HIT_BYTES
+        peak, peak_kind = measured_peaks()
+        rays_per_launch = count
+        achieved = rays_per_launch * bytes_per_ray / (kern_ms * 1e-3) / 1e9
+        out = {
+            "metric": "Mrays/s (primary closest-hit, 1080p)", "value": n / (frame_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+            "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": frame_ms,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "l2": "256 MiB flush between timed frames", "rays_per_step": n,
+                       "partition": "contiguous 8x4-tile rows per GPU, NCCL send/recv gather to rank 0" if world > 1 else "single GPU",
+                       "build_ms_incl_upload": build_ms, "bvh": blas[0].stats(), "raygen": module.info()},
+            "clocks": clocks, "gpu_launches": launches,
+            "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 16,
+                    "d2h_bytes_per_step": n * 4 if world > 1 else count * 4, "ms_per_step": e2e_ms},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",
+                         "kernel_ms": kern_ms, "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray,
+                         "tris_per_ray": tris_per_ray},
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            ref = entry.load_oracle()
+            if ref.available():
+                out["cpu_baseline"] = cpu_baseline_leg(pkg, ref, bundle)
+            else:
+                out["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "reference",
+                                       "sample": "oracle/_ref not built on this box"}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
