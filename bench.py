@@ -70,6 +70,17 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def sample_rows(ref, host, n, cores):
+    """Bounded sample of the frame for the CPU legs: image rows around the middle of the frame, sized
+    from a 60-row probe so that one pass costs about 1.5 s of wall time (at most the whole frame)."""
+    first, count = (HEIGHT // 2 - 30) * WIDTH, 60 * WIDTH
+    t0 = time.perf_counter()
+    ref.raygen("primary", host, n, first, count, cores)
+    dt = max(1e-4, time.perf_counter() - t0)
+    rows = int(60 * 1.5 / dt)
+    return max(60, min(HEIGHT, rows - rows % 4))
+
+
 def reference_arm(args, rank, world):
     """--impl reference: the reference's own CPU code (oracle/_ref: its bvh.cpp + radiance.cl/pbr.cl, the
     same user program compiled as C++) on the host cores, each step a bounded sample of the C2 frame."""
@@ -90,7 +101,7 @@ def reference_arm(args, rank, world):
     rt = scenes.rtprop(0, 1, 1, 0)
     host = [np.array(rt).reshape(1), scratch, image, np.array(b.camera).reshape(1), np.array(b.scene).reshape(1),
             b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData, b.materials, None, 0, tl.blob]
-    rows = 60   # bounded sample: 60 image rows (115 200 primary rays) through the middle of the frame
+    rows = sample_rows(ref, host, n, cores)
     first, count = (HEIGHT // 2 - rows // 2) * WIDTH, rows * WIDTH
     for _ in range(args.warmup):
         ref.raygen("primary", host, n, first, count, cores)
@@ -126,7 +137,7 @@ def cpu_baseline_leg(pkg, ref, bundle):
     host = [np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1), np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8),
             np.array(bundle.camera).reshape(1), np.array(bundle.scene).reshape(1), bundle.meshInfoData, bundle.vertexData,
             bundle.indexData, bundle.uvData, bundle.normalData, bundle.materials, None, 0, tl.blob]
-    rows = 60
+    rows = sample_rows(ref, host, n, cores)
     first, count = (HEIGHT // 2 - rows // 2) * WIDTH, rows * WIDTH
     ref.raygen("primary", host, n, first, count, cores)   # warm-up
     best = None
