@@ -1,0 +1,84 @@
+"""Generates tests/golden/*.npz by running the REFERENCE's own code (oracle/_ref: radiance/src/bvh.cpp
+unchanged + radiance/shader/*.cl compiled as C++). The reference ships no golden vectors or tests
+(SURVEY.md section 4), so these are the pinned known answers. Run in the build container:
+    python tests/golden/make_golden.py
+Inputs are seeded / closed-form; the script is committed with its outputs."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+import __graft_entry__ as entry  # noqa: E402
+
+ref = entry.load_oracle()
+scenes = entry.load_package().scenes
+out = os.path.dirname(os.path.abspath(__file__))
+rng = np.random.default_rng(20261104)
+
+# 1. random_pcg3d (radiance/shader/math.cl:10-23): integer hash, float stage
+v = rng.integers(0, 2**32, size=(256, 3), dtype=np.uint64).astype(np.uint32)
+v[:4] = [[0, 0, 0], [1, 2, 3], [0xffffffff, 0xffffffff, 0xffffffff], [7, 0, 479999]]
+np.savez(os.path.join(out, "pcg3d.npz"), input=v, output=ref.pcg3d(v))
+
+# 2. InverseMat4x4 (math.cl:56-183) on affine instance-like matrices
+mats, invs = [], []
+for k in range(32):
+    m = np.eye(4, dtype=np.float32)
+    a = rng.normal(size=(3, 3)).astype(np.float32)
+    m[:3, :3] = a + 2.0 * np.eye(3, dtype=np.float32)
+    m[:3, 3] = rng.normal(size=3).astype(np.float32) * 3
+    ok, inv = ref.inverse4x4(m)
+    assert ok
+    mats.append(m), invs.append(inv)
+np.savez(os.path.join(out, "inverse4x4.npz"), input=np.array(mats), output=np.array(invs))
+
+# 3. intersectTriangle (radiance.cl:211-251): random rays against random triangles + edge cases
+n = 2048
+o = rng.normal(size=(n, 3)).astype(np.float32) * 2
+tri = rng.normal(size=(n, 9)).astype(np.float32)
+tgt = (tri[:, 0:3] + tri[:, 3:6] + tri[:, 6:9]) / 3 + rng.normal(size=(n, 3)).astype(np.float32) * 0.4
+d = (tgt - o).astype(np.float32)
+# exact edge / vertex / parallel / behind cases
+o[0], d[0], tri[0] = [0.25, 0.25, 1], [0, 0, -1], [0, 0, 0, 1, 0, 0, 0, 1, 0]
+o[1], d[1], tri[1] = [0.5, 0.0, 1], [0, 0, -1], [0, 0, 0, 1, 0, 0, 0, 1, 0]       # on an edge (inclusive)
+o[2], d[2], tri[2] = [0.0, 0.0, 1], [0, 0, -1], [0, 0, 0, 1, 0, 0, 0, 1, 0]       # on a vertex
+o[3], d[3], tri[3] = [0.25, 0.25, 1], [1, 0, 0], [0, 0, 0, 1, 0, 0, 0, 1, 0]      # parallel: det == 0
+o[4], d[4], tri[4] = [0.25, 0.25, 1], [0, 0, 1], [0, 0, 0, 1, 0, 0, 0, 1, 0]      # behind: t < 0
+o[5], d[5], tri[5] = [0.25, 0.25, -1], [0, 0, 1], [0, 0, 0, 1, 0, 0, 0, 1, 0]     # back face: two-sided
+hit = np.zeros(n, np.uint8)
+res = np.zeros((n, 7), np.float32)
+for i in range(n):
+    ok, r = ref.intersect_triangle(o[i], d[i], tri[i])
+    hit[i], res[i] = ok, r
+np.savez(os.path.join(out, "triangle.npz"), origin=o, direction=d, triangle=tri, hit=hit, result=res)
+
+# 4. traceRay hit records (radiance.cl:254-275) on the two small parity scenes
+def record(name, bundle, rays):
+    tl = scenes.build_reference_scene(ref, bundle)
+    closest = tl.trace(rays)
+    first = tl.trace(rays, terminate_on_first_hit=True)
+    np.savez_compressed(os.path.join(out, name), rays=rays, hit=closest["hit"].astype(np.uint8), t=closest["t"],
+                        prim=closest["prim"], inst=closest["inst"], bary=closest["bary"], point=closest["point"],
+                        occluded=first["hit"].astype(np.uint8))
+
+b = scenes.cornell_like()
+b.camera["x"], b.camera["y"] = 0.013, 1.037
+record("cornell_hits.npz", b, scenes.pinhole_rays(b.camera, stride=8, jitter=(0.37, 0.61)))
+b = scenes.heightfield_scene(64, 160, 90)
+record("heightfield64_hits.npz", b, scenes.pinhole_rays(b.camera, jitter=(0.29, 0.71)))
+
+# 5. raygen image of programs/primary.cl through the reference runtime (Cornell, 96x72, 2 spp)
+b = scenes.cornell_like()
+b.camera["x"], b.camera["y"] = 0.013, 1.037
+w, h = 96, 72
+cam = np.array(b.camera).reshape(()).copy()
+cam["widthPixel"], cam["heightPixel"] = w, h
+scratch, image = np.zeros(w * h * 4, np.float32), np.zeros(w * h * 4, np.uint8)
+tl = scenes.build_reference_scene(ref, b)
+ref.raygen("primary", [np.array(scenes.rtprop(0, 2, 1, 0)).reshape(1), scratch, image, cam.reshape(1),
+                       np.array(b.scene).reshape(1), b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData,
+                       b.materials, None, 0, tl.blob], w * h)
+np.savez_compressed(os.path.join(out, "primary_cornell_96x72.npz"), image=image.reshape(h, w, 4), scratch=scratch.reshape(h, w, 4))
+print("golden vectors written to", out)
