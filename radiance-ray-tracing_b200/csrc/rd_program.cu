@@ -5,6 +5,7 @@
 // TraceRays) and tools/genSBT.py (switch generation from sbt.json).
 #include <nvrtc.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <string>
 #include <vector>
@@ -254,6 +255,13 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
     std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "-default-device", "--pre-include=cl_compat.h",
                                      "-lineinfo", "-w", "--ptxas-options=-v"};
     opts.push_back(fmad ? "--fmad=true" : "--fmad=false");
+    // developer knob for ablations: extra NVRTC flags (e.g. "-DRD_POSTPONE=5 -DRD_DEQUANT_I2F=1")
+    std::vector<std::string> extra;
+    if (const char* env = getenv("RD_NVRTC_FLAGS")) {
+        std::string e(env); size_t a = 0;
+        while (a < e.size()) { size_t b = e.find(' ', a); if (b == std::string::npos) b = e.size(); if (b > a) extra.push_back(e.substr(a, b - a)); a = b + 1; }
+    }
+    for (auto& x : extra) opts.push_back(x.c_str());
     r = nvrtcCompileProgram(prog, (int)opts.size(), opts.data());
     size_t logSize = 0;
     nvrtcGetProgramLogSize(prog, &logSize);

@@ -55,6 +55,9 @@ static inline float rd_u2f_(rd_u32 u) { float f; memcpy(&f, &u, 4); return f; }
 #define RD_U2F(u) rd_u2f_(u)
 #endif
 
+#ifndef RD_POSTPONE
+#define RD_POSTPONE 0   // 0 = off, k = postpone when fewer than 1/k of the active lanes have triangles
+#endif
 #ifndef RD_STACK_ENTRIES
 #define RD_STACK_ENTRIES 48
 #endif
@@ -120,17 +123,48 @@ RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, f
     f.octinv4 = (7u - oct) * 0x01010101u;
 }
 
+// byte j of q -> float 1 + byte * 2^-15 without an int->float conversion: the byte is dropped into
+// mantissa bits 8..15 of 1.0f by one PRMT. The 1.0f pattern is kept in a register (opaque to the
+// compiler) so the byte selector can be the instruction's immediate operand.
+#ifndef RD_DEQUANT_I2F
+#define RD_DEQUANT_I2F 0
+#endif
+#ifdef __CUDA_ARCH__
+#define RD_BYTE_AS_UNIT_FLOAT(q, j) __uint_as_float(__byte_perm((q), rdOneBits, 0x7604u | ((j) << 4)))
+#else
+#define RD_BYTE_AS_UNIT_FLOAT(q, j) RD_U2F(0x3f800000u | ((((q) >> (8 * (j))) & 0xffu) << 8))
+#endif
+
 // Tests the 8 quantised child boxes of one node against the ray interval [tmin, tbest].
 // Returns the hit mask: bits 24..31 = inner children keyed by visiting priority (highest first),
 // bits 0..23 = leaf records (one bit per primitive record relative to primBase).
+// Plane distance of quantised coordinate c on one axis: t = (p + c*s - o) / d = c*a + b with
+// a = s/d, b = (p - o)/d. With u = 1 + c*2^-15 this is t = u*A + (b - A), A = a*2^15; the
+// cancellation costs at most |A|*2^-23 (0.4 % of a grid step), which is given back by widening the
+// near/far constants by |A|*2^-21, so the test stays conservative.
 RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const RdU4& n3, const RdU4& n4,
                           const RdRayFrame& f, float tmin, float tbest)
 {
     const float sx = RD_U2F((n0.w & 0xffu) << 23), sy = RD_U2F(((n0.w >> 8) & 0xffu) << 23),
                 sz = RD_U2F(((n0.w >> 16) & 0xffu) << 23);
-    const float ax = sx * f.ix, ay = sy * f.iy, az = sz * f.iz;
-    const float bx = (RD_U2F(n0.x) - f.ox) * f.ix, by = (RD_U2F(n0.y) - f.oy) * f.iy,
-                bz = (RD_U2F(n0.z) - f.oz) * f.iz;
+#if RD_DEQUANT_I2F
+    const float Ax = sx * f.ix, Ay = sy * f.iy, Az = sz * f.iz;
+    const float bx = (RD_U2F(n0.x) - f.ox) * f.ix, by = (RD_U2F(n0.y) - f.oy) * f.iy, bz = (RD_U2F(n0.z) - f.oz) * f.iz;
+    const float nbx = bx, nby = by, nbz = bz, fbx = bx, fby = by, fbz = bz;
+#define RD_Q2F(q, j) ((float)(((q) >> (8 * (j))) & 0xffu))
+#else
+#ifdef __CUDA_ARCH__
+    rd_u32 rdOneBits;
+    asm("mov.b32 %0, 0x3f800000;" : "=r"(rdOneBits));
+#endif
+#define RD_Q2F(q, j) RD_BYTE_AS_UNIT_FLOAT(q, j)
+    const float Ax = sx * f.ix * 32768.0f, Ay = sy * f.iy * 32768.0f, Az = sz * f.iz * 32768.0f;
+    const float bx = (RD_U2F(n0.x) - f.ox) * f.ix - Ax, by = (RD_U2F(n0.y) - f.oy) * f.iy - Ay,
+                bz = (RD_U2F(n0.z) - f.oz) * f.iz - Az;
+    const float px = fabsf(Ax) * 4.76837158e-7f, py = fabsf(Ay) * 4.76837158e-7f, pz = fabsf(Az) * 4.76837158e-7f;
+    const float nbx = bx - px, nby = by - py, nbz = bz - pz;   // near planes lean early
+    const float fbx = bx + px, fby = by + py, fbz = bz + pz;   // far planes lean late
+#endif
     rd_u32 hitmask = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
@@ -151,17 +185,18 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 #endif
         for (int j = 0; j < 4; ++j) {
             const int sh = 8 * j;
-            const float t0x = RD_FMA((float)((nx >> sh) & 0xffu), ax, bx);
-            const float t0y = RD_FMA((float)((ny >> sh) & 0xffu), ay, by);
-            const float t0z = RD_FMA((float)((nz >> sh) & 0xffu), az, bz);
-            const float t1x = RD_FMA((float)((fx >> sh) & 0xffu), ax, bx);
-            const float t1y = RD_FMA((float)((fy >> sh) & 0xffu), ay, by);
-            const float t1z = RD_FMA((float)((fz >> sh) & 0xffu), az, bz);
+            const float t0x = RD_FMA(RD_Q2F(nx, j), Ax, nbx);
+            const float t0y = RD_FMA(RD_Q2F(ny, j), Ay, nby);
+            const float t0z = RD_FMA(RD_Q2F(nz, j), Az, nbz);
+            const float t1x = RD_FMA(RD_Q2F(fx, j), Ax, fbx);
+            const float t1y = RD_FMA(RD_Q2F(fy, j), Ay, fby);
+            const float t1z = RD_FMA(RD_Q2F(fz, j), Az, fbz);
             const float tn = RD_FMAX(RD_FMAX(t0x, t0y), RD_FMAX(t0z, tmin));
             const float tf = RD_FMIN(RD_FMIN(t1x, t1y), RD_FMIN(t1z, tbest));
             if (tn <= tf) hitmask |= ((childBits4 >> sh) & 0xffu) << ((bitIndex4 >> sh) & 0xffu);
         }
     }
+#undef RD_Q2F
     return hitmask;
 }
 
@@ -214,6 +249,18 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
             const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
             ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
             tg.x = n1.y; tg.y = hm & 0x00ffffffu;
+#if RD_POSTPONE && defined(__CUDA_ARCH__)
+            // triangle postponing (Ylitie et al. 2017): when only a few lanes of the warp found
+            // triangles in this step, park the group on the stack and keep walking nodes so the
+            // triangle tests of several steps run together later
+            if (blasSp >= 0) {
+                const unsigned act = __activemask();
+                const unsigned withTris = __ballot_sync(act, tg.y != 0u);
+                if (tg.y && ng.y > 0x00ffffffu && __popc(withTris) * RD_POSTPONE < __popc(act) && sp < RD_STACK_ENTRIES) {
+                    stack[sp++] = tg; tg.y = 0;
+                }
+            }
+#endif
         } else {
             tg = ng; ng.x = 0; ng.y = 0;
         }
