@@ -43,6 +43,65 @@ __global__ void __launch_bounds__(128) rd_k_trace(const RdScene* __restrict__ sc
     }
 }
 
+// Same traversal with dynamic ray fetch (Aila & Laine 2009): finished lanes do not wait for the
+// slowest ray of their batch; whenever at least RD_FETCH_MIN lanes of the warp are idle the warp grabs
+// that many new rays with one atomic and the idle lanes re-arm, so node tests run with (nearly) full
+// warps. Lanes keep their ray's traversal state in RdTraversal between steps.
+#ifndef RD_FETCH_MIN
+#define RD_FETCH_MIN 8
+#endif
+template <int MODE>
+__global__ void __launch_bounds__(128) rd_k_trace_dyn(const RdScene* __restrict__ scene, const float4* __restrict__ rayA,
+                                                       const float4* __restrict__ rayB, float4* __restrict__ hitA,
+                                                       rd_u32* __restrict__ hitB, unsigned long long n,
+                                                       unsigned long long* __restrict__ counters)
+{
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned ltMask = (1u << lane) - 1u;
+    RdTraversal T;
+    RdCountingHit cb; cb.terminate = (MODE & 1) != 0; cb.nodes = 0; cb.tris = 0;
+    bool active = false, exhausted = false;
+    unsigned long long mine = 0;
+    for (;;) {
+        unsigned act = __ballot_sync(0xffffffffu, active);
+        if (!exhausted && __popc(act) <= 32 - RD_FETCH_MIN) {
+            const unsigned idle = ~act;
+            const unsigned cnt = (unsigned)__popc(idle);
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(&counters[4], (unsigned long long)cnt);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (!active) {
+                const unsigned long long i = base + (unsigned)__popc(idle & ltMask);
+                if (i < n) {
+                    const float4 a = __ldg(&rayA[i]), b = __ldg(&rayB[i]);
+                    T.begin(scene, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w);
+                    active = true; mine = i;
+                }
+            }
+            if (base + cnt >= n) exhausted = true;
+            act = __ballot_sync(0xffffffffu, active);
+        }
+        if (act == 0u) break;
+        if (active) {
+            bool more;
+            if (MODE >= 2) more = T.step(scene, cb);
+            else if (MODE == 1) { RdFirstHit f; more = T.step(scene, f); }
+            else { RdNoAnyHit f; more = T.step(scene, f); }
+            if (!more) {
+                hitA[mine] = make_float4(T.hit.t, T.hit.b1, T.hit.b2, __uint_as_float(T.hit.prim));
+                hitB[mine] = T.hit.inst;
+                active = false;
+            }
+        }
+    }
+    if (MODE >= 2) {
+        unsigned long long cn = cb.nodes, ct = cb.tris;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { cn += __shfl_xor_sync(0xffffffffu, cn, o); ct += __shfl_xor_sync(0xffffffffu, ct, o); }
+        if (lane == 0) { atomicAdd(&counters[0], cn); atomicAdd(&counters[1], ct); }
+    }
+}
+
 extern "C" int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA, rd_handle rayB, rd_handle hitA,
                                  rd_handle hitB, size_t n, unsigned flags)
 {
@@ -65,11 +124,23 @@ extern "C" int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA,
     const RdScene* S = (const RdScene*)T->dptr;
     const float4 *a = (const float4*)A->dptr, *b = (const float4*)B->dptr;
     float4* ha = (float4*)HA->dptr; rd_u32* hb = (rd_u32*)HB->dptr;
-    switch (mode) {
-        case 0: rd_k_trace<0><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
-        case 1: rd_k_trace<1><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
-        case 2: rd_k_trace<2><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
-        default: rd_k_trace<3><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+    if (flags & RD_TRACE_STATIC_BATCHES) {
+        switch (mode) {
+            case 0: rd_k_trace<0><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            case 1: rd_k_trace<1><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            case 2: rd_k_trace<2><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            default: rd_k_trace<3><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+        }
+    } else {
+        // persistent: one wave of blocks sized to the machine
+        unsigned pblocks = (unsigned)p->smCount * 6;
+        if (pblocks > blocks) pblocks = blocks;
+        switch (mode) {
+            case 0: rd_k_trace_dyn<0><<<pblocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            case 1: rd_k_trace_dyn<1><<<pblocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            case 2: rd_k_trace_dyn<2><<<pblocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+            default: rd_k_trace_dyn<3><<<pblocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
+        }
     }
     p->launches += 1;
     RD_CUDA(cudaGetLastError());

@@ -56,7 +56,7 @@ static inline float rd_u2f_(rd_u32 u) { float f; memcpy(&f, &u, 4); return f; }
 #endif
 
 #ifndef RD_POSTPONE
-#define RD_POSTPONE 0   // 0 = off, k = postpone when fewer than 1/k of the active lanes have triangles
+#define RD_POSTPONE 5   // 0 = off, k = postpone when fewer than 1/k of the active lanes have triangles
 #endif
 #ifndef RD_STACK_ENTRIES
 #define RD_STACK_ENTRIES 48
@@ -208,37 +208,53 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 #define RD_LOAD_F4(dst, ptr) { dst = *(const RdF4*)(ptr); }
 #endif
 
-// Walks the two-level structure for one ray. `onCandidate(hit)` is invoked after every accepted
-// closer candidate (hit already committed) and returns false to stop (any-hit semantics).
-// Returns true iff something was accepted; `hit` holds the closest accepted candidate so far.
-template <class OnCandidate>
-RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz,
-                       float tmin, float tmax, RdHitRec& hit, OnCandidate& onCandidate)
-{
-    struct Entry { rd_u32 x, y; };
-    Entry stack[RD_STACK_ENTRIES];
-    int sp = 0, blasSp = -1;          // blasSp >= 0 while inside a bottom-level structure
-    const RdNode8* nodes = scene->nodes;
-    const RdTri* tris = 0;
-    const RdInstance* curInst = 0;
-    RdRayFrame f;
-    rd_frame_set(f, ox, oy, oz, dx, dy, dz);
-    // The interval is open at tmax in the reference (t < Tmax); boxes are culled with <= so use
-    // tmax itself as the first "best" bound and keep strictness in the triangle accept test.
-    float tbest = tmax;
-    bool any = false;
-    hit.t = RD_MISS_T; hit.b1 = 0.0f; hit.b2 = 0.0f; hit.prim = RD_INVALID; hit.inst = RD_INVALID;
-    Entry ng, tg;
-    ng.x = 0; ng.y = 0x80000000u; tg.x = 0; tg.y = 0;
-    for (;;) {
+// Traversal state of one ray over the two-level structure. begin() arms it, step() runs one
+// iteration (one node test + the triangle / instance records it exposed, or one pop) and returns
+// false when the ray is finished. Kept as a struct so that a persistent kernel can interleave
+// steps with ray fetching (csrc/rd_trace.cu); rd_traverse() below is the plain loop.
+struct RdStackEntry { rd_u32 x, y; };
+
+struct RdTraversal {
+    RdStackEntry stack[RD_STACK_ENTRIES];
+    int sp, blasSp;                   // blasSp >= 0 while inside a bottom-level structure
+    const RdNode8* nodes;
+    const RdTri* tris;
+    const RdInstance* curInst;
+    RdRayFrame f;                     // ray in the current space (world or instance-local)
+    float wox, woy, woz, wdx, wdy, wdz, tmin, tmax, tbest;
+    RdStackEntry ng, tg;              // node group / record group being worked on
+    RdHitRec hit;
+    bool any;
+
+    RD_HD void push(const RdScene* scene, RdStackEntry e)
+    {
+        if (sp < RD_STACK_ENTRIES) stack[sp++] = e;
+        else if (scene->status) scene->status[0] = 1u;
+    }
+
+    RD_HD void begin(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
+    {
+        sp = 0; blasSp = -1; nodes = scene->nodes; tris = 0; curInst = 0;
+        wox = ox; woy = oy; woz = oz; wdx = dx; wdy = dy; wdz = dz; tmin = tmin_; tmax = tmax_;
+        rd_frame_set(f, ox, oy, oz, dx, dy, dz);
+        // the interval is open at tmax in the reference (t < Tmax); boxes are culled with <= so tmax
+        // itself is the first bound and strictness stays in the triangle accept test
+        tbest = tmax_;
+        any = false;
+        hit.t = RD_MISS_T; hit.b1 = 0.0f; hit.b2 = 0.0f; hit.prim = RD_INVALID; hit.inst = RD_INVALID;
+        ng.x = 0; ng.y = 0x80000000u; tg.x = 0; tg.y = 0;
+    }
+
+    // `onCandidate(hit)` runs after every accepted closer candidate (hit already committed) and
+    // returns false to stop the ray (any-hit semantics).
+    template <class OnCandidate>
+    RD_HD bool step(const RdScene* scene, OnCandidate& onCandidate)
+    {
         if (ng.y > 0x00ffffffu) {
             const rd_u32 bit = 31u - (rd_u32)RD_CLZ(ng.y);
             const rd_u32 imask = ng.y & 0xffu;   // low byte of an inner group = imask
             ng.y &= ~(1u << bit);
-            if (ng.y > 0x00ffffffu) {
-                if (sp < RD_STACK_ENTRIES) stack[sp++] = ng;
-                else if (scene->status) scene->status[0] = 1u;
-            }
+            if (ng.y > 0x00ffffffu) push(scene, ng);
             const rd_u32 slot = (bit - 24u) ^ (f.octinv4 & 0xffu);
             const rd_u32 rel = (rd_u32)RD_POPC(imask & ~(0xffffffffu << slot));
             const RdNode8* n = nodes + (ng.x + rel);
@@ -270,15 +286,15 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
             if (blasSp < 0) {
                 // top level: record k is an instance -> descend into its bottom-level structure
                 const rd_u32 ii = scene->leafInstances[tg.x + k];
-                if (tg.y) { if (sp < RD_STACK_ENTRIES) stack[sp++] = tg; else if (scene->status) scene->status[0] = 1u; }
-                if (ng.y > 0x00ffffffu) { if (sp < RD_STACK_ENTRIES) stack[sp++] = ng; else if (scene->status) scene->status[0] = 1u; }
+                if (tg.y) push(scene, tg);
+                if (ng.y > 0x00ffffffu) push(scene, ng);
                 blasSp = sp;
                 curInst = scene->instances + ii;
                 const float* m = curInst->inv;
-                const float lox = rd_row_dot(m + 0, ox, oy, oz, 1.0f), loy = rd_row_dot(m + 4, ox, oy, oz, 1.0f),
-                            loz = rd_row_dot(m + 8, ox, oy, oz, 1.0f);
-                const float ldx = rd_row_dot(m + 0, dx, dy, dz, 0.0f), ldy = rd_row_dot(m + 4, dx, dy, dz, 0.0f),
-                            ldz = rd_row_dot(m + 8, dx, dy, dz, 0.0f);
+                const float lox = rd_row_dot(m + 0, wox, woy, woz, 1.0f), loy = rd_row_dot(m + 4, wox, woy, woz, 1.0f),
+                            loz = rd_row_dot(m + 8, wox, woy, woz, 1.0f);
+                const float ldx = rd_row_dot(m + 0, wdx, wdy, wdz, 0.0f), ldy = rd_row_dot(m + 4, wdx, wdy, wdz, 0.0f),
+                            ldz = rd_row_dot(m + 8, wdx, wdy, wdz, 0.0f);
                 rd_frame_set(f, lox, loy, loz, ldx, ldy, ldz);
                 nodes = curInst->nodes; tris = curInst->tris;
                 ng.x = 0; ng.y = 0x80000000u; tg.y = 0;
@@ -294,20 +310,33 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
                 t < hit.t && t > tmin && t < tmax) {
                 hit.t = t; hit.b1 = b1; hit.b2 = b2; hit.prim = RD_F2U(a.w); hit.inst = curInst->instanceID;
                 tbest = t; any = true;
-                if (!onCandidate(hit)) return true;
+                if (!onCandidate(hit)) return false;
             }
         }
         if (ng.y <= 0x00ffffffu) {
             if (blasSp >= 0 && sp == blasSp) {
                 // bottom-level structure exhausted: back to world space
                 blasSp = -1; nodes = scene->nodes;
-                rd_frame_set(f, ox, oy, oz, dx, dy, dz);
+                rd_frame_set(f, wox, woy, woz, wdx, wdy, wdz);
             }
-            if (sp == 0) break;
+            if (sp == 0) return false;
             ng = stack[--sp];
         }
+        return true;
     }
-    return any;
+};
+
+// Walks the two-level structure for one ray. Returns true iff something was accepted; `hit` holds
+// the closest accepted candidate.
+template <class OnCandidate>
+RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz,
+                       float tmin, float tmax, RdHitRec& hit, OnCandidate& onCandidate)
+{
+    RdTraversal T;
+    T.begin(scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
+    while (T.step(scene, onCandidate)) {}
+    hit = T.hit;
+    return T.any;
 }
 
 // callback interface: operator() = any-hit; countNode / countTri = optional fetch statistics

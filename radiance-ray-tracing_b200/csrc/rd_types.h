@@ -77,5 +77,7 @@ struct RD_ALIGN(16) RdScene {
 
 // rd_trace flags
 #define RD_TRACE_TERMINATE_ON_FIRST_HIT 1u
+#define RD_TRACE_COUNTERS 2u
+#define RD_TRACE_STATIC_BATCHES 4u
 
 #endif
