@@ -125,7 +125,10 @@ int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA, rd_handle 
 /* totals of the last RD_TRACE_COUNTERS launch: [0] wide nodes fetched, [1] triangle records fetched,
  * [2] rays */
 int rd_trace_counters(rd_platform* p, uint64_t out[3]);
-/* pinhole / thin-lens primary rays of samples/shader.cl:111-173 into rayA/rayB (width*height rays) */
+/* pinhole / thin-lens primary rays of samples/shader.cl:111-173 into rayA/rayB (width*height rays). Ray slot
+ * i belongs to work-item i; with option "tile" on and width % 8 == 0, height % 4 == 0 the slots enumerate
+ * 8x4 pixel tiles row by row (slot -> pixel: tile = i / 32, lane = i % 32, x = 8*(tile % (W/8)) + lane % 8,
+ * y = 4*(tile / (W/8)) + lane / 8), otherwise slot i is pixel i in row-major order */
 int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID, unsigned totalSamples,
                              unsigned width, unsigned height, rd_handle rayA, rd_handle rayB);
 

@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(128) rd_k_trace_dyn(const RdScene* __restrict_
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned ltMask = (1u << lane) - 1u;
+    RdStackEntry stackMemory[RD_STACK_ENTRIES];
     RdTraversal T;
     RdCountingHit cb; cb.terminate = (MODE & 1) != 0; cb.nodes = 0; cb.tris = 0;
     bool active = false, exhausted = false;
@@ -74,7 +75,7 @@ __global__ void __launch_bounds__(128) rd_k_trace_dyn(const RdScene* __restrict_
                 const unsigned long long i = base + (unsigned)__popc(idle & ltMask);
                 if (i < n) {
                     const float4 a = __ldg(&rayA[i]), b = __ldg(&rayB[i]);
-                    T.begin(scene, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w);
+                    T.begin(stackMemory, scene, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w);
                     active = true; mine = i;
                 }
             }
@@ -183,13 +184,22 @@ __device__ __forceinline__ void rd_euler_zyx(const RdCamera& c, float& x, float&
     x = x2; y = cx * y2 - sx * z2; z = sx * y2 + cx * z2;
 }
 
+// Ray slot `slot` holds the ray of pixel `index`: with tileW != 0 the slots enumerate 8x4 pixel tiles
+// row by row (32 consecutive slots = one tile = one warp of the trace kernel), the same mapping
+// get_global_id() applies to raygen launches (shader/compat/cl_compat.h).
 __global__ void rd_k_primary_rays(const RdCamera* __restrict__ cam, unsigned frameID, unsigned totalSamples,
-                                  unsigned count, float4* __restrict__ rayA, float4* __restrict__ rayB)
+                                  unsigned count, unsigned tileW, float4* __restrict__ rayA, float4* __restrict__ rayB)
 {
-    const unsigned index = blockIdx.x * blockDim.x + threadIdx.x;
-    if (index >= count) return;
+    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= count) return;
     const RdCamera c = *cam;
     const int w = (int)c.widthPixel;
+    unsigned index = slot;
+    if (tileW) {
+        const unsigned tilesX = tileW >> 3, tile = slot >> 5, lane = slot & 31u;
+        const unsigned ty = tile / tilesX, tx = tile - ty * tilesX;
+        index = ((ty << 2) + (lane >> 3)) * tileW + (tx << 3) + (lane & 7u);
+    }
     const int px = (int)index % w, py = (int)index / w;
     float rnd[3];
     rd_pcg3d(frameID, totalSamples, index, rnd);
@@ -224,8 +234,8 @@ __global__ void rd_k_primary_rays(const RdCamera* __restrict__ cam, unsigned fra
         len = sqrtf(dx * dx + dy * dy + dz * dz);
         dx /= len; dy /= len; dz /= len;
     }
-    rayA[index] = make_float4(ox, oy, oz, 0.001f);
-    rayB[index] = make_float4(dx, dy, dz, 1000.0f);
+    rayA[slot] = make_float4(ox, oy, oz, 0.001f);
+    rayB[slot] = make_float4(dx, dy, dz, 1000.0f);
 }
 
 extern "C" int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID, unsigned totalSamples,
@@ -239,8 +249,9 @@ extern "C" int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsign
     }
     if (!n) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
+    const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     rd_k_primary_rays<<<(unsigned)((n + 255) / 256), 256, 0, p->stream>>>((const RdCamera*)C->dptr, frameID, totalSamples,
-                                                                            (unsigned)n, (float4*)A->dptr, (float4*)B->dptr);
+                                                                            (unsigned)n, tileW, (float4*)A->dptr, (float4*)B->dptr);
     p->launches += 1;
     RD_CUDA(cudaGetLastError());
     return RD_OK;

@@ -215,7 +215,8 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 struct RdStackEntry { rd_u32 x, y; };
 
 struct RdTraversal {
-    RdStackEntry stack[RD_STACK_ENTRIES];
+    RdStackEntry* stack;              // RD_STACK_ENTRIES entries owned by the caller (thread-local memory);
+                                      // kept outside so the scalar state below stays in registers
     int sp, blasSp;                   // blasSp >= 0 while inside a bottom-level structure
     const RdNode8* nodes;
     const RdTri* tris;
@@ -232,9 +233,9 @@ struct RdTraversal {
         else if (scene->status) scene->status[0] = 1u;
     }
 
-    RD_HD void begin(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
+    RD_HD void begin(RdStackEntry* stackMemory, const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
     {
-        sp = 0; blasSp = -1; nodes = scene->nodes; tris = 0; curInst = 0;
+        stack = stackMemory; sp = 0; blasSp = -1; nodes = scene->nodes; tris = 0; curInst = 0;
         wox = ox; woy = oy; woz = oz; wdx = dx; wdy = dy; wdz = dz; tmin = tmin_; tmax = tmax_;
         rd_frame_set(f, ox, oy, oz, dx, dy, dz);
         // the interval is open at tmax in the reference (t < Tmax); boxes are culled with <= so tmax
@@ -307,7 +308,9 @@ struct RdTraversal {
             float t, b1, b2;
             if (rd_intersect_triangle(f.ox, f.oy, f.oz, f.dx, f.dy, f.dz, a.x, a.y, a.z, b.x, b.y, b.z,
                                       c.x, c.y, c.z, &t, &b1, &b2) &&
-                t < hit.t && t > tmin && t < tmax) {
+                t > tmin && t < tmax &&
+                (t < hit.t || (t == hit.t && (curInst->instanceID < hit.inst ||
+                                              (curInst->instanceID == hit.inst && RD_F2U(a.w) < hit.prim))))) {
                 hit.t = t; hit.b1 = b1; hit.b2 = b2; hit.prim = RD_F2U(a.w); hit.inst = curInst->instanceID;
                 tbest = t; any = true;
                 if (!onCandidate(hit)) return false;
@@ -332,8 +335,9 @@ template <class OnCandidate>
 RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz,
                        float tmin, float tmax, RdHitRec& hit, OnCandidate& onCandidate)
 {
+    RdStackEntry stackMemory[RD_STACK_ENTRIES];
     RdTraversal T;
-    T.begin(scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
+    T.begin(stackMemory, scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
     while (T.step(scene, onCandidate)) {}
     hit = T.hit;
     return T.any;
