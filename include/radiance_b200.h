@@ -133,8 +133,12 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
                              unsigned width, unsigned height, rd_handle rayA, rd_handle rayB);
 
 /* runtime options: "fmad" (0/1, NVRTC contraction for user code), "tile" (0/1 8x4 pixel tiles per warp),
- * "block" (threads per block of raygen launches) */
+ * "block" (threads per block of raygen launches), "count_rays" (0/1: modules created afterwards count
+ * every traceRay invocation, the numerator of the Mrays/s metric; read with rd_ray_count) */
 int rd_set_option(rd_platform* p, const char* key, long value);
+/* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
+ * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */
+int rd_ray_count(rd_platform* p, uint64_t* out, int reset);
 /* number of kernels this library launched since platform creation */
 uint64_t rd_launch_count(rd_platform* p);
 

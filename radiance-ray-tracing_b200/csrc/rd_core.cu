@@ -34,7 +34,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     rd_platform* p = new rd_platform();
     p->device = device;
     p->boundModule = 0;
-    p->optFmad = 1; p->optTile = 1; p->optBlock = 128;
+    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0;
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     RD_CUDA(cudaMalloc(&p->dstatus, 64));
@@ -219,6 +219,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     if (!p || !key) { rd_set_error("rd_set_option: null argument"); return RD_E_ARG; }
     if (!strcmp(key, "fmad")) p->optFmad = value;
     else if (!strcmp(key, "tile")) p->optTile = value;
+    else if (!strcmp(key, "count_rays")) p->optCountRays = value;
     else if (!strcmp(key, "block")) { if (value < 32 || value > 1024 || (value & 31)) { rd_set_error("block must be a multiple of 32 in [32,1024]"); return RD_E_ARG; } p->optBlock = value; }
     else { rd_set_error("rd_set_option: unknown key '%s'", key); return RD_E_ARG; }
     return RD_OK;

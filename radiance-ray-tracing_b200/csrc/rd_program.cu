@@ -232,7 +232,7 @@ extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 // ---- NVRTC ------------------------------------------------------------------------------------
 // OpenCL-C user program (+ optional sbt.json) -> sm_100a cubin. Needs no device.
 static int rd_compile_program(const char* code, unsigned size, const std::string& sbtJson, bool fmad,
-                              std::vector<char>* cubin, std::string* log)
+                              std::vector<char>* cubin, std::string* log, bool countRays = false)
 {
     std::string src(code, size ? size : strlen(code));
     while (!src.empty() && src.back() == '\0') src.pop_back();
@@ -255,6 +255,7 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
     std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "-default-device", "--pre-include=cl_compat.h",
                                      "-lineinfo", "-w", "--ptxas-options=-v"};
     opts.push_back(fmad ? "--fmad=true" : "--fmad=false");
+    if (countRays) opts.push_back("-DRD_COUNT_RAYS=1");
     // developer knob for ablations: extra NVRTC flags (e.g. "-DRD_POSTPONE=5 -DRD_DEQUANT_I2F=1")
     std::vector<std::string> extra;
     if (const char* env = getenv("RD_NVRTC_FLAGS")) {
@@ -301,7 +302,7 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     RD_CUDA(cudaSetDevice(p->device));
     { int drc = rd_driver_init(); if (drc) return drc; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log);
+    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0);
     if (rc) return rc;
     rd_module* m = new rd_module();
     m->ptxInfo = log;
@@ -385,6 +386,18 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
         RD_CU(cuLaunchKernel(m->raygen, 1, 1, 1, tail, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
+    return RD_OK;
+}
+
+extern "C" int rd_ray_count(rd_platform* p, uint64_t* out, int reset)
+{
+    if (!p || !out) { rd_set_error("rd_ray_count: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    unsigned long long v = 0;
+    RD_CUDA(cudaMemcpy(&v, p->dstatus + 2, 8, cudaMemcpyDeviceToHost));
+    if (reset) RD_CUDA(cudaMemset(p->dstatus + 2, 0, 8));
+    *out = v;
     return RD_OK;
 }
 

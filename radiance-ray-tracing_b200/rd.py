@@ -25,7 +25,7 @@ ABI_SYMBOLS = [
     "rd_blas_build", "rd_blas_build_device", "rd_blas_free", "rd_blas_stats", "rd_tlas_build",
     "rd_shader_module_create", "rd_module_free", "rd_shader_compile_check", "rd_module_info", "rd_sbt_load_json",
     "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
-    "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count",
+    "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
 ]
 
 
@@ -71,6 +71,7 @@ def lib():
             "rd_trace_rays": [vp, u, u, u, u, u], "rd_trace_rays_async": [vp, u, u], "rd_trace_rays_range": [vp, u, u, C.c_ulonglong, C.c_ulonglong],
             "rd_trace_ray_list": [vp, vp, vp, vp, vp, vp, sz, u], "rd_trace_counters": [vp, C.POINTER(C.c_uint64)],
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
+            "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
         }
         for name, args in sigs.items():
             f = getattr(L, name)
@@ -114,6 +115,12 @@ class Platform:
 
     def set_option(self, key, value):
         _check(lib().rd_set_option(self.handle, key.encode(), int(value)))
+
+    def ray_count(self, reset=True):
+        """traceRay invocations counted by modules compiled under option count_rays."""
+        v = C.c_uint64(0)
+        _check(lib().rd_ray_count(self.handle, C.byref(v), int(bool(reset))))
+        return int(v.value)
 
 
 class Mesh:

@@ -74,6 +74,10 @@ RD_DEV void traceRay(
     image2d_array_t imageArray, sampler_t sampler)
 {
     const RdScene* scene = (const RdScene*)topLevel;
+#ifdef RD_COUNT_RAYS
+    // metric pass only (option "count_rays"): every traceRay invocation is one ray of the Mrays/s figure
+    atomicAdd((unsigned long long*)(scene->status + 2), 1ull);
+#endif
     RdUserAnyHit cb;
     cb.scene = scene; cb.o = origin; cb.d = direction; cb.sbtRecordOffset = sbtRecordOffset;
     cb.payload = payload; cb.sceneData = sceneData; cb.imageArray = imageArray; cb.sampler = sampler; cb.cont = true;

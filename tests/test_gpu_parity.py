@@ -129,3 +129,44 @@ def test_primary_program_image_matches_reference(pkg, plt, ref):
     assert rmse <= IMAGE_RMSE_U8, "RMSE %g" % rmse
     assert (np.abs(d).max(axis=-1) > 8).mean() <= 1e-3   # isolated edge pixels only
     assert (img[..., 3] == 255).all()
+
+
+PATH_RMSE_U8 = 2.0   # 8-bit levels; libm vs libdevice transcendentals perturb sampled directions by ULPs
+
+
+def test_path_program_image_matches_reference(pkg, plt, ref):
+    """programs/path.cl (bounce loop, nested shadow traceRay with any-hit termination, pbr.cl sampling):
+    same program text through NVRTC on the GPU and against the reference runtime on the host."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 200, 152
+    rt = scenes.rtprop(0, 4, 4, 0)
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, rt)
+    plt.set_option("count_rays", 1)
+    try:
+        pipe, _ = scenes.make_pipeline(plt, "path")
+    finally:
+        plt.set_option("count_rays", 0)
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    plt.ray_count()
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    rays = plt.ray_count()
+    img, scratch = ds.read_image(), ds.read_scratch()
+    exp, exp_scratch = reference_image(ref, scenes, b, "path", w, h, rt)
+    # every sample traces a primary ray, every surface hit a shadow ray and (below the depth limit) a bounce ray
+    assert w * h * 4 < rays <= w * h * 4 * 8
+    d = img[..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+    rmse = np.sqrt((d * d).mean())
+    assert rmse <= PATH_RMSE_U8, "RMSE %g" % rmse
+    assert abs(img[..., :3].mean() - exp[..., :3].mean()) <= 0.25
+    assert (np.abs(d).max(axis=-1) > 16).mean() <= 5e-3
+    # the accumulated radiance agrees before tone mapping as well
+    rel = np.abs(scratch[..., :3] - exp_scratch[..., :3]).mean() / np.abs(exp_scratch[..., :3]).mean()
+    assert rel <= 0.01, "scratch relative L1 %g" % rel
+    # progressive accumulation: a second call continues the running mean (samples/shader.cl:262-279)
+    ds.set_rtprop(4, 4, 4)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    s2 = ds.read_scratch()
+    assert np.isfinite(s2).all() and not np.array_equal(s2, scratch)
