@@ -134,7 +134,10 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
 
 /* runtime options: "fmad" (0/1, NVRTC contraction for user code), "tile" (0/1 8x4 pixel tiles per warp),
  * "block" (threads per block of raygen launches), "count_rays" (0/1: modules created afterwards count
- * every traceRay invocation, the numerator of the Mrays/s metric; read with rd_ray_count) */
+ * every traceRay invocation, the numerator of the Mrays/s metric; read with rd_ray_count),
+ * "max_trace_depth" (1..8, default 2: how deep traceRay may nest -- raygen -> hit shader -> shadow ray is 2;
+ * the user program is compiled once per level so every level inlines, PipelineCreateInfo::maxRayRecursionDepth
+ * of radiance/include/radiance.h:74 is the reference's unused counterpart) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */

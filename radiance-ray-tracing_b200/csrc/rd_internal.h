@@ -45,12 +45,12 @@ struct rd_module {
 struct rd_platform {
     int device;
     cudaStream_t stream;
-    uint32_t* dstatus;        // [0] stack overflow flag, [2..3] 64-bit traceRay counter (option count_rays)
+    uint32_t* dstatus;        // [0] stack overflow flag, [1] traceRay nesting exceeded, [2..3] 64-bit traceRay counter (option count_rays)
     unsigned long long* dcounters;   // trace counters [nodes, tris, rays] + work counter at [4]
     std::vector<uint64_t> boundArgs;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth;
     uint64_t launches;
     int smCount;
 };

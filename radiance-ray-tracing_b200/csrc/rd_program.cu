@@ -232,7 +232,7 @@ extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 // ---- NVRTC ------------------------------------------------------------------------------------
 // OpenCL-C user program (+ optional sbt.json) -> sm_100a cubin. Needs no device.
 static int rd_compile_program(const char* code, unsigned size, const std::string& sbtJson, bool fmad,
-                              std::vector<char>* cubin, std::string* log, bool countRays = false)
+                              std::vector<char>* cubin, std::string* log, bool countRays = false, int maxDepth = 2)
 {
     std::string src(code, size ? size : strlen(code));
     while (!src.empty() && src.back() == '\0') src.pop_back();
@@ -249,8 +249,36 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
         }
         src += generate_dispatchers(rows, needHit, needMiss, needAny);
     }
+    // One copy of the user program per traceRay nesting level, each in its own namespace, so that the
+    // traceRay -> callHit -> <hit shader> -> traceRay chain has no cycle and inlines completely (see
+    // shader/radiance.cl "per-level part"). Level 0 owns the raygen kernel; the last level's traceRay
+    // is a stub that raises the depth-exceeded flag.
+    const bool hasAny = !needAny || bare.find("callAnyHit") != std::string::npos || src.find("callAnyHit(bool* cont") != std::string::npos;
+    std::string mainSrc = "#include \"radiance.cl\"\n#include \"pbr.cl\"\n";
+    if (hasAny) mainSrc += "#define RD_HAS_ANYHIT 1\n";
+    char line[1024];
+    for (int k = 1; k <= maxDepth; ++k) {
+        snprintf(line, sizeof(line),
+                 "namespace rd_l%d { struct Payload; struct SceneData;\n"
+                 "RD_DEV void callHit(int, struct Payload*, struct HitData*, struct SceneData*, image2d_array_t, sampler_t);\n"
+                 "RD_DEV void callMiss(int, struct Payload*, struct SceneData*, image2d_array_t, sampler_t);\n"
+                 "RD_DEV void callAnyHit(bool*, int, struct Payload*, struct HitData*, struct SceneData*, image2d_array_t, sampler_t); }\n", k);
+        mainSrc += line;
+    }
+    for (int k = 0; k <= maxDepth; ++k) {
+        snprintf(line, sizeof(line), "#undef RD_LEVEL\n#define RD_LEVEL %d\n#undef RD_LEVEL_PART_DONE\n#undef RD_NEXT_NS\n#define RD_NEXT_NS rd_l%d\n", k, k + 1);
+        mainSrc += line;
+        if (k == maxDepth) mainSrc += "#define RD_LAST_LEVEL 1\n";
+        if (k == 1) mainSrc += "#undef __kernel\n#define __kernel static __device__\n";
+        snprintf(line, sizeof(line), "namespace rd_l%d {\n#include \"rd_user_program.cl\"\n}\n", k);
+        mainSrc += line;
+    }
+    std::vector<const char*> hdrNames(rd_embedded_names, rd_embedded_names + rd_embedded_count);
+    std::vector<const char*> hdrSources(rd_embedded_sources, rd_embedded_sources + rd_embedded_count);
+    hdrNames.push_back("rd_user_program.cl");
+    hdrSources.push_back(src.c_str());
     nvrtcProgram prog;
-    nvrtcResult r = nvrtcCreateProgram(&prog, src.c_str(), "user_program.cl", rd_embedded_count, rd_embedded_sources, rd_embedded_names);
+    nvrtcResult r = nvrtcCreateProgram(&prog, mainSrc.c_str(), "rd_program_levels.cu", (int)hdrNames.size(), hdrSources.data(), hdrNames.data());
     if (r != NVRTC_SUCCESS) { rd_set_error("nvrtcCreateProgram: %s", nvrtcGetErrorString(r)); return RD_E_COMPILE; }
     std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "-default-device", "--pre-include=cl_compat.h",
                                      "-lineinfo", "-w", "--ptxas-options=-v"};
@@ -279,6 +307,10 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
     r = nvrtcGetCUBIN(prog, cubin->data());
     nvrtcDestroyProgram(&prog);
     if (r != NVRTC_SUCCESS || !cubinSize) { rd_set_error("nvrtcGetCUBIN: %s", nvrtcGetErrorString(r)); return RD_E_COMPILE; }
+    // developer knob: keep the cubin for cuobjdump -sass / nvdisasm
+    if (const char* dump = getenv("RD_DUMP_CUBIN")) {
+        if (FILE* f = fopen(dump, "wb")) { fwrite(cubin->data(), 1, cubin->size(), f); fclose(f); }
+    }
     return RD_OK;
 }
 
@@ -302,7 +334,7 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     RD_CUDA(cudaSetDevice(p->device));
     { int drc = rd_driver_init(); if (drc) return drc; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0);
+    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth);
     if (rc) return rc;
     rd_module* m = new rd_module();
     m->ptxInfo = log;
@@ -413,12 +445,13 @@ extern "C" int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned
     int rc = rd_trace_rays_async(p, width, height);
     if (rc) return rc;
     RD_CUDA(cudaStreamSynchronize(p->stream));   // blocking like clFinish (radiance.cpp:261)
-    uint32_t status = 0;
-    RD_CUDA(cudaMemcpy(&status, p->dstatus, 4, cudaMemcpyDeviceToHost));
-    if (status) {
-        cudaMemset(p->dstatus, 0, 4);
-        rd_set_error("rd_trace_rays: traversal stack overflow on the device (results incomplete)");
-        return RD_E_OVERFLOW;
+    uint32_t status[2] = {0, 0};
+    RD_CUDA(cudaMemcpy(status, p->dstatus, 8, cudaMemcpyDeviceToHost));
+    if (status[0] || status[1]) {
+        cudaMemset(p->dstatus, 0, 8);
+        if (status[0]) { rd_set_error("rd_trace_rays: traversal stack overflow on the device (results incomplete)"); return RD_E_OVERFLOW; }
+        rd_set_error("rd_trace_rays: traceRay nested deeper than option max_trace_depth (%ld)", p->optMaxDepth);
+        return RD_E_STATE;
     }
     return RD_OK;
 }

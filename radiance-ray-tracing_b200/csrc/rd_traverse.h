@@ -58,6 +58,9 @@ static inline float rd_u2f_(rd_u32 u) { float f; memcpy(&f, &u, 4); return f; }
 #ifndef RD_POSTPONE
 #define RD_POSTPONE 5   // 0 = off, k = postpone when fewer than 1/k of the active lanes have triangles
 #endif
+#ifndef RD_RECONVERGE
+#define RD_RECONVERGE 1
+#endif
 #ifndef RD_STACK_ENTRIES
 #define RD_STACK_ENTRIES 48
 #endif
@@ -127,7 +130,7 @@ RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, f
 // mantissa bits 8..15 of 1.0f by one PRMT. The 1.0f pattern is kept in a register (opaque to the
 // compiler) so the byte selector can be the instruction's immediate operand.
 #ifndef RD_DEQUANT_I2F
-#define RD_DEQUANT_I2F 0
+#define RD_DEQUANT_I2F 1
 #endif
 #ifdef __CUDA_ARCH__
 #define RD_BYTE_AS_UNIT_FLOAT(q, j) __uint_as_float(__byte_perm((q), rdOneBits, 0x7604u | ((j) << 4)))
@@ -337,8 +340,18 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
 {
     RdStackEntry stackMemory[RD_STACK_ENTRIES];
     RdTraversal T;
+#if defined(__CUDA_ARCH__) && RD_RECONVERGE
+    // The walk leaves its loop from several places and ptxas puts no reconvergence point behind it:
+    // lanes that finish early would run everything that follows (shading, the caller's bounce loop,
+    // the next traceRay) on their own -- measured 2.2 of 32 lanes active in programs/path.cl. The lanes
+    // that enter together therefore wait for each other here before returning.
+    const unsigned together = __activemask();
+#endif
     T.begin(stackMemory, scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
     while (T.step(scene, onCandidate)) {}
+#if defined(__CUDA_ARCH__) && RD_RECONVERGE
+    __syncwarp(together);
+#endif
     hit = T.hit;
     return T.any;
 }

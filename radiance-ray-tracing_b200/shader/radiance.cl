@@ -9,9 +9,6 @@
 #include "data.cl"
 #include "math.cl"
 
-struct Payload;
-struct SceneData;
-
 struct HitData {
     float3 hitPoint;                    // object space (instance-local), as in the reference
     float distance;                     // ray parameter t (shared by world and object space)
@@ -22,14 +19,6 @@ struct HitData {
     float3 barycentric;                 // (1-b1-b2, b1, b2) for vertices (idx0, idx1, idx2)
     mat4x4 transform;                   // object -> world
 };
-
-// supplied by the user program (hand-written or generated from sbt.json)
-RD_DEV void callHit(int sbtRecordOffset, struct Payload* payload, struct HitData* hitData,
-                    struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
-RD_DEV void callMiss(int missIndex, struct Payload* payload,
-                     struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
-RD_DEV void callAnyHit(bool* cont, int sbtRecordOffset, struct Payload* payload, struct HitData* hitData,
-                       struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
 
 // HitData of a committed candidate: the instance-local ray is re-derived with the same rounded
 // operations the traversal used, so hitPoint = o_local + d_local * t matches it bit for bit.
@@ -50,22 +39,64 @@ RD_F void rd_fill_hit_data(const RdScene* scene, float3 o, float3 d, const RdHit
     for (int i = 0; i < 16; ++i) out->transform.s[i] = I->fwd[i];
 }
 
+#endif  // shared part
+
+// ---- per-level part ------------------------------------------------------------------------------
+// The reference's traceRay is reentrant: hit shaders call it again for shadow rays
+// (samples/shader.cl:499-501), which makes traceRay -> callHit -> material -> traceRay a cycle in the
+// call graph. A cycle forces real calls, and lanes that reach a real call at different times never
+// reconverge (measured: 2.2 of 32 lanes active, profiles/README_r1.md). csrc/rd_program.cu therefore
+// compiles the user program once per recursion level, each copy in its own namespace rd_l<k>: the
+// raygen kernel is taken from level 0, traceRay of level k dispatches into the user functions of
+// level k+1 (RD_NEXT_NS), and the last level's traceRay only raises the depth-exceeded flag. Every
+// copy inlines completely. Payload / SceneData are per-level types with identical layout.
+#if defined(RD_LEVEL) && !defined(RD_LEVEL_PART_DONE)
+#define RD_LEVEL_PART_DONE
+
+struct Payload;
+struct SceneData;
+
+// supplied by the user program (hand-written or generated from sbt.json)
+RD_DEV void callHit(int sbtRecordOffset, struct Payload* payload, struct HitData* hitData,
+                    struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
+RD_DEV void callMiss(int missIndex, struct Payload* payload,
+                     struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
+RD_DEV void callAnyHit(bool* cont, int sbtRecordOffset, struct Payload* payload, struct HitData* hitData,
+                       struct SceneData* sceneData, image2d_array_t imageArray, sampler_t sampler);
+
+#ifdef RD_LAST_LEVEL
+RD_F void traceRay(
+    __global struct AccelStruct* topLevel,
+    int sbtRecordOffset, int missIndex,
+    float3 origin, float3 direction,
+    float Tmin, float Tmax,
+    struct Payload* payload, struct SceneData* sceneData,
+    image2d_array_t imageArray, sampler_t sampler)
+{
+    // deeper than option "max_trace_depth": nothing is traced, rd_trace_rays reports RD_E_STATE
+    const RdScene* scene = (const RdScene*)topLevel;
+    if (scene->status) scene->status[1] = 1u;
+}
+#else
 struct RdUserAnyHit {
     const RdScene* scene; float3 o, d; int sbtRecordOffset;
     struct Payload* payload; struct SceneData* sceneData; image2d_array_t imageArray; sampler_t sampler;
     bool cont;
     RD_F bool operator()(const RdHitRec& h)
     {
+#ifdef RD_HAS_ANYHIT
         struct HitData hd;
         rd_fill_hit_data(scene, o, d, h, &hd);
-        callAnyHit(&cont, sbtRecordOffset, payload, &hd, sceneData, imageArray, sampler);
+        RD_NEXT_NS::callAnyHit(&cont, sbtRecordOffset, (RD_NEXT_NS::Payload*)payload, &hd,
+                               (RD_NEXT_NS::SceneData*)sceneData, imageArray, sampler);
+#endif
         return cont;
     }
     RD_F void countNode() const {}
     RD_F void countTri() const {}
 };
 
-RD_DEV void traceRay(
+RD_F void traceRay(
     __global struct AccelStruct* topLevel,
     int sbtRecordOffset, int missIndex,
     float3 origin, float3 direction,
@@ -85,10 +116,12 @@ RD_DEV void traceRay(
     if (rd_traverse(scene, origin.x, origin.y, origin.z, direction.x, direction.y, direction.z, Tmin, Tmax, h, cb)) {
         struct HitData hd;
         rd_fill_hit_data(scene, origin, direction, h, &hd);
-        callHit(sbtRecordOffset, payload, &hd, sceneData, imageArray, sampler);
+        RD_NEXT_NS::callHit(sbtRecordOffset, (RD_NEXT_NS::Payload*)payload, &hd, (RD_NEXT_NS::SceneData*)sceneData,
+                            imageArray, sampler);
     } else {
-        callMiss(missIndex, payload, sceneData, imageArray, sampler);
+        RD_NEXT_NS::callMiss(missIndex, (RD_NEXT_NS::Payload*)payload, (RD_NEXT_NS::SceneData*)sceneData,
+                             imageArray, sampler);
     }
 }
-
-#endif
+#endif  // RD_LAST_LEVEL
+#endif  // per-level part

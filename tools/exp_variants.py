@@ -20,7 +20,7 @@ stream = torch.cuda.ExternalStream(plt.stream(), device=0)
 bundle = scenes.heightfield_scene(n_grid, W, H)
 tlas, blas = scenes.build_scene(plt, bundle)
 print("bvh", blas[0].stats(), flush=True)
-ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, 1, 1, 0))
+ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, int(os.environ.get('RD_EXP_SPP', '1')), int(os.environ.get('RD_EXP_DEPTH', '1')), 0))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 VARIANTS = json.loads(os.environ.get("RD_EXP_VARIANTS", "null")) or [
     {"flags": ""}, {"flags": "-DRD_DEQUANT_I2F=1"}, {"flags": "-DRD_POSTPONE=5"}, {"flags": "-DRD_POSTPONE=3"},
