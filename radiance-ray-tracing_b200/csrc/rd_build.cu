@@ -5,6 +5,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <float.h>
 #include <string.h>
+#include <stdlib.h>
 #include "rd_internal.h"
 #include "rd_build.h"
 
@@ -153,6 +154,10 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     RD_CUDA(tmp.alloc(&T.first, ni)); RD_CUDA(tmp.alloc(&T.last, ni));
     RD_CUDA(tmp.alloc(&T.parent, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.arrive, ni));
     RD_CUDA(tmp.alloc(&T.lo, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.hi, 2 * (size_t)n));
+    T.cost = 0; T.dec = 0;
+    if (!getenv("RD_BUILD_GREEDY")) {   // developer knob: greedy collapse instead of the SAH dynamic program
+        RD_CUDA(tmp.alloc(&T.cost, 8 * (size_t)ni)); RD_CUDA(tmp.alloc(&T.dec, 8 * (size_t)ni));
+    }
     RD_CUDA(cudaMemsetAsync(T.arrive, 0, ni * sizeof(rd_u32), st));
     rd_k_leaf_boxes<<<rd_grid(n), RD_BT, 0, st>>>(T, dlo, dhi);
     p->launches += 1;

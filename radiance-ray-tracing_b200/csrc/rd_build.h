@@ -43,7 +43,13 @@ struct RdBinTree {
     rd_u32* arrive;         // [n-1] refit arrival counters (zeroed)
     RdF4* lo;               // [2n-1] boxes: inner i -> slot i, leaf pos -> slot n-1+pos
     RdF4* hi;
+    float* cost;            // [8(n-1)] cost[8i + k-1] = SAH cost of subtree i laid out in at most k slots of its parent
+    rd_u8* dec;             // [8(n-1)] decisions that reach those costs (see rd_dp_node)
 };
+
+// SAH constants of the wide-node cost model: one 8-wide node test vs one triangle test
+#define RD_SAH_NODE 1.0f
+#define RD_SAH_PRIM 0.35f
 
 RD_HD rd_u64 rd_expand21(rd_u32 v)
 {
@@ -112,6 +118,62 @@ RD_HD rd_u32 rd_bin_slot(const RdBinTree& T, rd_u32 ref)
     return (ref & RD_BIN_LEAF) ? (T.n - 1u) + (ref & ~RD_BIN_LEAF) : ref;
 }
 
+RD_HD float rd_half_area(const RdF4& l, const RdF4& h)
+{
+    const float ex = h.x - l.x, ey = h.y - l.y, ez = h.z - l.z;
+    return ex * ey + ey * ez + ez * ex;
+}
+
+// Optimal 8-wide layout of the binary topology by dynamic programming (Ylitie, Karras & Laine 2017,
+// section 4.2). cost(n, k) = cheapest way to present subtree n to its parent in at most k child slots:
+//   cost(n, 1) = min( leaf slot: A(n) * prims * c_prim   (prims <= RD_LEAF_MAX),
+//                     own wide node: A(n) * c_node + dist(n, 8) )
+//   cost(n, k) = min( dist(n, k), cost(n, k - 1) ),   dist(n, j) = min_i cost(left, i) + cost(right, j - i)
+// dec[0] = 0: leaf slot, else the split i of dist(n, 8) used when n becomes a wide node;
+// dec[k-1] (k >= 2) = split i of dist(n, k), or 0 for "no better than k - 1 slots".
+RD_HD void rd_dp_node(const RdBinTree& T, rd_u32 cur, const RdF4& l, const RdF4& h)
+{
+    const float inf = 3.0e38f;
+    float c[2][8];
+    const rd_u32 kid[2] = {T.left[cur], T.right[cur]};
+    for (int s = 0; s < 2; ++s) {
+        if (kid[s] & RD_BIN_LEAF) {
+            const rd_u32 b = rd_bin_slot(T, kid[s]);
+            const float a = rd_half_area(T.lo[b], T.hi[b]) * RD_SAH_PRIM;
+            for (int k = 0; k < 8; ++k) c[s][k] = a;
+        } else {
+#ifdef __CUDA_ARCH__
+            const volatile float* src = (const volatile float*)(T.cost + 8u * (size_t)kid[s]);
+#else
+            const float* src = T.cost + 8u * (size_t)kid[s];
+#endif
+            for (int k = 0; k < 8; ++k) c[s][k] = src[k];
+        }
+    }
+    float dist[9]; rd_u8 split[9];
+    for (int j = 2; j <= 8; ++j) {
+        float best = inf; rd_u8 bi = 1;
+        for (int i = 1; i < j; ++i) {
+            const float v = c[0][i - 1] + c[1][j - i - 1];
+            if (v < best) { best = v; bi = (rd_u8)i; }
+        }
+        dist[j] = best; split[j] = bi;
+    }
+    const float A = rd_half_area(l, h);
+    const rd_u32 prims = T.last[cur] - T.first[cur] + 1u;
+    const float cLeaf = prims <= RD_LEAF_MAX ? A * (float)prims * RD_SAH_PRIM : inf;
+    const float cNode = A * RD_SAH_NODE + dist[8];
+    float* outc = T.cost + 8u * (size_t)cur;
+    rd_u8* outd = T.dec + 8u * (size_t)cur;
+    float prev = cLeaf <= cNode ? cLeaf : cNode;
+    outc[0] = prev; outd[0] = cLeaf <= cNode ? (rd_u8)0 : split[8];
+    for (int k = 2; k <= 8; ++k) {
+        if (dist[k] < prev) { prev = dist[k]; outd[k - 1] = split[k]; }
+        else outd[k - 1] = 0;
+        outc[k - 1] = prev;
+    }
+}
+
 // Refit: the thread of leaf `pos` climbs; the second arrival at a node merges its children.
 RD_HD void rd_refit_from_leaf(const RdBinTree& T, rd_u32 pos)
 {
@@ -134,6 +196,7 @@ RD_HD void rd_refit_from_leaf(const RdBinTree& T, rd_u32 pos)
         l.x = fminf(la.x, lb.x); l.y = fminf(la.y, lb.y); l.z = fminf(la.z, lb.z); l.w = 0.0f;
         h.x = fmaxf(ha.x, hb.x); h.y = fmaxf(ha.y, hb.y); h.z = fmaxf(ha.z, hb.z); h.w = 0.0f;
         T.lo[cur] = l; T.hi[cur] = h;
+        if (T.cost) rd_dp_node(T, cur, l, h);
         cur = T.parent[cur];
     }
 }
@@ -187,19 +250,35 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
     if ((root & RD_BIN_LEAF) || rd_bin_count(T, root) <= RD_LEAF_MAX) {
         ch[n++] = root;              // tiny mesh: the root itself is the only (leaf) child
     } else {
-        ch[n++] = T.left[root]; ch[n++] = T.right[root];
-        while (n < 8) {
-            int best = -1; float bestArea = -1.0f;
-            for (int k = 0; k < n; ++k) {
-                if ((ch[k] & RD_BIN_LEAF) || rd_bin_count(T, ch[k]) <= RD_LEAF_MAX) continue;
-                const RdF4 l = T.lo[ch[k]], h = T.hi[ch[k]];
-                const float ex = h.x - l.x, ey = h.y - l.y, ez = h.z - l.z;
-                const float area = ex * ey + ey * ez + ez * ex;
-                if (area > bestArea) { bestArea = area; best = k; }
+        if (T.cost && T.dec[8u * (size_t)root]) {
+            // follow the decisions of the dynamic program from "root as a wide node with 8 slots"
+            rd_u32 sref[16]; rd_u8 sbud[16]; int sp = 0;
+            const rd_u8 k0 = T.dec[8u * (size_t)root];
+            sref[sp] = T.right[root]; sbud[sp++] = (rd_u8)(8 - k0);
+            sref[sp] = T.left[root]; sbud[sp++] = k0;
+            while (sp > 0) {
+                const rd_u32 r = sref[--sp]; rd_u8 bud = sbud[sp];
+                if (r & RD_BIN_LEAF) { ch[n++] = r; continue; }
+                const rd_u8* d = T.dec + 8u * (size_t)r;
+                while (bud > 1 && d[bud - 1] == 0) --bud;
+                if (bud == 1) { ch[n++] = r; continue; }
+                const rd_u8 i = d[bud - 1];
+                sref[sp] = T.right[r]; sbud[sp++] = (rd_u8)(bud - i);
+                sref[sp] = T.left[r]; sbud[sp++] = i;
             }
-            if (best < 0) break;
-            const rd_u32 b = ch[best];
-            ch[best] = T.left[b]; ch[n++] = T.right[b];
+        } else {
+            ch[n++] = T.left[root]; ch[n++] = T.right[root];
+            while (n < 8) {   // greedy by surface area (no cost table)
+                int best = -1; float bestArea = -1.0f;
+                for (int k = 0; k < n; ++k) {
+                    if ((ch[k] & RD_BIN_LEAF) || rd_bin_count(T, ch[k]) <= RD_LEAF_MAX) continue;
+                    const float area = rd_half_area(T.lo[ch[k]], T.hi[ch[k]]);
+                    if (area > bestArea) { bestArea = area; best = k; }
+                }
+                if (best < 0) break;
+                const rd_u32 b = ch[best];
+                ch[best] = T.left[b]; ch[n++] = T.right[b];
+            }
         }
     }
     // octant-keyed slot assignment (greedy): slot s prefers children displaced towards

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(128) rd_k_trace_dyn(const RdScene* __restrict_
 {
     const unsigned lane = threadIdx.x & 31u;
     const unsigned ltMask = (1u << lane) - 1u;
-    RdStackEntry stackMemory[RD_STACK_ENTRIES];
+    RdStackEntry stackMemory[RD_STACK_ALLOC];
     RdTraversal T;
     RdCountingHit cb; cb.terminate = (MODE & 1) != 0; cb.nodes = 0; cb.tris = 0;
     bool active = false, exhausted = false;

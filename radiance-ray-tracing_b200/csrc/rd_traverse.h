@@ -55,9 +55,6 @@ static inline float rd_u2f_(rd_u32 u) { float f; memcpy(&f, &u, 4); return f; }
 #define RD_U2F(u) rd_u2f_(u)
 #endif
 
-#ifndef RD_POSTPONE
-#define RD_POSTPONE 5   // 0 = off, k = postpone when fewer than 1/k of the active lanes have triangles
-#endif
 #ifndef RD_RECONVERGE
 #define RD_RECONVERGE 1
 #endif
@@ -70,6 +67,43 @@ struct RdHitRec {
     rd_u32 prim, inst;   // primitive index inside the mesh, instanceID (caller order)
 };
 
+// RD_FAST_MT = 1 (ablation only): the same test with fused multiply-adds and the hardware reciprocal
+// (about 2/3 of the instructions, +3.7 % Mrays/s on C2). Measured against the reference it moves
+// barycentrics of grazing hits by up to 9e-4 and flips hit/miss on 2e-5 of the C3 primary rays, so the
+// default keeps every operation separately rounded in the reference's order: t / barycentrics are then
+// bit-identical to the reference built without contraction.
+#ifndef RD_FAST_MT
+#define RD_FAST_MT 0
+#endif
+
+#if RD_FAST_MT
+RD_HD bool rd_intersect_triangle(float ox, float oy, float oz, float dx, float dy, float dz,
+                                 float ax, float ay, float az, float bx, float by, float bz,
+                                 float cx, float cy, float cz, float* t, float* b1, float* b2)
+{
+    const float e1x = bx - ax, e1y = by - ay, e1z = bz - az;
+    const float e2x = cx - ax, e2y = cy - ay, e2z = cz - az;
+    const float px = RD_FMA(dy, e2z, -dz * e2y), py = RD_FMA(dz, e2x, -dx * e2z), pz = RD_FMA(dx, e2y, -dy * e2x);
+    const float det = RD_FMA(e1x, px, RD_FMA(e1y, py, e1z * pz));
+    if (det == 0.0f) return false;
+#ifdef __CUDA_ARCH__
+    float inv;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(det));
+#else
+    const float inv = 1.0f / det;
+#endif
+    const float sx = ox - ax, sy = oy - ay, sz = oz - az;
+    const float u = inv * RD_FMA(sx, px, RD_FMA(sy, py, sz * pz));
+    const float qx = RD_FMA(sy, e1z, -sz * e1y), qy = RD_FMA(sz, e1x, -sx * e1z), qz = RD_FMA(sx, e1y, -sy * e1x);
+    const float v = inv * RD_FMA(dx, qx, RD_FMA(dy, qy, dz * qz));
+    const float tt = inv * RD_FMA(e2x, qx, RD_FMA(e2y, qy, e2z * qz));
+    if (u < 0.0f || u > 1.0f) return false;
+    if (v < 0.0f || u + v > 1.0f) return false;
+    if (!(tt > 0.0f)) return false;
+    *t = tt; *b1 = u; *b2 = v;
+    return true;
+}
+#else
 // Moeller-Trumbore with the reference's expression order (radiance/shader/radiance.cl:211-251).
 RD_HD bool rd_intersect_triangle(float ox, float oy, float oz, float dx, float dy, float dz,
                                  float ax, float ay, float az, float bx, float by, float bz,
@@ -98,6 +132,7 @@ RD_HD bool rd_intersect_triangle(float ox, float oy, float oz, float dx, float d
     *t = tt; *b1 = u; *b2 = v;
     return true;
 }
+#endif
 
 // row-major 3x4 times (x,y,z,w) with the reference's left-to-right sum (math.cl:25-31)
 RD_HD float rd_row_dot(const float* r, float x, float y, float z, float w)
@@ -212,21 +247,42 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 #endif
 
 // Traversal state of one ray over the two-level structure. begin() arms it, step() runs one
-// iteration (one node test + the triangle / instance records it exposed, or one pop) and returns
-// false when the ray is finished. Kept as a struct so that a persistent kernel can interleave
-// steps with ray fetching (csrc/rd_trace.cu); rd_traverse() below is the plain loop.
+// iteration and returns false when the ray is finished. Kept as a struct so that a persistent kernel
+// can interleave steps with ray fetching (csrc/rd_trace.cu); rd_traverse() below is the plain loop.
+//
+// One iteration has three phases that the lanes of a warp go through together:
+//   1. node phase     every lane with an inner child pending tests one 8-wide node; the triangle
+//                     records the test exposed are only NOTED in the lane's pending list
+//   2. triangle phase the warp votes; when at least 1/RD_FLUSH_DIV of the lanes hold pending records
+//                     (or one lane must flush: list full / nothing else left in this bottom-level
+//                     structure) every lane tests all its pending triangles
+//   3. pop phase      lanes without inner work take the next stack entry
+// Testing triangles as they appear ran the 87-instruction Moeller-Trumbore block with 6 of 32 lanes
+// active (ncu, profiles/README_r1.md); collecting them first is the triangle postponing of Ylitie,
+// Karras & Laine 2017 driven by a warp vote. Top-level leaf records are instances and are entered at
+// once.
 struct RdStackEntry { rd_u32 x, y; };
 
+#ifndef RD_PEND_MAX
+#define RD_PEND_MAX 1      // pending triangle groups per lane before it must flush
+#endif
+#ifndef RD_FLUSH_DIV
+#define RD_FLUSH_DIV 1     // flush when >= 1/RD_FLUSH_DIV of the active lanes hold pending triangles; 1 = at once
+                           // (measured fastest on C2: 4026 vs 3917 Mrays/s for 2..4, profiles/exp_variants_r1d.log)
+#endif
+#define RD_STACK_ALLOC (RD_STACK_ENTRIES + RD_PEND_MAX)
+
 struct RdTraversal {
-    RdStackEntry* stack;              // RD_STACK_ENTRIES entries owned by the caller (thread-local memory);
+    RdStackEntry* stack;              // RD_STACK_ALLOC entries owned by the caller (thread-local memory);
                                       // kept outside so the scalar state below stays in registers
-    int sp, blasSp;                   // blasSp >= 0 while inside a bottom-level structure
+    RdStackEntry* pend;               // pending triangle groups (the tail of the same allocation)
+    int sp, blasSp, np;               // blasSp >= 0 while inside a bottom-level structure
     const RdNode8* nodes;
     const RdTri* tris;
     const RdInstance* curInst;
     RdRayFrame f;                     // ray in the current space (world or instance-local)
     float wox, woy, woz, wdx, wdy, wdz, tmin, tmax, tbest;
-    RdStackEntry ng, tg;              // node group / record group being worked on
+    RdStackEntry ng;                  // node group being worked on
     RdHitRec hit;
     bool any;
 
@@ -238,7 +294,8 @@ struct RdTraversal {
 
     RD_HD void begin(RdStackEntry* stackMemory, const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
     {
-        stack = stackMemory; sp = 0; blasSp = -1; nodes = scene->nodes; tris = 0; curInst = 0;
+        stack = stackMemory; pend = stackMemory + RD_STACK_ENTRIES; sp = 0; blasSp = -1; np = 0;
+        nodes = scene->nodes; tris = 0; curInst = 0;
         wox = ox; woy = oy; woz = oz; wdx = dx; wdy = dy; wdz = dz; tmin = tmin_; tmax = tmax_;
         rd_frame_set(f, ox, oy, oz, dx, dy, dz);
         // the interval is open at tmax in the reference (t < Tmax); boxes are culled with <= so tmax
@@ -246,7 +303,7 @@ struct RdTraversal {
         tbest = tmax_;
         any = false;
         hit.t = RD_MISS_T; hit.b1 = 0.0f; hit.b2 = 0.0f; hit.prim = RD_INVALID; hit.inst = RD_INVALID;
-        ng.x = 0; ng.y = 0x80000000u; tg.x = 0; tg.y = 0;
+        ng.x = 0; ng.y = 0x80000000u;
     }
 
     // `onCandidate(hit)` runs after every accepted closer candidate (hit already committed) and
@@ -254,6 +311,8 @@ struct RdTraversal {
     template <class OnCandidate>
     RD_HD bool step(const RdScene* scene, OnCandidate& onCandidate)
     {
+        RdStackEntry tg; tg.x = 0; tg.y = 0;   // top-level leaf records (instances) to enter now
+        // ---- 1. node phase
         if (ng.y > 0x00ffffffu) {
             const rd_u32 bit = 31u - (rd_u32)RD_CLZ(ng.y);
             const rd_u32 imask = ng.y & 0xffu;   // low byte of an inner group = imask
@@ -268,27 +327,19 @@ struct RdTraversal {
             onCandidate.countNode();
             const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
             ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
-            tg.x = n1.y; tg.y = hm & 0x00ffffffu;
-#if RD_POSTPONE && defined(__CUDA_ARCH__)
-            // triangle postponing (Ylitie et al. 2017): when only a few lanes of the warp found
-            // triangles in this step, park the group on the stack and keep walking nodes so the
-            // triangle tests of several steps run together later
-            if (blasSp >= 0) {
-                const unsigned act = __activemask();
-                const unsigned withTris = __ballot_sync(act, tg.y != 0u);
-                if (tg.y && ng.y > 0x00ffffffu && __popc(withTris) * RD_POSTPONE < __popc(act) && sp < RD_STACK_ENTRIES) {
-                    stack[sp++] = tg; tg.y = 0;
-                }
+            const rd_u32 leafBits = hm & 0x00ffffffu;
+            if (leafBits) {
+                if (blasSp < 0) { tg.x = n1.y; tg.y = leafBits; }
+                else { pend[np].x = n1.y; pend[np].y = leafBits; ++np; }
             }
-#endif
-        } else {
-            tg = ng; ng.x = 0; ng.y = 0;
+        } else if (ng.y) {
+            tg = ng; ng.x = 0; ng.y = 0;   // a parked top-level instance group came off the stack
         }
-        while (tg.y) {
-            const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
-            tg.y &= tg.y - 1u;
-            if (blasSp < 0) {
-                // top level: record k is an instance -> descend into its bottom-level structure
+        if (blasSp < 0) {
+            if (tg.y) {
+                // top level: the first record is an instance -> descend into its bottom-level structure
+                const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
+                tg.y &= tg.y - 1u;
                 const rd_u32 ii = scene->leafInstances[tg.x + k];
                 if (tg.y) push(scene, tg);
                 if (ng.y > 0x00ffffffu) push(scene, ng);
@@ -301,27 +352,50 @@ struct RdTraversal {
                             ldz = rd_row_dot(m + 8, wdx, wdy, wdz, 0.0f);
                 rd_frame_set(f, lox, loy, loz, ldx, ldy, ldz);
                 nodes = curInst->nodes; tris = curInst->tris;
-                ng.x = 0; ng.y = 0x80000000u; tg.y = 0;
-                break;
+                ng.x = 0; ng.y = 0x80000000u;
+                return true;
             }
-            const RdTri* tr = tris + (tg.x + k);
-            RdF4 a, b, c;
-            RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
-            onCandidate.countTri();
-            float t, b1, b2;
-            if (rd_intersect_triangle(f.ox, f.oy, f.oz, f.dx, f.dy, f.dz, a.x, a.y, a.z, b.x, b.y, b.z,
-                                      c.x, c.y, c.z, &t, &b1, &b2) &&
-                t > tmin && t < tmax &&
-                (t < hit.t || (t == hit.t && (curInst->instanceID < hit.inst ||
-                                              (curInst->instanceID == hit.inst && RD_F2U(a.w) < hit.prim))))) {
-                hit.t = t; hit.b1 = b1; hit.b2 = b2; hit.prim = RD_F2U(a.w); hit.inst = curInst->instanceID;
-                tbest = t; any = true;
-                if (!onCandidate(hit)) return false;
+        } else {
+            // ---- 2. triangle phase
+            const bool exhausted = ng.y <= 0x00ffffffu && sp == blasSp;   // about to leave this structure
+            bool flush = np > 0 && (np == RD_PEND_MAX || exhausted);
+#if defined(__CUDA_ARCH__) && RD_FLUSH_DIV > 1
+            {
+                const unsigned act = __activemask();
+                const unsigned forced = __ballot_sync(act, flush);
+                const unsigned holding = __ballot_sync(act, np > 0);
+                flush = np > 0 && (forced != 0u || __popc(holding) * RD_FLUSH_DIV >= __popc(act));
+            }
+#else
+            flush = np > 0;
+#endif
+            if (flush) {
+                RdStackEntry g; g.x = 0; g.y = 0;
+                while (np > 0 || g.y) {
+                    if (!g.y) g = pend[--np];
+                    const rd_u32 k = (rd_u32)RD_FFS(g.y) - 1u;
+                    g.y &= g.y - 1u;
+                    const RdTri* tr = tris + (g.x + k);
+                    RdF4 a, b, c;
+                    RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
+                    onCandidate.countTri();
+                    float t, b1, b2;
+                    if (rd_intersect_triangle(f.ox, f.oy, f.oz, f.dx, f.dy, f.dz, a.x, a.y, a.z, b.x, b.y, b.z,
+                                              c.x, c.y, c.z, &t, &b1, &b2) &&
+                        t > tmin && t < tmax &&
+                        (t < hit.t || (t == hit.t && (curInst->instanceID < hit.inst ||
+                                                      (curInst->instanceID == hit.inst && RD_F2U(a.w) < hit.prim))))) {
+                        hit.t = t; hit.b1 = b1; hit.b2 = b2; hit.prim = RD_F2U(a.w); hit.inst = curInst->instanceID;
+                        tbest = t; any = true;
+                        if (!onCandidate(hit)) return false;
+                    }
+                }
             }
         }
+        // ---- 3. pop phase
         if (ng.y <= 0x00ffffffu) {
             if (blasSp >= 0 && sp == blasSp) {
-                // bottom-level structure exhausted: back to world space
+                // bottom-level structure exhausted (its pending list was flushed above): back to world space
                 blasSp = -1; nodes = scene->nodes;
                 rd_frame_set(f, wox, woy, woz, wdx, wdy, wdz);
             }
@@ -338,7 +412,7 @@ template <class OnCandidate>
 RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz,
                        float tmin, float tmax, RdHitRec& hit, OnCandidate& onCandidate)
 {
-    RdStackEntry stackMemory[RD_STACK_ENTRIES];
+    RdStackEntry stackMemory[RD_STACK_ALLOC];
     RdTraversal T;
 #if defined(__CUDA_ARCH__) && RD_RECONVERGE
     // The walk leaves its loop from several places and ptxas puts no reconvergence point behind it:
