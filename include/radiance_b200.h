@@ -137,7 +137,11 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * every traceRay invocation, the numerator of the Mrays/s metric; read with rd_ray_count),
  * "max_trace_depth" (1..8, default 2: how deep traceRay may nest -- raygen -> hit shader -> shadow ray is 2;
  * the user program is compiled once per level so every level inlines, PipelineCreateInfo::maxRayRecursionDepth
- * of radiance/include/radiance.h:74 is the reference's unused counterpart) */
+ * of radiance/include/radiance.h:74 is the reference's unused counterpart),
+ * "wavefront" (0/1: rd_trace_rays runs the sample / bounce loop of samples/shader.cl:196-281 as stage launches
+ * over ray queues in HBM -- generate, trace, sort by hit group, shade, resolve -- instead of one raygen
+ * launch; needs the wavefrontScene / wavefrontPrimary hooks in the program),
+ * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */

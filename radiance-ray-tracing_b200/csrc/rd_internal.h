@@ -38,8 +38,17 @@ struct rd_blas {
 
 struct rd_module {
     CUmodule mod; CUfunction raygen;
+    CUfunction wfGenerate, wfShade, wfResolve;   // 0 when the program has no wavefront hooks
+    unsigned wfPayloadSize; float wfRay[4];      // sizeof(struct Payload); sbtRecordOffset, missIndex, Tmin, Tmax
     int numRegs; int localBytes;
     std::string ptxInfo;
+};
+
+// device buffers of wavefront mode (rd_wavefront.h), grown on demand
+struct RdWfBuffers {
+    unsigned char* payload; void *color, *contrib, *rayA[2], *rayB[2]; unsigned *pathOf[2];
+    void* hitA; unsigned *hitB, *keys, *order, *counts, *hist; void* dstate;
+    unsigned capacity, payloadStride;
 };
 
 struct rd_platform {
@@ -48,9 +57,11 @@ struct rd_platform {
     uint32_t* dstatus;        // [0] stack overflow flag, [1] traceRay nesting exceeded, [2..3] 64-bit traceRay counter (option count_rays)
     unsigned long long* dcounters;   // trace counters [nodes, tris, rays] + work counter at [4]
     std::vector<uint64_t> boundArgs;
+    std::vector<int> boundKinds;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays, optMaxDepth;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort;
+    RdWfBuffers wf;
     uint64_t launches;
     int smCount;
 };
@@ -83,5 +94,14 @@ static inline RdHandleObj* rd_obj(rd_handle h)
 // rd_build.cu: generic device build over primitive boxes (dlo/dhi: n float4 each, device)
 struct RdBuildResult { RdNode8* nodes; uint32_t* leafPrim; uint32_t nodeCount, levels; float lo[3], hi[3]; };
 int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out);
+
+// rd_wavefront.cu
+struct RdWfState;
+int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride);
+void rd_wf_release(rd_platform* p);
+int rd_wf_upload_state(rd_platform* p, const RdWfState* host);
+int rd_wf_advance(rd_platform* p, unsigned op, unsigned a);
+int rd_wf_trace(rd_platform* p, const void* scene);
+int rd_wf_sort(rd_platform* p, unsigned count);
 
 #endif

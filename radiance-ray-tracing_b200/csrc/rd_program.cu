@@ -4,6 +4,7 @@
 // through clBuildProgram with -I SHADER_LIB_PATH), :226-267 (BindPipeline, BindDescriptorSet,
 // TraceRays) and tools/genSBT.py (switch generation from sbt.json).
 #include <nvrtc.h>
+#include <ctype.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -11,6 +12,7 @@
 #include <vector>
 #include "rd_internal.h"
 #include "rd_embedded.h"
+#include "rd_wavefront.h"
 
 // The driver API is reached through cudaGetDriverEntryPoint instead of linking libcuda.so.1, so the
 // library (and its symbol table) can be loaded on a machine without a driver; every entry point is
@@ -220,6 +222,168 @@ static std::string generate_dispatchers(const std::vector<SbtRow>& rows, bool hi
     return s;
 }
 
+
+// ---- wavefront stage kernels --------------------------------------------------------------------
+// Parameter list of the program's raygen kernel: (type text, name) per parameter, in order. The
+// generated stage kernels repeat it so that the same descriptor set binds to them.
+struct RaygenParam { std::string type, name; };
+static bool parse_raygen_params(const std::string& bare, std::vector<RaygenParam>* out)
+{
+    size_t pos = 0;
+    while ((pos = bare.find("raygen", pos)) != std::string::npos) {
+        size_t q = pos + 6;
+        while (q < bare.size() && (bare[q] == ' ' || bare[q] == '\t' || bare[q] == '\n' || bare[q] == '\r')) ++q;
+        if (q < bare.size() && bare[q] == '(' && bare.rfind("__kernel", pos) != std::string::npos) { pos = q; break; }
+        pos += 6;
+    }
+    if (pos == std::string::npos) return false;
+    size_t end = bare.find(')', pos);
+    if (end == std::string::npos) return false;
+    std::string list = bare.substr(pos + 1, end - pos - 1);
+    size_t a = 0;
+    while (a <= list.size()) {
+        size_t b = list.find(',', a);
+        if (b == std::string::npos) b = list.size();
+        std::string item = list.substr(a, b - a);
+        size_t e = item.find_last_not_of(" \t\r\n");
+        if (e != std::string::npos) {
+            size_t st = e;
+            while (st > 0 && (isalnum((unsigned char)item[st - 1]) || item[st - 1] == '_')) --st;
+            RaygenParam rp; rp.name = item.substr(st, e - st + 1); rp.type = item.substr(0, st);
+            if (rp.name.empty()) return false;
+            out->push_back(rp);
+        }
+        a = b + 1;
+    }
+    return !out->empty();
+}
+
+// generate / shade / resolve kernels around the user's wavefront hooks:
+//   void wavefrontScene(struct SceneData*, <raygen parameters>)      fill SceneData from the descriptors
+//   void wavefrontPrimary(struct Payload*, struct SceneData*, uint frameID, uint totalSamples)
+//   float3 wavefrontTonemap(float3)                                  optional, default shader.cl:289-298
+// The loop they implement is samples/shader.cl:228-281.
+static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P, bool hasTonemap)
+{
+    std::string plist, names, image = "0", sampler = "0", top;
+    for (size_t i = 0; i < P.size(); ++i) {
+        plist += P[i].type + " " + P[i].name + ", ";
+        names += (i ? ", " : "") + P[i].name;
+        if (P[i].type.find("image2d_array_t") != std::string::npos) image = P[i].name;
+        else if (P[i].type.find("sampler_t") != std::string::npos) sampler = P[i].name;
+        else if (P[i].type.find("AccelStruct") != std::string::npos) top = P[i].name;
+    }
+    if (top.empty() || P.size() < 3) return "";
+    std::string s = "\n// ---- wavefront stages generated by the runtime ----\n#include \"rd_wavefront.h\"\nnamespace rd_l0 {\n";
+    s += "extern \"C\" __global__ void rd_wf_generate(" + plist + "const RdWfState* wfp)\n{\n"
+         "    const RdWfState wf = *wfp;\n"
+         "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
+         "    if (slot >= wf.count) return;\n"
+         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    struct SceneData sd; struct Payload pl;\n"
+         "    wavefrontScene(&sd, " + names + ");\n"
+         "    sd.depth = 0; sd.frameID = wf.frameID;\n"
+         "    wavefrontPrimary(&pl, &sd, wf.frameID, wf.totalSamples);\n"
+         "    pl.hit = false;\n"
+         "    *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride) = pl;\n"
+         "    RdF4 a, b, one, zero;\n"
+         "    a.x = pl.nextRayOrigin.x; a.y = pl.nextRayOrigin.y; a.z = pl.nextRayOrigin.z; a.w = wf.tmin;\n"
+         "    b.x = pl.nextRayDirection.x; b.y = pl.nextRayDirection.y; b.z = pl.nextRayDirection.z; b.w = wf.tmax;\n"
+         "    one.x = one.y = one.z = one.w = 1.0f; zero.x = zero.y = zero.z = zero.w = 0.0f;\n"
+         "    wf.rayA[wf.cur][slot] = a; wf.rayB[wf.cur][slot] = b; wf.pathOf[wf.cur][slot] = slot;\n"
+         "    wf.color[slot] = zero; wf.contrib[slot] = one;\n"
+         "    if (slot == 0) { wf.counts[wf.cur] = wf.count; wf.counts[wf.cur ^ 1u] = 0u; }\n"
+         "}\n\n";
+    s += "extern \"C\" __global__ void rd_wf_shade(" + plist + "const RdWfState* wfp)\n{\n"
+         "    const RdWfState wf = *wfp;\n"
+         "    const unsigned n = wf.counts[wf.cur];\n"
+         "    const unsigned jj = blockIdx.x * blockDim.x + threadIdx.x;\n"
+         "    if (jj >= n) return;\n"
+         "    const unsigned j = wf.sortOn ? wf.order[jj] : jj;\n"
+         "    const unsigned slot = wf.pathOf[wf.cur][j];\n"
+         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    rd_wf_gid[threadIdx.x] = gid;\n"
+         "    struct SceneData sd;\n"
+         "    wavefrontScene(&sd, " + names + ");\n"
+         "    sd.depth = wf.depth; sd.frameID = wf.frameID;\n"
+         "    struct Payload pl = *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride);\n"
+         "    const RdF4 ha = wf.hitA[j];\n"
+         "    if (ha.x < RD_MISS_T) {\n"
+         "        const RdF4 ra = wf.rayA[wf.cur][j], rb = wf.rayB[wf.cur][j];\n"
+         "        RdHitRec h; h.t = ha.x; h.b1 = ha.y; h.b2 = ha.z; h.prim = RD_F2U(ha.w); h.inst = wf.hitB[j];\n"
+         "        struct HitData hd;\n"
+         "        rd_fill_hit_data((const RdScene*)" + top + ", float3(ra.x, ra.y, ra.z), float3(rb.x, rb.y, rb.z), h, &hd);\n"
+         "        rd_l1::callHit(wf.sbtRecordOffset, (rd_l1::Payload*)&pl, &hd, (rd_l1::SceneData*)&sd, " + image + ", " + sampler + ");\n"
+         "    } else {\n"
+         "        rd_l1::callMiss(wf.missIndex, (rd_l1::Payload*)&pl, (rd_l1::SceneData*)&sd, " + image + ", " + sampler + ");\n"
+         "    }\n"
+         "    // bounce loop body of samples/shader.cl:238-260\n"
+         "    RdF4 col = wf.color[slot], con = wf.contrib[slot];\n"
+         "    bool more = false;\n"
+         "    if (pl.hit) {\n"
+         "        col.x += con.x * pl.color.x; col.y += con.y * pl.color.y; col.z += con.z * pl.color.z;\n"
+         "        con.x *= pl.nextFactor.x; con.y *= pl.nextFactor.y; con.z *= pl.nextFactor.z;\n"
+         "        more = true;\n"
+         "    } else if (wf.depth == 0) { col.x = pl.color.x; col.y = pl.color.y; col.z = pl.color.z; }\n"
+         "    if (wf.depth + 1u >= wf.maxDepth || wf.debug) more = false;\n"
+         "    // live paths are compacted into the next queue: one atomic per warp\n"
+         "    const unsigned act = __activemask();\n"
+         "    const unsigned live = __ballot_sync(act, more);\n"
+         "    unsigned base = 0;\n"
+         "    const unsigned lane = threadIdx.x & 31u;\n"
+         "    if (live) {\n"
+         "        const unsigned leader = (unsigned)__ffs(live) - 1u;\n"
+         "        if (lane == leader) base = atomicAdd(&wf.counts[wf.cur ^ 1u], (unsigned)__popc(live));\n"
+         "        base = __shfl_sync(act, base, leader);\n"
+         "    }\n"
+         "    if (more) {\n"
+         "        const unsigned k = base + (unsigned)__popc(live & ((1u << lane) - 1u));\n"
+         "        RdF4 a, b;\n"
+         "        a.x = pl.nextRayOrigin.x; a.y = pl.nextRayOrigin.y; a.z = pl.nextRayOrigin.z; a.w = wf.tmin;\n"
+         "        b.x = pl.nextRayDirection.x; b.y = pl.nextRayDirection.y; b.z = pl.nextRayDirection.z; b.w = wf.tmax;\n"
+         "        wf.rayA[wf.cur ^ 1u][k] = a; wf.rayB[wf.cur ^ 1u][k] = b; wf.pathOf[wf.cur ^ 1u][k] = slot;\n"
+         "        pl.hit = false;\n"
+         "        *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride) = pl;\n"
+         "        wf.color[slot] = col; wf.contrib[slot] = con;\n"
+         "    } else {\n"
+         "        // the sample is complete: running mean of samples/shader.cl:262-279\n"
+         "        float* px = (float*)" + P[1].name + " + 4 * (size_t)gid;\n"
+         "        if (wf.frameID == 0) { px[0] = col.x; px[1] = col.y; px[2] = col.z; }\n"
+         "        else {\n"
+         "            px[0] = (wf.frameID * px[0] + col.x) / (wf.frameID + 1);\n"
+         "            px[1] = (wf.frameID * px[1] + col.y) / (wf.frameID + 1);\n"
+         "            px[2] = (wf.frameID * px[2] + col.z) / (wf.frameID + 1);\n"
+         "        }\n"
+         "    }\n"
+         "}\n\n";
+    s += "extern \"C\" __global__ void rd_wf_resolve(" + plist + "const RdWfState* wfp)\n{\n"
+         "    const RdWfState wf = *wfp;\n"
+         "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
+         "    if (slot >= wf.count) return;\n"
+         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    const float* px = (const float*)" + P[1].name + " + 4 * (size_t)gid;\n"
+         "    float3 color = {px[0], px[1], px[2]};\n"
+         "    if (!wf.debug) {\n";
+    if (hasTonemap) s += "        color = wavefrontTonemap(color);\n";
+    else s += "        // samples/shader.cl:47-56, 289-298: ACES approximation, then pow 0.7\n"
+              "        color *= 0.6f;\n"
+              "        color = clamp((color * (2.51f * color + 0.03f)) / (color * (2.43f * color + 0.59f) + 0.14f), 0.0f, 1.0f);\n"
+              "        color = pow(color, 0.7f);\n";
+    s += "    }\n"
+         "    uchar* out = (uchar*)" + P[2].name + " + 4 * (size_t)gid;\n"
+         "    out[0] = (int)(color.x * 255); out[1] = (int)(color.y * 255); out[2] = (int)(color.z * 255); out[3] = 255;\n"
+         "}\n"
+         "#ifndef WAVEFRONT_SBT_RECORD_OFFSET\n#define WAVEFRONT_SBT_RECORD_OFFSET 1\n#endif\n"
+         "#ifndef WAVEFRONT_MISS_INDEX\n#define WAVEFRONT_MISS_INDEX 3\n#endif\n"
+         "#ifndef WAVEFRONT_TMIN\n#define WAVEFRONT_TMIN 0.001f\n#endif\n"
+         "#ifndef WAVEFRONT_TMAX\n#define WAVEFRONT_TMAX 1000.0f\n#endif\n"
+         "extern \"C\" __global__ void rd_wf_query(float* out)\n{\n"
+         "    out[0] = (float)sizeof(struct Payload); out[1] = WAVEFRONT_SBT_RECORD_OFFSET; out[2] = WAVEFRONT_MISS_INDEX;\n"
+         "    out[3] = WAVEFRONT_TMIN; out[4] = WAVEFRONT_TMAX;\n}\n"
+         "}  // namespace rd_l0\n";
+    return s;
+}
+
 extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 {
     if (!p || !json_text) { rd_set_error("rd_sbt_load_json: null argument"); return RD_E_ARG; }
@@ -272,6 +436,12 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
         if (k == 1) mainSrc += "#undef __kernel\n#define __kernel static __device__\n";
         snprintf(line, sizeof(line), "namespace rd_l%d {\n#include \"rd_user_program.cl\"\n}\n", k);
         mainSrc += line;
+    }
+    // wavefront stages when the program provides the hooks
+    if (defines_function(bare, "wavefrontScene") && defines_function(bare, "wavefrontPrimary")) {
+        std::vector<RaygenParam> params;
+        if (parse_raygen_params(bare, &params))
+            mainSrc += generate_wavefront_kernels(params, bare.find("wavefrontTonemap") != std::string::npos);
     }
     std::vector<const char*> hdrNames(rd_embedded_names, rd_embedded_names + rd_embedded_count);
     std::vector<const char*> hdrSources(rd_embedded_sources, rd_embedded_sources + rd_embedded_count);
@@ -342,6 +512,25 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     if (cr != CUDA_SUCCESS) { const char* s = 0; cuGetErrorString(cr, &s); rd_set_error("cuModuleLoadData: %s", s ? s : "?"); delete m; return RD_E_CUDA; }
     cr = cuModuleGetFunction(&m->raygen, m->mod, "raygen");   // the reference always extracts "raygen" (radiance.cpp:177)
     if (cr != CUDA_SUCCESS) { rd_set_error("program has no __kernel named raygen"); cuModuleUnload(m->mod); delete m; return RD_E_COMPILE; }
+    // wavefront stages exist when the program defines the hooks (generate_wavefront_kernels)
+    m->wfGenerate = m->wfShade = m->wfResolve = 0; m->wfPayloadSize = 0;
+    if (cuModuleGetFunction(&m->wfGenerate, m->mod, "rd_wf_generate") == CUDA_SUCCESS &&
+        cuModuleGetFunction(&m->wfShade, m->mod, "rd_wf_shade") == CUDA_SUCCESS &&
+        cuModuleGetFunction(&m->wfResolve, m->mod, "rd_wf_resolve") == CUDA_SUCCESS) {
+        // sizeof(struct Payload) and the WAVEFRONT_* ray constants are known to the compiled program only
+        CUfunction query = 0; float* dq = 0; float hq[5] = {0, 0, 0, 0, 0};
+        if (cuModuleGetFunction(&query, m->mod, "rd_wf_query") == CUDA_SUCCESS && cudaMalloc(&dq, sizeof(hq)) == cudaSuccess) {
+            void* qargv[] = {&dq};
+            if (cuLaunchKernel(query, 1, 1, 1, 1, 1, 1, 0, (CUstream)p->stream, qargv, 0) == CUDA_SUCCESS &&
+                cudaMemcpyAsync(hq, dq, sizeof(hq), cudaMemcpyDeviceToHost, p->stream) == cudaSuccess)
+                cudaStreamSynchronize(p->stream);
+            cudaFree(dq);
+            p->launches += 1;
+        }
+        m->wfPayloadSize = (unsigned)hq[0];
+        for (int i = 0; i < 4; ++i) m->wfRay[i] = hq[1 + i];
+        if (!m->wfPayloadSize) m->wfGenerate = 0;
+    } else m->wfGenerate = 0;
     cuFuncGetAttribute(&m->numRegs, CU_FUNC_ATTRIBUTE_NUM_REGS, m->raygen);
     cuFuncGetAttribute(&m->localBytes, CU_FUNC_ATTRIBUTE_LOCAL_SIZE_BYTES, m->raygen);
     *out = m;
@@ -374,12 +563,74 @@ extern "C" int rd_pipeline_bind(rd_platform* p, rd_module* const* modules, unsig
 extern "C" int rd_descriptors_bind(rd_platform* p, const rd_handle* handles, unsigned n)
 {
     if (!p || (n && !handles)) { rd_set_error("rd_descriptors_bind: null argument"); return RD_E_ARG; }
-    p->boundArgs.clear();
+    p->boundArgs.clear(); p->boundKinds.clear();
     for (unsigned i = 0; i < n; ++i) {
         RdHandleObj* o = rd_obj(handles[i]);
         if (!o) { rd_set_error("rd_descriptors_bind: descriptor %u is not a handle of this library", i); return RD_E_ARG; }
-        p->boundArgs.push_back(o->arg);
+        p->boundArgs.push_back(o->arg); p->boundKinds.push_back((int)o->kind);
     }
+    return RD_OK;
+}
+
+
+// ---- wavefront sequencer ------------------------------------------------------------------------
+// RD::TraceRays in wavefront mode: the sample loop and the bounce loop of samples/shader.cl:196-281 as
+// stage launches (rd_wavefront.h). The only host read is RTProp (16 bytes) before the first stage.
+static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
+                                   unsigned long long count)
+{
+    rd_module* m = p->boundModule;
+    if (!m->wfGenerate) {
+        rd_set_error("rd_trace_rays: option wavefront is on but the program defines no wavefrontScene / wavefrontPrimary hooks");
+        return RD_E_STATE;
+    }
+    if (p->boundArgs.size() < 3) { rd_set_error("rd_trace_rays: wavefront mode needs RTProp, imageScratch, image as descriptors 0..2"); return RD_E_STATE; }
+    const unsigned total = width * height;
+    unsigned rt[4] = {0, 0, 0, 0};   // RayTraceProperties: totalSamples, batchSize, depth, debug (core.h:103-109)
+    RD_CUDA(cudaMemcpyAsync(rt, (const void*)p->boundArgs[0], 16, cudaMemcpyDeviceToHost, p->stream));
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    const unsigned stride = (m->wfPayloadSize + 15u) & ~15u;
+    int rc = rd_wf_reserve(p, (unsigned)count, stride);
+    if (rc) return rc;
+    // the scene header is whichever descriptor is a top-level structure
+    const void* scene = 0;
+    for (size_t i = 0; i < p->boundKinds.size(); ++i) if (p->boundKinds[i] == RD_H_TLAS) scene = (const void*)p->boundArgs[i];
+    if (!scene) { rd_set_error("rd_trace_rays: no top-level acceleration structure in the descriptor set"); return RD_E_STATE; }
+    RdWfBuffers& B = p->wf;
+    RdWfState S; memset(&S, 0, sizeof(S));
+    S.payload = B.payload; S.color = (RdF4*)B.color; S.contrib = (RdF4*)B.contrib;
+    for (int q = 0; q < 2; ++q) { S.rayA[q] = (RdF4*)B.rayA[q]; S.rayB[q] = (RdF4*)B.rayB[q]; S.pathOf[q] = B.pathOf[q]; }
+    S.hitA = (RdF4*)B.hitA; S.hitB = B.hitB; S.keys = B.keys; S.order = B.order; S.counts = B.counts; S.hist = B.hist;
+    S.payloadStride = stride; S.cur = 0; S.first = (unsigned)first; S.count = (unsigned)count; S.total = total;
+    S.tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
+    S.frameID = rt[0]; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
+    S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
+    rc = rd_wf_upload_state(p, &S);
+    if (rc) return rc;
+    CUdeviceptr dinfo; size_t infoBytes = 0;
+    RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
+    const unsigned info[4] = {(unsigned)first, total, S.tileW, 1u};
+    RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
+    std::vector<uint64_t> args(p->boundArgs);
+    args.push_back((uint64_t)(uintptr_t)B.dstate);
+    std::vector<void*> argv(args.size());
+    for (size_t i = 0; i < argv.size(); ++i) argv[i] = &args[i];
+    const unsigned blocks = (unsigned)((count + 127) / 128);
+    for (unsigned k = 0; k < rt[1]; ++k) {
+        rc = rd_wf_advance(p, 0u, rt[0] + k); if (rc) return rc;
+        RD_CU(cuLaunchKernel(m->wfGenerate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+        p->launches += 1;
+        for (unsigned d = 0; d < rt[2]; ++d) {
+            rc = rd_wf_trace(p, scene); if (rc) return rc;
+            if (S.sortOn) { rc = rd_wf_sort(p, (unsigned)count); if (rc) return rc; }
+            RD_CU(cuLaunchKernel(m->wfShade, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+            p->launches += 1;
+            rc = rd_wf_advance(p, 2u, 0u); if (rc) return rc;
+            if (rt[3]) break;
+        }
+    }
+    RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+    p->launches += 1;
     return RD_OK;
 }
 
@@ -398,6 +649,7 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
     if (!count) count = total - first;
     if (!count) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
+    if (p->optWavefront) return rd_trace_rays_wavefront(p, width, height, first, count);
     rd_module* m = p->boundModule;
     CUdeviceptr dinfo; size_t infoBytes = 0;
     RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));

@@ -1,0 +1,179 @@
+// rd_wavefront.cu -- library stages of wavefront mode: queue tracing, the hit-group / material sort
+// and the host loop that sequences the stages (RD::TraceRays in wavefront mode).
+// Replaces the loop nest inside the reference's raygen kernel (samples/shader.cl:196-281) by stage
+// launches over queues in HBM; see rd_wavefront.h for the state and csrc/rd_program.cu for the
+// generate / shade / resolve kernels that are compiled together with the user program.
+#include <string.h>
+#include "rd_internal.h"
+#include "rd_traverse.h"
+#include "rd_wavefront.h"
+
+// ---- trace stage --------------------------------------------------------------------------------
+// Closest hit for every entry of the current queue. Persistent warps take batches of 32 consecutive
+// entries from a counter (queue size lives in HBM: no host round trip between stages). Also emits
+// the shade stage's sort key: (hit group row, capped at 255) * 4 + (instanceCustomIndex & 3), where
+// the row is instanceSBTOffset + sbtRecordOffset for hits (radiance.cl:23-28 dispatch rule) and the
+// miss index for misses.
+__global__ void __launch_bounds__(128) rd_k_wf_trace(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
+{
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    const unsigned lane = threadIdx.x & 31u;
+    const float4* __restrict__ rayA = (const float4*)wf.rayA[wf.cur];
+    const float4* __restrict__ rayB = (const float4*)wf.rayB[wf.cur];
+    for (;;) {
+        unsigned base = 0;
+        if (lane == 0) base = atomicAdd(&wf.counts[2], 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        const unsigned j = base + lane;
+        if (j < n) {
+            const float4 a = __ldg(&rayA[j]), b = __ldg(&rayB[j]);
+            RdHitRec h; RdNoAnyHit cb;
+            rd_traverse(scene, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w, h, cb);
+            ((float4*)wf.hitA)[j] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
+            wf.hitB[j] = h.inst;
+            unsigned row = (unsigned)wf.missIndex, mat = 0u;
+            if (h.t < RD_MISS_T) {
+                const RdInstance* I = scene->instances + h.inst;
+                row = I->sbtOffset + (unsigned)wf.sbtRecordOffset; mat = I->customID & 3u;
+            }
+            wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
+        }
+    }
+}
+
+// ---- sort stage ---------------------------------------------------------------------------------
+// Counting sort of the queue entries by key (RD_WF_KEY_BINS bins): block-local histograms in shared
+// memory, one scan block, then a scatter in which every warp ranks its entries with match_any and
+// claims a run of output positions per distinct key with one atomic (warp-level compaction).
+__global__ void rd_k_wf_hist(const RdWfState* __restrict__ wfp)
+{
+    __shared__ unsigned bins[RD_WF_KEY_BINS];
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    for (unsigned b = threadIdx.x; b < RD_WF_KEY_BINS; b += blockDim.x) bins[b] = 0u;
+    __syncthreads();
+    for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
+        atomicAdd(&bins[wf.keys[j]], 1u);
+    __syncthreads();
+    for (unsigned b = threadIdx.x; b < RD_WF_KEY_BINS; b += blockDim.x)
+        if (bins[b]) atomicAdd(&wf.hist[b], bins[b]);
+}
+
+__global__ void rd_k_wf_scan(const RdWfState* __restrict__ wfp)   // one block of RD_WF_KEY_BINS threads
+{
+    __shared__ unsigned warpSums[32];
+    const RdWfState wf = *wfp;
+    const unsigned t = threadIdx.x, lane = t & 31u, w = t >> 5;
+    const unsigned v = wf.hist[t];
+    unsigned x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= (unsigned)o) x += y; }
+    if (lane == 31u) warpSums[w] = x;
+    __syncthreads();
+    if (w == 0) {
+        unsigned s = warpSums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= (unsigned)o) s += y; }
+        warpSums[lane] = s;
+    }
+    __syncthreads();
+    wf.hist[t] = x - v + (w ? warpSums[w - 1] : 0u);   // exclusive prefix = first output position of the bin
+}
+
+__global__ void rd_k_wf_scatter(const RdWfState* __restrict__ wfp)
+{
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u;
+    const bool valid = j < n;
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    if (!valid) return;
+    const unsigned key = wf.keys[j];
+    const unsigned same = __match_any_sync(act, key);
+    const unsigned leader = (unsigned)__ffs(same) - 1u;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(&wf.hist[key], (unsigned)__popc(same));
+    base = __shfl_sync(same, base, leader);
+    wf.order[base + (unsigned)__popc(same & ((1u << lane) - 1u))] = j;
+}
+
+// per-stage state edits on the device (keeps the stage sequence free of host synchronisation)
+__global__ void rd_k_wf_advance(RdWfState* wf, unsigned op, unsigned a, unsigned b)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    if (op == 0) { wf->frameID = a; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; }                    // new sample
+    else if (op == 1) { wf->counts[2] = 0; }                                                           // before trace
+    else if (op == 2) { wf->cur ^= 1u; wf->counts[wf->cur ^ 1u] = 0; wf->depth += 1; wf->counts[2] = 0; } // after shade
+}
+
+// ---- launch wrappers used by the stage sequencer in rd_program.cu -------------------------------
+int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride)
+{
+    RdWfBuffers& B = p->wf;
+    if (B.capacity >= count && B.payloadStride >= payloadStride && B.dstate) return RD_OK;
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    void** all[] = {(void**)&B.payload, (void**)&B.color, (void**)&B.contrib, (void**)&B.rayA[0], (void**)&B.rayA[1], (void**)&B.rayB[0],
+                    (void**)&B.rayB[1], (void**)&B.pathOf[0], (void**)&B.pathOf[1], (void**)&B.hitA, (void**)&B.hitB, (void**)&B.keys,
+                    (void**)&B.order, (void**)&B.counts, (void**)&B.hist, (void**)&B.dstate};
+    for (void** q : all) { if (*q) cudaFree(*q); *q = 0; }
+    const size_t n = count ? count : 1;
+    RD_CUDA(cudaMalloc(&B.payload, n * payloadStride));
+    RD_CUDA(cudaMalloc(&B.color, n * 16)); RD_CUDA(cudaMalloc(&B.contrib, n * 16));
+    for (int q = 0; q < 2; ++q) {
+        RD_CUDA(cudaMalloc(&B.rayA[q], n * 16)); RD_CUDA(cudaMalloc(&B.rayB[q], n * 16)); RD_CUDA(cudaMalloc(&B.pathOf[q], n * 4));
+    }
+    RD_CUDA(cudaMalloc(&B.hitA, n * 16)); RD_CUDA(cudaMalloc(&B.hitB, n * 4));
+    RD_CUDA(cudaMalloc(&B.keys, n * 4)); RD_CUDA(cudaMalloc(&B.order, n * 4));
+    RD_CUDA(cudaMalloc(&B.counts, 64)); RD_CUDA(cudaMalloc(&B.hist, RD_WF_KEY_BINS * 4));
+    RD_CUDA(cudaMalloc(&B.dstate, sizeof(RdWfState)));
+    RD_CUDA(cudaMemset(B.counts, 0, 64));
+    B.capacity = count; B.payloadStride = payloadStride;
+    return RD_OK;
+}
+
+void rd_wf_release(rd_platform* p)
+{
+    RdWfBuffers& B = p->wf;
+    void* all[] = {B.payload, B.color, B.contrib, B.rayA[0], B.rayA[1], B.rayB[0], B.rayB[1], B.pathOf[0], B.pathOf[1],
+                   B.hitA, B.hitB, B.keys, B.order, B.counts, B.hist, B.dstate};
+    for (void* q : all) if (q) cudaFree(q);
+    memset(&B, 0, sizeof(B));
+}
+
+int rd_wf_upload_state(rd_platform* p, const RdWfState* host)
+{
+    RD_CUDA(cudaMemcpyAsync(p->wf.dstate, host, sizeof(RdWfState), cudaMemcpyHostToDevice, p->stream));
+    return RD_OK;
+}
+
+int rd_wf_advance(rd_platform* p, unsigned op, unsigned a)
+{
+    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, op, a, 0u);
+    p->launches += 1;
+    RD_CUDA(cudaGetLastError());
+    return RD_OK;
+}
+
+int rd_wf_trace(rd_platform* p, const void* scene)
+{
+    rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+    p->launches += 1;
+    RD_CUDA(cudaGetLastError());
+    return RD_OK;
+}
+
+int rd_wf_sort(rd_platform* p, unsigned count)
+{
+    const RdWfState* S = (const RdWfState*)p->wf.dstate;
+    RD_CUDA(cudaMemsetAsync(p->wf.hist, 0, RD_WF_KEY_BINS * 4, p->stream));
+    unsigned hb = (count + 255u) / 256u; if (hb > (unsigned)p->smCount * 8u) hb = (unsigned)p->smCount * 8u; if (!hb) hb = 1;
+    rd_k_wf_hist<<<hb, 256, 0, p->stream>>>(S);
+    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, p->stream>>>(S);
+    rd_k_wf_scatter<<<(count + 255u) / 256u, 256, 0, p->stream>>>(S);
+    p->launches += 3;
+    RD_CUDA(cudaGetLastError());
+    return RD_OK;
+}

@@ -1,0 +1,50 @@
+// rd_wavefront.h -- state shared by the wavefront stages (library kernels in rd_wavefront.cu and the
+// generate / shade / resolve kernels that rd_program.cu appends to the user program for NVRTC).
+//
+// Wavefront mode runs the sample loop and the bounce loop that the reference spells out inside its
+// raygen kernel (samples/shader.cl:196-281) as a sequence of stage launches over queues in HBM:
+//   generate -> [ trace -> sort by hit group / material -> shade ] x depth -> (next sample) -> resolve
+// A path owns one slot (its launch-local work-item index); the user's `struct Payload` lives in the
+// payload array of that slot between stages. Ray / hit queues are structure-of-arrays, 16-byte
+// records, compacted every bounce (only live paths are traced and shaded).
+#ifndef RD_WAVEFRONT_H
+#define RD_WAVEFRONT_H
+#include "rd_types.h"
+
+#define RD_WF_KEY_BINS 1024u      // (hit group row, capped at 255) * 4 + (instanceCustomIndex & 3)
+
+struct RD_ALIGN(16) RdWfState {
+    // per path slot
+    unsigned char* payload;       // slot * payloadStride: the user's struct Payload
+    RdF4* color;                  // accumulated sample colour (shader.cl:228 `color`)
+    RdF4* contrib;                // path throughput (shader.cl:229 `contribution`)
+    // compact queues, double buffered: entry j of queue q
+    RdF4* rayA[2];                // { o.xyz, tmin }
+    RdF4* rayB[2];                // { d.xyz, tmax }
+    rd_u32* pathOf[2];            // slot of the path the ray belongs to
+    RdF4* hitA;                   // { t, b1, b2, primID bits } of queue `cur`
+    rd_u32* hitB;                 // instanceID
+    rd_u32* keys;                 // sort key of entry j
+    rd_u32* order;                // entries of queue `cur` in key order (0 = identity)
+    rd_u32* counts;               // [0], [1] queue sizes; [2] batch fetch counter of the trace kernel
+    rd_u32* hist;                 // RD_WF_KEY_BINS bin counters / cursors
+    rd_u32 payloadStride, cur;
+    rd_u32 first, count;          // work-item range of this TraceRays call (slot s = work-item first + s)
+    rd_u32 total, tileW;          // NDRange size and the width of the 8x4 tile remap (0 = identity)
+    rd_u32 frameID, totalSamples; // sample being traced, RTProp->totalSamples
+    rd_u32 depth, maxDepth;       // bounce index of this stage, RTProp->depth
+    rd_u32 debug, sortOn;
+    int sbtRecordOffset, missIndex;
+    float tmin, tmax;
+};
+
+// work-item t of the launch -> global id (pixel index), same mapping as get_global_id in cl_compat.h
+RD_HD rd_u32 rd_wf_global_id(rd_u32 t, rd_u32 tileW)
+{
+    if (!tileW) return t;
+    const rd_u32 tilesX = tileW >> 3, tile = t >> 5, lane = t & 31u;
+    const rd_u32 ty = tile / tilesX, tx = tile - ty * tilesX;
+    return ((ty << 2) + (lane >> 3)) * tileW + (tx << 3) + (lane & 7u);
+}
+
+#endif

@@ -18,7 +18,13 @@ struct Payload {
     bool hit;
 };
 
+struct PhysicalCamera {
+    float widthPixel, heightPixel, focalLength, sensorWidth, focalDistance, fStop;
+    float x, y, z, wx, wy, wz;
+};
+
 struct SceneData {
+    __global struct PhysicalCamera* camData;
     __global struct SceneProperties* scene;
     __global struct MeshInfo* meshInfoData;
     __global float* vertexData;
@@ -30,10 +36,6 @@ struct SceneData {
     unsigned int frameID;
 };
 
-struct PhysicalCamera {
-    float widthPixel, heightPixel, focalLength, sensorWidth, focalDistance, fStop;
-    float x, y, z, wx, wy, wz;
-};
 
 // pinhole camera of samples/shader.cl:111-153 (jittered pixel, sensor point, Rx Ry Rz rotation)
 void cameraRay(__global const struct PhysicalCamera* cam, uint3 seed, float3* origin, float3* direction)
@@ -59,6 +61,52 @@ void cameraRay(__global const struct PhysicalCamera* cam, uint3 seed, float3* or
     *direction = t0.xyz;
 }
 
+// ---- wavefront hooks (INTEGRATION.md "Wavefront mode"): the two pieces of raygen that the runtime
+// cannot guess, factored out so that the inline kernel below and the wavefront stages share them.
+void wavefrontScene(struct SceneData* sceneData,
+    __global struct RayTraceProperties* RTProp,
+    __global float* imageScratch,
+    __global uchar* image,
+    __global struct PhysicalCamera* camData,
+    __global struct SceneProperties* scene,
+    __global struct MeshInfo* meshInfoData,
+    __global float* vertexData,
+    __global uint* indexData,
+    __global float* uvData,
+    __global float* normalData,
+    __global struct Material* materials,
+    image2d_array_t imageArray,
+    sampler_t sampler,
+    __global struct AccelStruct* topLevel)
+{
+    sceneData->camData = camData;
+    sceneData->scene = scene;
+    sceneData->meshInfoData = meshInfoData;
+    sceneData->vertexData = vertexData;
+    sceneData->indexData = indexData;
+    sceneData->normalData = normalData;
+    sceneData->materials = materials;
+    sceneData->topLevel = topLevel;
+    sceneData->depth = 0;
+    sceneData->frameID = 0;
+}
+
+void wavefrontPrimary(struct Payload* payload, struct SceneData* sceneData, unsigned int frameID, unsigned int totalSamples)
+{
+    uint3 seed = {frameID, totalSamples, (uint)get_global_id(0)};
+    cameraRay(sceneData->camData, seed, &payload->nextRayOrigin, &payload->nextRayDirection);
+    payload->color = 0.0f;
+    payload->nextFactor = 1.0f;
+    payload->hit = false;
+}
+
+// Reinhard + gamma (shader2.cl:167-173)
+float3 wavefrontTonemap(float3 color)
+{
+    color = color / (color + 1.0f);
+    return pow(color, 0.4545f);
+}
+
 __kernel void raygen(
     __global struct RayTraceProperties* RTProp,
     __global float* imageScratch,
@@ -77,52 +125,43 @@ __kernel void raygen(
 {
     const int index = get_global_id(0);
     struct SceneData sceneData;
-    sceneData.scene = scene;
-    sceneData.meshInfoData = meshInfoData;
-    sceneData.vertexData = vertexData;
-    sceneData.indexData = indexData;
-    sceneData.normalData = normalData;
-    sceneData.materials = materials;
-    sceneData.topLevel = topLevel;
+    wavefrontScene(&sceneData, RTProp, imageScratch, image, camData, scene, meshInfoData, vertexData, indexData,
+                   uvData, normalData, materials, imageArray, sampler, topLevel);
 
     unsigned int frameID = RTProp->totalSamples;
     for (unsigned int k = 0; k < RTProp->batchSize; ++k, ++frameID) {
         struct Payload payload;
-        uint3 seed = {frameID, RTProp->totalSamples, (uint)index};
-        cameraRay(camData, seed, &payload.nextRayOrigin, &payload.nextRayDirection);
-        payload.color = 0.0f;
-        payload.nextFactor = 1.0f;
-        payload.hit = false;
+        wavefrontPrimary(&payload, &sceneData, frameID, RTProp->totalSamples);
         sceneData.depth = 0;
         sceneData.frameID = frameID;
 
+        // bounce loop of samples/shader.cl:228-260 (a primary miss ends the path instead of re-tracing it)
         float3 color = 0.0f;
         float3 contribution = 1.0f;
         while (sceneData.depth < RTProp->depth) {
             traceRay(topLevel, 1, 3, payload.nextRayOrigin, payload.nextRayDirection,
                      0.001f, 1000.0f, &payload, &sceneData, imageArray, sampler);
-            if (!payload.hit) {
-                // the sky lights the path that escapes
+            if (payload.hit) {
                 color += contribution * payload.color;
+                contribution *= payload.nextFactor;
+            } else {
+                if (sceneData.depth == 0) color = payload.color;
                 break;
             }
-            color += contribution * payload.color;
-            contribution *= payload.nextFactor;
             sceneData.depth++;
             payload.hit = false;
+            if (RTProp->debug) break;
         }
         for (int c = 0; c < 3; ++c) {
             const float old = frameID == 0 ? 0.0f : imageScratch[4 * index + c];
             imageScratch[4 * index + c] = (frameID * old + color[c]) / (frameID + 1);
         }
     }
-    // Reinhard + gamma (shader2.cl:167-173)
-    for (int c = 0; c < 3; ++c) {
-        float v = imageScratch[4 * index + c];
-        v = v / (v + 1.0f);
-        v = pow(v, 0.4545f);
-        image[4 * index + c] = (uchar)(int)(v * 255.0f);
-    }
+    float3 shown = {imageScratch[4 * index], imageScratch[4 * index + 1], imageScratch[4 * index + 2]};
+    if (!RTProp->debug) shown = wavefrontTonemap(shown);
+    image[4 * index + 0] = (int)(shown.x * 255);
+    image[4 * index + 1] = (int)(shown.y * 255);
+    image[4 * index + 2] = (int)(shown.z * 255);
     image[4 * index + 3] = 255;
 }
 

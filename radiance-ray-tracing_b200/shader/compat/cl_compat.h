@@ -382,9 +382,13 @@ RD_F rd_uint4 convert_uint4(const rd_float4& a) { return rd_uint4((uint)a.x, (ui
 // Set by the launcher before each launch: first global id of this launch, total work-items,
 // and the image width used for the optional 8x4 pixel-tile remap (0 = identity mapping).
 extern "C" { __constant__ unsigned int rd_launch_info[4]; }
+// Wavefront stages (csrc/rd_wavefront.h) run a path on whatever thread its queue entry lands on; the
+// stage stores the path's work-item id here before calling user code and sets rd_launch_info[3].
+__shared__ unsigned int rd_wf_gid[256];
 RD_F size_t get_global_id(uint dim)
 {
     if (dim != 0) return 0;
+    if (rd_launch_info[3]) return rd_wf_gid[threadIdx.x];
     unsigned int t = rd_launch_info[0] + blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int w = rd_launch_info[2];
     if (w) {

@@ -170,3 +170,47 @@ def test_path_program_image_matches_reference(pkg, plt, ref):
     rd.TraceRays(plt, 0, 0, 0, w, h)
     s2 = ds.read_scratch()
     assert np.isfinite(s2).all() and not np.array_equal(s2, scratch)
+
+
+def test_wavefront_mode_matches_inline_and_reference(pkg, plt, ref):
+    """Wavefront mode (generate / trace / sort / shade / resolve stages over HBM queues) renders the same
+    image as the inline raygen kernel of the same program, with the hit-group sort on and off, and both
+    match the reference runtime on the host."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 200, 152
+    rt = scenes.rtprop(0, 3, 4, 0)
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, rt)
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    images = {}
+    try:
+        for mode, wf, srt in (("inline", 0, 1), ("sorted", 1, 1), ("unsorted", 1, 0)):
+            plt.set_option("wavefront", wf)
+            plt.set_option("wf_sort", srt)
+            ds.set_rtprop(0, 3, 4)
+            launches = plt.launch_count()
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+            images[mode] = (ds.read_image(), ds.read_scratch(), plt.launch_count() - launches)
+    finally:
+        plt.set_option("wavefront", 0)
+    assert images["inline"][2] <= 2 and images["sorted"][2] > images["unsorted"][2] > 3 * 4
+    # the order in which paths are shaded cannot change any path
+    assert np.array_equal(images["sorted"][1], images["unsorted"][1])
+    assert np.array_equal(images["sorted"][0], images["unsorted"][0])
+    d = images["sorted"][0][..., :3].astype(np.float64) - images["inline"][0][..., :3].astype(np.float64)
+    assert np.sqrt((d * d).mean()) <= 0.5, "wavefront vs inline RMSE %g" % np.sqrt((d * d).mean())
+    exp, _ = reference_image(ref, scenes, b, "path", w, h, rt)
+    d = images["sorted"][0][..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+    assert np.sqrt((d * d).mean()) <= PATH_RMSE_U8
+    # a program without the hooks refuses wavefront mode loudly
+    pipe2, _ = scenes.make_pipeline(plt, "primary")
+    rd.BindPipeline(plt, pipe2)
+    plt.set_option("wavefront", 1)
+    try:
+        with pytest.raises(rd.RadianceError, match="wavefront"):
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+    finally:
+        plt.set_option("wavefront", 0)

@@ -40,16 +40,27 @@ for program in sys.argv[5:] or ["path"]:
     plt.set_option("count_rays", 0)
     pipe, module = scenes.make_pipeline(plt, program)
     rd.BindPipeline(plt, pipe)
-    ms = []
-    for it in range(4):
-        with torch.cuda.stream(stream):
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(stream)
-            rd.TraceRaysAsync(plt, W, H)
-            e1.record(stream)
-        torch.cuda.synchronize()
-        ms.append(e0.elapsed_time(e1))
-    t = float(np.median(ms[1:]))
-    img = ds.read_image()
-    print("%s: %d spp depth %d: %.2f ms/frame, %d rays/frame (%.2f per sample), %.0f Mrays/s, regs %s, mean rgb %s" % (
-        program, spp, depth, t, rays, rays / (W * H * spp), rays / t / 1e3, module.info(), img[..., :3].mean(axis=(0, 1))), flush=True)
+    base_img = None
+    for mode, wf, srt in (("inline", 0, 0), ("wavefront+sort", 1, 1), ("wavefront", 1, 0)):
+        plt.set_option("wavefront", wf)
+        plt.set_option("wf_sort", srt)
+        ms = []
+        l0 = plt.launch_count()
+        for it in range(4):
+            ds.set_rtprop(0, spp, depth)
+            with torch.cuda.stream(stream):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                rd.TraceRaysAsync(plt, W, H)
+                e1.record(stream)
+            torch.cuda.synchronize()
+            ms.append(e0.elapsed_time(e1))
+        t = float(np.median(ms[1:]))
+        img = ds.read_image()
+        if base_img is None:
+            base_img = img
+        d = img[..., :3].astype(np.float64) - base_img[..., :3].astype(np.float64)
+        print("%s [%s]: %d spp depth %d: %.2f ms/frame, %d rays/frame (%.2f per sample), %.0f Mrays/s, launches/frame %d, regs %s, mean rgb %s, rmse vs inline %.3f" % (
+            program, mode, spp, depth, t, rays, rays / (W * H * spp), rays / t / 1e3, (plt.launch_count() - l0) // 4, module.info(),
+            img[..., :3].mean(axis=(0, 1)), np.sqrt((d * d).mean())), flush=True)
+    plt.set_option("wavefront", 0)
