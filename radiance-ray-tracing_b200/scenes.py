@@ -243,6 +243,40 @@ def blob_field_scene(n=2237, width=1920, height=1080, seed=1, sphere_subdiv=5):
     return b
 
 
+def groups_scene(n=2240, side=64, groups=64, width=1920, height=1080, seed=1):
+    """C4: the n x n height-field cut into side x side spatial patches, one instance per patch,
+    SBTOffset = hit group of the patch in a checkerboard (neighbouring patches never share a group),
+    customInstanceID = material = group. n=2240, side=64: 4096 instances, 10 035 200 triangles."""
+    assert n % side == 0 and groups <= 64
+    c = n // side
+    v, _ = heightfield(n, seed)
+    grid = v.reshape(n + 1, n + 1, 3)
+    # local index pattern of one (c+1) x (c+1) vertex patch, same winding as heightfield()
+    g = np.arange(c, dtype=np.uint32)
+    qx, qz = np.meshgrid(g, g, indexing="xy")
+    q = (qz * (c + 1) + qx).reshape(-1)
+    a, b, cc, d = q, q + 1, q + np.uint32(c + 1), q + np.uint32(c + 2)
+    tris = np.empty((2 * c * c, 3), np.uint32)
+    tris[0::2] = np.stack([a, cc, b], axis=-1)
+    tris[1::2] = np.stack([b, cc, d], axis=-1)
+    meshes, inst, mesh_mats = [], [], []
+    gs = int(np.sqrt(groups))
+    eye = np.eye(4, dtype=np.float32)
+    for pz in range(side):
+        for px in range(side):
+            pv = np.ascontiguousarray(grid[pz * c:(pz + 1) * c + 1, px * c:(px + 1) * c + 1].reshape(-1, 3))
+            k = ((px % gs) + gs * (pz % gs)) % groups
+            meshes.append((pv, tris))
+            inst.append((len(meshes) - 1, eye, k, k))
+            mesh_mats.append(k)
+    mats = [material((0.45 + 0.5 * ((k * 37) % 64) / 64.0, 0.45 + 0.5 * ((k * 11) % 64) / 64.0, 0.45 + 0.5 * ((k * 23) % 64) / 64.0),
+                     0.9 if k % 8 == 0 else 0.0, 0.3 + 0.5 * ((k * 5) % 16) / 16.0) for k in range(groups)]
+    bndl = SceneBundle(meshes, inst, mats, mesh_mats)
+    bndl.camera = camera(width, height, (0.0, 0.6, 0.9), (-0.6, 0.0, 0.0), 0.030, 0.036, 2.0, 0.0)
+    bndl.scene = scene_properties((-0.4, -1.0, -0.3), (6.0, 6.0, 6.0))
+    return bndl
+
+
 def pinhole_rays(cam, tmin=0.001, tmax=1000.0, stride=1, jitter=None):
     """Explicit primary-ray list for hit-ID parity tests (float32, host-generated once and shared
     by oracle and GPU): pinhole of samples/shader.cl:111-153 with a fixed sub-pixel offset."""

@@ -214,3 +214,33 @@ def test_wavefront_mode_matches_inline_and_reference(pkg, plt, ref):
             rd.TraceRays(plt, 0, 0, 0, w, h)
     finally:
         plt.set_option("wavefront", 0)
+
+
+def test_hit_group_dispatch_matches_reference(pkg, plt, ref):
+    """programs/groups.cl (config C4: 64 hit groups, instance SBTOffset selects rows 1+k / 65+k of the
+    131-row sbt.json): inline and wavefront (sorted / unsorted) images against the reference runtime."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = scenes.groups_scene(64, 8, 64, 192, 144)   # 64 instances, 8192 triangles, every group used once
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 192, 144
+    rt = scenes.rtprop(0, 2, 3, 0)
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, rt)
+    pipe, _ = scenes.make_pipeline(plt, "groups")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    out = {}
+    try:
+        for mode, wf, srt in (("inline", 0, 1), ("sorted", 1, 1), ("unsorted", 1, 0)):
+            plt.set_option("wavefront", wf)
+            plt.set_option("wf_sort", srt)
+            ds.set_rtprop(0, 2, 3)
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+            out[mode] = ds.read_image()
+    finally:
+        plt.set_option("wavefront", 0)
+    assert np.array_equal(out["sorted"], out["unsorted"])
+    exp, _ = reference_image(ref, scenes, b, "groups", w, h, rt)
+    assert len(np.unique(exp[..., :3].reshape(-1, 3), axis=0)) > 500   # the groups really shade differently
+    for mode in ("inline", "sorted"):
+        d = out[mode][..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+        assert np.sqrt((d * d).mean()) <= PATH_RMSE_U8, "%s RMSE %g" % (mode, np.sqrt((d * d).mean()))

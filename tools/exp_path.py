@@ -22,12 +22,13 @@ plt = rd.Platform.GetPlatform(0)
 stream = torch.cuda.ExternalStream(plt.stream(), device=0)
 t0 = time.perf_counter()
 bundle = {"cornell": lambda: scenes.cornell_like(), "hf": lambda: scenes.heightfield_scene(n_grid, W, H),
-          "c3": lambda: scenes.blob_field_scene(n_grid, W, H)}[scene]()
+          "c3": lambda: scenes.blob_field_scene(n_grid, W, H),
+          "c4": lambda: scenes.groups_scene(n_grid, int(os.environ.get("RD_EXP_SIDE", "64")), 64, W, H)}[scene]()
 print("scene %s host generation %.1f s, %d triangles" % (scene, time.perf_counter() - t0, bundle.triangle_count()), flush=True)
 t0 = time.perf_counter()
 tlas, blas = scenes.build_scene(plt, bundle)
 plt.sync()
-print("build+upload %.1f ms" % ((time.perf_counter() - t0) * 1e3), [b.stats() for b in blas], flush=True)
+print("build+upload %.1f ms" % ((time.perf_counter() - t0) * 1e3), [b.stats() for b in blas[:8]], len(blas), flush=True)
 ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, spp, depth, 0))
 for program in sys.argv[5:] or ["path"]:
     plt.set_option("count_rays", 1)
