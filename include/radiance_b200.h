@@ -83,6 +83,20 @@ int rd_blas_stats(rd_blas* b, uint64_t out[4]);
 /* RD::BuildAccelStruct(Platform*, std::vector<Instance>&), radiance/src/radiance.cpp:54-84 */
 int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, unsigned n, rd_handle* out);
 
+/* RD::FileToTopAccelStruct, radiance/src/radiance.cpp:450-479: reads a blob in the reference's byte layout
+ * (radiance.cpp:318-425, core.h:34-101), keeps its geometry and instance table and rebuilds the native
+ * structure on the GPU. A short or malformed file is RD_E_IO (the reference throws, radiance.cpp:458-459).
+ * _memory: same from a host buffer; blasOut/blasCount (optional) receive the bottom-level structures that were
+ * built (array allocated with malloc, release with rd_free_host; the structures with rd_blas_free). */
+int rd_tlas_load(rd_platform* p, const char* path, rd_handle* out);
+int rd_tlas_load_memory(rd_platform* p, const void* data, size_t size, rd_handle* out, rd_blas*** blasOut, unsigned* blasCount);
+/* RD::TopAccelStructToFile, radiance/src/radiance.cpp:428-448: writes the scene in the reference's blob format
+ * (binary BVH in DeviceBVHNode layout, leaves below 8 primitives), walkable by the reference's traceRay.
+ * _memory: into a malloc'ed buffer (release with rd_free_host). Fails with RD_E_ARG above 4 GiB (32-bit offsets). */
+int rd_tlas_save(rd_platform* p, rd_handle tlas, const char* path);
+int rd_tlas_save_memory(rd_platform* p, rd_handle tlas, void** dataOut, size_t* sizeOut);
+void rd_free_host(void* ptr);
+
 /* RD::CreateShaderModule, radiance/src/radiance.cpp:152-179: compiles an OpenCL-C user program
  * (samples/shader.cl conventions) with NVRTC for sm_100a; kernel "raygen" is extracted. `name` is
  * accepted and ignored like in the reference. */

@@ -278,7 +278,7 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
         float inv[16];
         if (!rd_inverse4x4(I.fwd, inv)) { rd_set_error("rd_tlas_build: instance %u transform is singular", i); return RD_E_ARG; }
         memcpy(I.inv, inv, 48);
-        I.sbtOffset = instances[i].SBTOffset; I.instanceID = i; I.customID = instances[i].customInstanceID; I.flags = 0;
+        I.sbtOffset = instances[i].SBTOffset; I.instanceID = i; I.customID = instances[i].customInstanceID; I.flags = b->triCount;   // flags = triangle records of the BLAS (rd_tlas_save)
         I.nodes = b->nodes; I.tris = b->tris;
         RdF4 bl, bh; bl.x = b->lo[0]; bl.y = b->lo[1]; bl.z = b->lo[2]; bl.w = 0; bh.x = b->hi[0]; bh.y = b->hi[1]; bh.z = b->hi[2]; bh.w = 0;
         rd_instance_world_box(I.fwd, bl, bh, &lo[i], &hi[i]);

@@ -26,6 +26,7 @@ ABI_SYMBOLS = [
     "rd_shader_module_create", "rd_module_free", "rd_shader_compile_check", "rd_module_info", "rd_sbt_load_json",
     "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
+    "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
 ]
 
 
@@ -72,7 +73,10 @@ def lib():
             "rd_trace_ray_list": [vp, vp, vp, vp, vp, vp, sz, u], "rd_trace_counters": [vp, C.POINTER(C.c_uint64)],
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
             "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
+            "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
+            "rd_tlas_save": [vp, vp, C.c_char_p], "rd_tlas_save_memory": [vp, vp, C.POINTER(vp), C.POINTER(sz)],
         }
+        L.rd_free_host.argtypes, L.rd_free_host.restype = [vp], None
         for name, args in sigs.items():
             f = getattr(L, name)
             f.argtypes, f.restype = args, C.c_int
@@ -180,6 +184,33 @@ def BuildAccelStruct(plt, arg):
     out = C.c_void_p()
     _check(lib().rd_tlas_build(plt.handle, arr, len(instances), C.byref(out)))
     return Handle(plt, out, keep=[i.bottomAccelStruct for i in instances])
+
+
+def TopAccelStructToFile(plt, accelStruct, path):
+    """RD::TopAccelStructToFile (radiance.cpp:428-448): reference blob format."""
+    _check(lib().rd_tlas_save(plt.handle, accelStruct.handle, str(path).encode()))
+
+
+def FileToTopAccelStruct(plt, path):
+    """RD::FileToTopAccelStruct (radiance.cpp:450-479); returns the handle (the reference fills an out-parameter)."""
+    out = C.c_void_p()
+    _check(lib().rd_tlas_load(plt.handle, str(path).encode(), C.byref(out)))
+    return Handle(plt, out)
+
+
+def TopAccelStructToBytes(plt, accelStruct):
+    data, size = C.c_void_p(), C.c_size_t(0)
+    _check(lib().rd_tlas_save_memory(plt.handle, accelStruct.handle, C.byref(data), C.byref(size)))
+    blob = np.ctypeslib.as_array(C.cast(data, C.POINTER(C.c_ubyte)), (size.value,)).copy()
+    lib().rd_free_host(data)
+    return blob
+
+
+def TopAccelStructFromBytes(plt, blob):
+    blob = np.ascontiguousarray(blob, np.uint8)
+    out = C.c_void_p()
+    _check(lib().rd_tlas_load_memory(plt.handle, blob.ctypes.data, blob.nbytes, C.byref(out), None, None))
+    return Handle(plt, out)
 
 
 def CreateBuffer(plt, size):

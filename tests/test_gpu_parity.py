@@ -244,3 +244,50 @@ def test_hit_group_dispatch_matches_reference(pkg, plt, ref):
     for mode in ("inline", "sorted"):
         d = out[mode][..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
         assert np.sqrt((d * d).mean()) <= PATH_RMSE_U8, "%s RMSE %g" % (mode, np.sqrt((d * d).mean()))
+
+
+def test_reference_blob_import(pkg, plt, ref):
+    """RD::FileToTopAccelStruct: the blob the reference's own builder + packers produce (oracle/_ref) loads
+    into the native structure and traces to the same hits as the reference walking that blob."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tl = scenes.build_reference_scene(ref, b)
+    rays = scenes.pinhole_rays(b.camera, stride=3, jitter=(0.41, 0.27))
+    exp = tl.trace(rays)
+    tlas = rd.TopAccelStructFromBytes(plt, tl.blob)
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    assert compare_hits(hitA, hitB, exp) > 20000
+    # truncated and foreign files are refused (the reference throws on a short read, radiance.cpp:458-459)
+    with pytest.raises(rd.RadianceError):
+        rd.TopAccelStructFromBytes(plt, tl.blob[: len(tl.blob) // 2])
+    with pytest.raises(rd.RadianceError):
+        rd.TopAccelStructFromBytes(plt, np.zeros(64, np.uint8))
+
+
+def test_reference_blob_export_round_trip(pkg, plt, ref, tmp_path):
+    """RD::TopAccelStructToFile: the exported file is a valid reference blob -- the plain-C port of the
+    reference's traceRay (oracle/rd_oracle.c, pinned to the reference bit for bit) walks it to the hits the
+    GPU finds, and loading it back gives the same hits again."""
+    import importlib.util
+    import os
+    rd, scenes = pkg.rd, pkg.scenes
+    spec = importlib.util.spec_from_file_location("rd_oracle_portpy", os.path.join(os.path.dirname(__file__), "..", "oracle", "portpy.py"))
+    port = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(port)
+    if not port.available():
+        pytest.skip("oracle port not built")
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    rays = scenes.pinhole_rays(b.camera, stride=3, jitter=(0.41, 0.27))
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    path = str(tmp_path / "scene.cache")
+    rd.TopAccelStructToFile(plt, tlas, path)
+    blob = np.fromfile(path, np.uint8)
+    assert np.array_equal(blob, rd.TopAccelStructToBytes(plt, tlas))
+    out = port.trace(blob, rays)
+    assert compare_hits(hitA, hitB, out) > 20000
+    hit = out["hit"] == 1
+    assert np.array_equal(out["custom"][hit], np.array([i[3] for i in b.instances], np.uint32)[out["inst"][hit]])
+    back = rd.FileToTopAccelStruct(plt, path)
+    hitA2, hitB2 = rd.trace_host_rays(plt, back, rays)
+    assert np.array_equal(hitA2["prim"], hitA["prim"]) and np.array_equal(hitB2, hitB) and np.array_equal(hitA2["t"], hitA["t"])
