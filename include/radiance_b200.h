@@ -127,6 +127,21 @@ int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height);
 int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
                         unsigned long long count);
 
+/* Multi-GPU dynamic tile stealing (one process per GPU, scene replicated): persistent raygen blocks take chunks
+ * of `chunkItems` consecutive work-items (runs of 8x4 screen tiles) from one counter shared by all GPUs of the
+ * job -- it lives on the exporting rank's GPU, the other ranks map it through CUDA IPC and increment it with
+ * system-scope atomics over NVLink. Modules must be created under option "stealing" = 1. No reference
+ * counterpart (the reference is single-device, radiance/src/clcontext.cpp:12-40).
+ *   rank 0: rd_steal_counter_export -> 64-byte handle, sent to the other ranks (any transport)
+ *   others: rd_steal_counter_import
+ *   every rank, every frame: rd_trace_rays_steal(width, height, frame, chunkItems) with the same arguments;
+ *   each work-item is rendered by exactly one rank, pixels of the other ranks are left untouched.
+ * rd_steal_owned: the chunk ids this rank rendered in its last frame. */
+int rd_steal_counter_export(rd_platform* p, unsigned char handle[64]);
+int rd_steal_counter_import(rd_platform* p, const unsigned char handle[64]);
+int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned height, unsigned frame, unsigned chunkItems);
+int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, unsigned* count);
+
 /* Explicit ray list through the traversal kernel (wavefront building block; used for hit-ID parity
  * against the reference's traceRay, radiance/shader/radiance.cl:254-275).
  *   rayA[i] = {o.xyz, tmin}, rayB[i] = {d.xyz, tmax}; hitA[i] = {t, b1, b2, primID bits}, hitB[i] = instanceID.
@@ -155,6 +170,7 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wavefront" (0/1: rd_trace_rays runs the sample / bounce loop of samples/shader.cl:196-281 as stage launches
  * over ray queues in HBM -- generate, trace, sort by hit group, shade, resolve -- instead of one raygen
  * launch; needs the wavefrontScene / wavefrontPrimary hooks in the program),
+ * "stealing" (0/1: modules created afterwards also carry the persistent chunk-stealing raygen),
  * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow

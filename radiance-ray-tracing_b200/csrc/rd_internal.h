@@ -38,6 +38,7 @@ struct rd_blas {
 
 struct rd_module {
     CUmodule mod; CUfunction raygen;
+    CUfunction stealRaygen;                      // persistent raygen with chunk stealing (option "stealing")
     CUfunction wfGenerate, wfShade, wfResolve;   // 0 when the program has no wavefront hooks
     unsigned wfPayloadSize; float wfRay[4];      // sizeof(struct Payload); sbtRecordOffset, missIndex, Tmin, Tmax
     int numRegs; int localBytes;
@@ -60,7 +61,8 @@ struct rd_platform {
     std::vector<int> boundKinds;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal;
+    unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
     uint64_t launches;
     int smCount;

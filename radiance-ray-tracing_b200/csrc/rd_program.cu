@@ -384,6 +384,41 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
     return s;
 }
 
+
+// Persistent raygen for multi-GPU tile stealing: blocks take chunks of consecutive work-items (runs of 8x4
+// screen tiles) from one counter that every GPU of the job increments with system-scope atomics (the counter
+// lives on one GPU, the others reach it through a CUDA IPC mapping over NVLink), and run the user's raygen
+// body -- a device-function copy of it in namespace rd_ls -- for each work-item of the chunk.
+static std::string generate_steal_kernel(const std::vector<RaygenParam>& P)
+{
+    std::string plist, names;
+    for (size_t i = 0; i < P.size(); ++i) { plist += P[i].type + " " + P[i].name + ", "; names += (i ? ", " : "") + P[i].name; }
+    std::string s = "\n// ---- persistent raygen with chunk stealing, generated by the runtime ----\n"
+        "struct RdStealArgs { unsigned int* counter; unsigned int* owned; unsigned int numChunks, chunkItems, first, count, tileW, pad; };\n"
+        "namespace rd_ls {\n"
+        "extern \"C\" __global__ void rd_raygen_steal(" + plist + "RdStealArgs a)\n{\n"
+        "    __shared__ unsigned int chunkShared;\n"
+        "    for (;;) {\n"
+        "        if (threadIdx.x == 0) {\n"
+        "            chunkShared = atomicAdd_system(a.counter, 1u);\n"
+        "            if (chunkShared < a.numChunks && a.owned) a.owned[1u + atomicAdd(a.owned, 1u)] = chunkShared;\n"
+        "        }\n"
+        "        __syncthreads();\n"
+        "        const unsigned int chunk = chunkShared;\n"
+        "        __syncthreads();\n"
+        "        if (chunk >= a.numChunks) break;\n"
+        "        for (unsigned int w = threadIdx.x; w < a.chunkItems; w += blockDim.x) {\n"
+        "            const unsigned int t = chunk * a.chunkItems + w;\n"
+        "            if (t < a.count) {\n"
+        "                rd_wf_gid[threadIdx.x] = rd_wf_global_id(a.first + t, a.tileW);\n"
+        "                raygen(" + names + ");\n"
+        "            }\n"
+        "        }\n"
+        "    }\n"
+        "}\n}  // namespace rd_ls\n";
+    return s;
+}
+
 extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 {
     if (!p || !json_text) { rd_set_error("rd_sbt_load_json: null argument"); return RD_E_ARG; }
@@ -396,7 +431,7 @@ extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 // ---- NVRTC ------------------------------------------------------------------------------------
 // OpenCL-C user program (+ optional sbt.json) -> sm_100a cubin. Needs no device.
 static int rd_compile_program(const char* code, unsigned size, const std::string& sbtJson, bool fmad,
-                              std::vector<char>* cubin, std::string* log, bool countRays = false, int maxDepth = 2)
+                              std::vector<char>* cubin, std::string* log, bool countRays = false, int maxDepth = 2, bool steal = false)
 {
     std::string src(code, size ? size : strlen(code));
     while (!src.empty() && src.back() == '\0') src.pop_back();
@@ -442,6 +477,14 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
         std::vector<RaygenParam> params;
         if (parse_raygen_params(bare, &params))
             mainSrc += generate_wavefront_kernels(params, bare.find("wavefrontTonemap") != std::string::npos);
+    }
+    if (steal) {
+        std::vector<RaygenParam> params;
+        if (parse_raygen_params(bare, &params)) {
+            mainSrc += "#undef RD_LEVEL\n#define RD_LEVEL 0\n#undef RD_LEVEL_PART_DONE\n#undef RD_NEXT_NS\n#define RD_NEXT_NS rd_l1\n#undef RD_LAST_LEVEL\n"
+                       "#include \"rd_wavefront.h\"\nnamespace rd_ls {\n#include \"rd_user_program.cl\"\n}\n";
+            mainSrc += generate_steal_kernel(params);
+        }
     }
     std::vector<const char*> hdrNames(rd_embedded_names, rd_embedded_names + rd_embedded_count);
     std::vector<const char*> hdrSources(rd_embedded_sources, rd_embedded_sources + rd_embedded_count);
@@ -490,7 +533,7 @@ extern "C" int rd_shader_compile_check(const char* code, unsigned size, const ch
 {
     if (!code) { rd_set_error("rd_shader_compile_check: null argument"); return RD_E_ARG; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, sbt_json ? sbt_json : "", fmad != 0, &cubin, &log);
+    int rc = rd_compile_program(code, size, sbt_json ? sbt_json : "", fmad != 0, &cubin, &log, false, 2, getenv("RD_CHECK_STEAL") != 0);
     if (rc) return rc;
     if (cubinSize) *cubinSize = cubin.size();
     rd_set_error("%.15000s", log.c_str());   // ptxas -v statistics of a successful build
@@ -504,7 +547,7 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     RD_CUDA(cudaSetDevice(p->device));
     { int drc = rd_driver_init(); if (drc) return drc; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth);
+    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth, p->optSteal != 0);
     if (rc) return rc;
     rd_module* m = new rd_module();
     m->ptxInfo = log;
@@ -512,6 +555,8 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     if (cr != CUDA_SUCCESS) { const char* s = 0; cuGetErrorString(cr, &s); rd_set_error("cuModuleLoadData: %s", s ? s : "?"); delete m; return RD_E_CUDA; }
     cr = cuModuleGetFunction(&m->raygen, m->mod, "raygen");   // the reference always extracts "raygen" (radiance.cpp:177)
     if (cr != CUDA_SUCCESS) { rd_set_error("program has no __kernel named raygen"); cuModuleUnload(m->mod); delete m; return RD_E_COMPILE; }
+    m->stealRaygen = 0;
+    if (p->optSteal && cuModuleGetFunction(&m->stealRaygen, m->mod, "rd_raygen_steal") != CUDA_SUCCESS) m->stealRaygen = 0;
     // wavefront stages exist when the program defines the hooks (generate_wavefront_kernels)
     m->wfGenerate = m->wfShade = m->wfResolve = 0; m->wfPayloadSize = 0;
     if (cuModuleGetFunction(&m->wfGenerate, m->mod, "rd_wf_generate") == CUDA_SUCCESS &&
@@ -670,6 +715,100 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
         RD_CU(cuLaunchKernel(m->raygen, 1, 1, 1, tail, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
+    return RD_OK;
+}
+
+
+// ---- multi-GPU chunk stealing -------------------------------------------------------------------
+// One array of frame counters lives on the GPU of the exporting rank; the other ranks (one process per GPU)
+// map it with CUDA IPC and increment it with system-scope atomics from their persistent raygen blocks.
+// Frame f uses counter f % slots, the owner clears the slot half a ring ahead, so frames need no reset
+// round trip; the per-frame collective of the caller keeps the ranks within a frame of each other.
+#define RD_STEAL_SLOTS 1024u
+struct RdStealArgsHost { unsigned* counter; unsigned* owned; unsigned numChunks, chunkItems, first, count, tileW, pad; };
+
+extern "C" int rd_steal_counter_export(rd_platform* p, unsigned char handle[64])
+{
+    if (!p || !handle) { rd_set_error("rd_steal_counter_export: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    if (!p->stealCounters) {
+        RD_CUDA(cudaMalloc(&p->stealCounters, RD_STEAL_SLOTS * sizeof(unsigned)));
+        RD_CUDA(cudaMemset(p->stealCounters, 0, RD_STEAL_SLOTS * sizeof(unsigned)));
+        p->stealSlots = RD_STEAL_SLOTS; p->stealImported = 0;
+    }
+    cudaIpcMemHandle_t h;
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    RD_CUDA(cudaIpcGetMemHandle(&h, p->stealCounters));
+    memcpy(handle, &h, 64);
+    return RD_OK;
+}
+
+extern "C" int rd_steal_counter_import(rd_platform* p, const unsigned char handle[64])
+{
+    if (!p || !handle) { rd_set_error("rd_steal_counter_import: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    cudaIpcMemHandle_t h; memcpy(&h, handle, 64);
+    void* ptr = 0;
+    RD_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+    p->stealCounters = (unsigned*)ptr; p->stealSlots = RD_STEAL_SLOTS; p->stealImported = 1;
+    return RD_OK;
+}
+
+// RD::TraceRays with chunk stealing: every rank calls it with the same width, height, frame and chunkItems;
+// each work-item of the NDRange is rendered by exactly one rank. Asynchronous on the platform stream.
+extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned height, unsigned frame, unsigned chunkItems)
+{
+    if (!p || !p->boundModule) { rd_set_error("rd_trace_rays_steal: no pipeline bound"); return RD_E_STATE; }
+    rd_module* m = p->boundModule;
+    if (!m->stealRaygen) { rd_set_error("rd_trace_rays_steal: module was not created under option stealing"); return RD_E_STATE; }
+    RD_CUDA(cudaSetDevice(p->device));
+    if (!p->stealCounters) {   // single process: a private counter
+        unsigned char tmp[64];
+        int rc = rd_steal_counter_export(p, tmp);
+        if (rc) return rc;
+    }
+    const unsigned long long total = (unsigned long long)width * height;
+    if (!total || !chunkItems || total > 0xffffffffull) { rd_set_error("rd_trace_rays_steal: bad size"); return RD_E_ARG; }
+    const unsigned numChunks = (unsigned)((total + chunkItems - 1) / chunkItems);
+    if (p->stealOwnedCap < numChunks + 1) {
+        if (p->stealOwned) cudaFree(p->stealOwned);
+        RD_CUDA(cudaMalloc(&p->stealOwned, ((size_t)numChunks + 1) * sizeof(unsigned)));
+        p->stealOwnedCap = numChunks + 1;
+    }
+    RD_CUDA(cudaMemsetAsync(p->stealOwned, 0, sizeof(unsigned), p->stream));
+    if (!p->stealImported)   // the owner clears the slot that comes into use half a ring from now
+        RD_CUDA(cudaMemsetAsync(p->stealCounters + ((frame + p->stealSlots / 2) % p->stealSlots), 0, sizeof(unsigned), p->stream));
+    CUdeviceptr dinfo; size_t infoBytes = 0;
+    RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
+    const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
+    const unsigned info[4] = {0u, (unsigned)total, tileW, 1u};
+    RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
+    RdStealArgsHost a;
+    a.counter = p->stealCounters + (frame % p->stealSlots); a.owned = p->stealOwned;
+    a.numChunks = numChunks; a.chunkItems = chunkItems; a.first = 0; a.count = (unsigned)total; a.tileW = tileW; a.pad = 0;
+    std::vector<void*> argv(p->boundArgs.size() + 1);
+    for (size_t i = 0; i < p->boundArgs.size(); ++i) argv[i] = &p->boundArgs[i];
+    argv[p->boundArgs.size()] = &a;
+    const unsigned block = (unsigned)p->optBlock;
+    unsigned blocks = (unsigned)p->smCount * 8u;
+    if (blocks > numChunks) blocks = numChunks;
+    RD_CU(cuLaunchKernel(m->stealRaygen, blocks, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+    p->launches += 1;
+    return RD_OK;
+}
+
+// chunks this rank rendered in the last rd_trace_rays_steal (synchronises the stream); returns the count and
+// copies up to `capacity` chunk ids
+extern "C" int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, unsigned* count)
+{
+    if (!p || !count) { rd_set_error("rd_steal_owned: null argument"); return RD_E_ARG; }
+    *count = 0;
+    if (!p->stealOwned) return RD_OK;
+    RD_CUDA(cudaSetDevice(p->device));
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    RD_CUDA(cudaMemcpy(count, p->stealOwned, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    const unsigned n = *count < capacity ? *count : capacity;
+    if (ids && n) RD_CUDA(cudaMemcpy(ids, p->stealOwned + 1, (size_t)n * sizeof(unsigned), cudaMemcpyDeviceToHost));
     return RD_OK;
 }
 

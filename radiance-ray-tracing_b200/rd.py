@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
+    "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned",
 ]
 
 
@@ -74,6 +75,8 @@ def lib():
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
             "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
+            "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
+            "rd_steal_owned": [vp, vp, u, C.POINTER(u)],
             "rd_tlas_save": [vp, vp, C.c_char_p], "rd_tlas_save_memory": [vp, vp, C.POINTER(vp), C.POINTER(sz)],
         }
         L.rd_free_host.argtypes, L.rd_free_host.restype = [vp], None
@@ -184,6 +187,28 @@ def BuildAccelStruct(plt, arg):
     out = C.c_void_p()
     _check(lib().rd_tlas_build(plt.handle, arr, len(instances), C.byref(out)))
     return Handle(plt, out, keep=[i.bottomAccelStruct for i in instances])
+
+
+def StealCounterExport(plt):
+    """64-byte IPC handle of this rank's chunk counter (rank 0 of a multi-GPU job)."""
+    h = np.zeros(64, np.uint8)
+    _check(lib().rd_steal_counter_export(plt.handle, h.ctypes.data))
+    return h
+
+
+def StealCounterImport(plt, handle):
+    h = np.ascontiguousarray(handle, np.uint8)
+    _check(lib().rd_steal_counter_import(plt.handle, h.ctypes.data))
+
+
+def TraceRaysSteal(plt, width, height, frame, chunk_items=1024):
+    _check(lib().rd_trace_rays_steal(plt.handle, width, height, frame, chunk_items))
+
+
+def StealOwned(plt, capacity=1 << 20):
+    ids, n = np.zeros(capacity, np.uint32), C.c_uint(0)
+    _check(lib().rd_steal_owned(plt.handle, ids.ctypes.data, capacity, C.byref(n)))
+    return ids[:min(capacity, n.value)].copy()
 
 
 def TopAccelStructToFile(plt, accelStruct, path):

@@ -291,3 +291,28 @@ def test_reference_blob_export_round_trip(pkg, plt, ref, tmp_path):
     back = rd.FileToTopAccelStruct(plt, path)
     hitA2, hitB2 = rd.trace_host_rays(plt, back, rays)
     assert np.array_equal(hitA2["prim"], hitA["prim"]) and np.array_equal(hitB2, hitB) and np.array_equal(hitA2["t"], hitA["t"])
+
+
+def test_chunk_stealing_renders_every_pixel_once(pkg, plt):
+    """Persistent raygen with chunk stealing (multi-GPU partition, here with a private counter): same image as
+    the plain launch, and the chunks it claimed are exactly all chunks, each once."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 320, 240
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 2, 3, 0))
+    plt.set_option("stealing", 1)
+    try:
+        pipe, _ = scenes.make_pipeline(plt, "path")
+    finally:
+        plt.set_option("stealing", 0)
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    plain = ds.read_image()
+    rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
+    for frame in (0, 1, 700):
+        rd.TraceRaysSteal(plt, w, h, frame, 512)
+        owned = rd.StealOwned(plt)
+        assert np.array_equal(np.sort(owned), np.arange(w * h // 512))
+    assert np.array_equal(ds.read_image(), plain)
