@@ -119,13 +119,6 @@ def reference_arm(args, rank, world):
                       "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
-def tile_row_range(rank, world):
-    """Contiguous run of 8x4-tile rows owned by `rank`: (first work-item, count, first pixel row, rows)."""
-    tile_rows = HEIGHT // 4
-    r0, r1 = tile_rows * rank // world, tile_rows * (rank + 1) // world
-    return r0 * 4 * WIDTH, (r1 - r0) * 4 * WIDTH, r0 * 4, (r1 - r0) * 4
-
-
 def cpu_baseline_leg(pkg, ref, bundle):
     """Reference CPU path on a bounded sample (rank 0, N=1 only): see reference_arm for the sample."""
     scenes = pkg.scenes
@@ -151,6 +144,59 @@ def cpu_baseline_leg(pkg, ref, bundle):
                       % (rows, HEIGHT, count, build_s)}
 
 
+def time_frames(torch, plt, rd, stream, flush, w, h, reps=3):
+    """Median device time (ms) of rd_trace_rays over `reps` frames after one warm-up, L2 flushed before each."""
+    ms = []
+    for it in range(reps + 1):
+        with torch.cuda.stream(stream):
+            flush.fill_(it)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            rd.TraceRaysAsync(plt, w, h)
+            e1.record(stream)
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    return float(np.median(ms[1:]))
+
+
+def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, depth, modes):
+    """Path-tracing configs (BASELINE configs[2], configs[3]) through RD::TraceRays: rays per frame counted by a
+    count_rays build of the same program, then each mode timed. Returns a dict for the JSON line."""
+    rd, scenes = pkg.rd, pkg.scenes
+    t0 = time.perf_counter()
+    tlas, blas = scenes.build_scene(plt, bundle)
+    plt.sync()
+    build_ms = (time.perf_counter() - t0) * 1e3
+    ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, spp, depth, 0))
+    plt.set_option("count_rays", 1)
+    try:
+        pipe, _ = scenes.make_pipeline(plt, program)
+    finally:
+        plt.set_option("count_rays", 0)
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    plt.ray_count()
+    rd.TraceRays(plt, 0, 0, 0, WIDTH, HEIGHT)
+    rays = plt.ray_count()
+    pipe, module = scenes.make_pipeline(plt, program)
+    rd.BindPipeline(plt, pipe)
+    out = {"workload": name, "triangles": bundle.triangle_count(), "instances": len(bundle.instances), "spp": spp, "depth": depth,
+           "rays_per_frame": rays, "build_ms_incl_upload": build_ms, "unit": "Mrays/s"}
+    try:
+        for mode, wf, srt in modes:
+            plt.set_option("wavefront", wf)
+            plt.set_option("wf_sort", srt)
+            l0 = plt.launch_count()
+            ms = time_frames(torch, plt, rd, stream, flush, WIDTH, HEIGHT)
+            out[mode] = {"value": rays / ms / 1e3, "ms_per_frame": ms, "launches_per_frame": (plt.launch_count() - l0) // 4}
+    finally:
+        plt.set_option("wavefront", 0)
+        plt.set_option("wf_sort", 1)
+    for h in [tlas] + list(blas):
+        h.free()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -158,6 +204,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partition", default="interleave", choices=["interleave", "steal", "static"],
+                    help="N>1: interleaved tile-row bands + sum-reduce (default), dynamic chunk stealing + sum-reduce, "
+                         "or contiguous tile rows + send/recv gather")
+    ap.add_argument("--band", type=int, default=1, help="tile rows per band of the interleaved partition")
+    ap.add_argument("--chunk", type=int, default=32, help="work-items per stolen chunk (multiple of 32)")
+    ap.add_argument("--extra", default="c3", choices=["c3", "all"], help="extra configs measured at N=1: C3, or C3 and C4")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C4 wavefront measurements (N=1 only)")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -172,8 +225,12 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     pkg = entry.load_package()
-    rd, scenes = pkg.rd, pkg.scenes
+    rd, scenes, mg = pkg.rd, pkg.scenes, pkg.multigpu
     plt = rd.Platform.GetPlatform(local)
+    steal = world > 1 and args.partition == "steal"
+    interleave = world > 1 and args.partition == "interleave"
+    if steal:
+        plt.set_option("stealing", 1)
     stream = torch.cuda.ExternalStream(plt.stream(), device=local)
 
     bundle = scenes.heightfield_scene(GRID_N, WIDTH, HEIGHT)
@@ -189,30 +246,39 @@ def main():
     pipe, module = scenes.make_pipeline(plt, "primary")
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
-    first, count, row0, rows = tile_row_range(rank, world)
+    first, count, row0, rows = mg.tile_row_range(rank, world, WIDTH, HEIGHT)
+    if steal:
+        mg.exchange_steal_handle(rd, plt, rank, world, dist, "cuda")
+        first, count = 0, n
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+    frame_no = [0]
 
-    def gather():
-        if world == 1:
-            return
-        ops = []
-        if rank == 0:
-            for r in range(1, world):
-                _, _, y0, ny = tile_row_range(r, world)
-                ops.append(dist.P2POp(dist.irecv, image_t[y0 * WIDTH * 4:(y0 + ny) * WIDTH * 4], r))
+    def render_and_gather():
+        """One frame of this rank's share + the frame's only collective; returns the event between them."""
+        e1 = torch.cuda.Event(enable_timing=True)
+        if steal:
+            image_t.zero_()
+            rd.TraceRaysSteal(plt, WIDTH, HEIGHT, frame_no[0], args.chunk)
+            frame_no[0] += 1
+            e1.record(stream)
+            mg.combine_sum(image_t, world, dist)
+        elif interleave:
+            image_t.zero_()
+            rd.TraceRaysInterleaved(plt, WIDTH, HEIGHT, rank, world, args.band)
+            e1.record(stream)
+            mg.combine_sum(image_t, world, dist)
         else:
-            ops.append(dist.P2POp(dist.isend, image_t[row0 * WIDTH * 4:(row0 + rows) * WIDTH * 4], 0))
-        for w in dist.batch_isend_irecv(ops):
-            w.wait()
+            rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
+            e1.record(stream)
+            mg.gather_rows(image_t, rank, world, WIDTH, HEIGHT, dist)
+        return e1
 
     def step(timed):
         with torch.cuda.stream(stream):
             flush.fill_(rank + 1)                       # evict the scene from L2 between frames
-            e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            e0, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
             e0.record(stream)
-            rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
-            e1.record(stream)
-            gather()
+            e1 = render_and_gather()
             e2.record(stream)
         return e0, e1, e2
 
@@ -248,9 +314,8 @@ def main():
 
     def e2e_step():
         rd.WriteBuffer(plt, ds.rdRTProp, 16, host_rt.data_ptr())
-        rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
         with torch.cuda.stream(stream):
-            gather()
+            render_and_gather()
         if rank == 0:
             rd.ReadBuffer(plt, ds.rdImage, n * 4 if world > 1 else count * 4, host_full.data_ptr(), 0)
         else:
@@ -280,14 +345,17 @@ def main():
         nodes_per_ray, tris_per_ray = c["nodes"] / c["rays"], c["tris"] / c["rays"]
         bytes_per_ray = nodes_per_ray * NODE_BYTES + tris_per_ray * TRI_BYTES + RAY_BYTES + HIT_BYTES
         peak, peak_kind = measured_peaks()
-        rays_per_launch = count
+        rays_per_launch = n // world if (steal or interleave) else count
         achieved = rays_per_launch * bytes_per_ray / (kern_ms * 1e-3) / 1e9
         out = {
             "metric": "Mrays/s (primary closest-hit, 1080p)", "value": n / (frame_ms * 1e-3) / 1e6, "unit": "Mrays/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": frame_ms,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "l2": "256 MiB flush between timed frames", "rays_per_step": n,
-                       "partition": "contiguous 8x4-tile rows per GPU, NCCL send/recv gather to rank 0" if world > 1 else "single GPU",
+                       "partition": ("single GPU" if world == 1 else
+                                     "interleaved bands of %d 8x4-tile row(s), round robin over ranks + NCCL sum-reduce to rank 0" % args.band if interleave else
+                                     "dynamic stealing of 8x4-tile chunks (IPC counter, system-scope atomics) + NCCL sum-reduce to rank 0" if steal
+                                     else "contiguous 8x4-tile rows per GPU, NCCL send/recv gather to rank 0"),
                        "build_ms_incl_upload": build_ms, "bvh": blas[0].stats(), "raygen": module.info()},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 16,
@@ -297,6 +365,21 @@ def main():
                          "kernel_ms": kern_ms, "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray,
                          "tris_per_ray": tris_per_ray},
         }
+        if world == 1 and not args.no_extra:
+            # the path-tracing half of the metric ("primary + 4-bounce path"): BASELINE configs[2] (and configs[3]
+            # with --extra all), wavefront mode against the inline raygen kernel of the same program
+            modes = (("inline", 0, 1), ("wavefront_sorted", 1, 1), ("wavefront_unsorted", 1, 0))
+            out["extra"] = {}
+            try:
+                out["extra"]["C3"] = extra_config(torch, pkg, plt, stream, flush,
+                    "C3: 4-bounce path tracing (depth 5) with any-hit shadow rays, 1080p 16 spp, blob-field n=2237, programs/path.cl",
+                    scenes.blob_field_scene(2237, WIDTH, HEIGHT), "path", 16, 5, modes)
+                if args.extra == "all":
+                    out["extra"]["C4"] = extra_config(torch, pkg, plt, stream, flush,
+                        "C4: 64 SBT hit groups, 4096 instances, n=2240 height-field, 1080p 16 spp depth 5, programs/groups.cl",
+                        scenes.groups_scene(2240, 64, 64, WIDTH, HEIGHT), "groups", 16, 5, modes)
+            except Exception as e:   # the headline line must survive a failure here
+                out["extra"]["error"] = repr(e)[:300]
         if world == 1 and not args.no_cpu_baseline:
             ref = entry.load_oracle()
             if ref.available():

@@ -127,6 +127,12 @@ int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height);
 int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
                         unsigned long long count);
 
+/* Multi-GPU static partition with interleaved bands: the frame's rows of 8x4 tiles are dealt to the ranks in
+ * bands of bandTileRows rows, round robin; one launch renders every band of `rank` (the expensive screen
+ * regions -- e.g. the horizon of a height-field -- are spread over all GPUs). No reference counterpart. */
+int rd_trace_rays_interleaved(rd_platform* p, unsigned width, unsigned height, unsigned rank, unsigned world,
+                              unsigned bandTileRows);
+
 /* Multi-GPU dynamic tile stealing (one process per GPU, scene replicated): persistent raygen blocks take chunks
  * of `chunkItems` consecutive work-items (runs of 8x4 screen tiles) from one counter shared by all GPUs of the
  * job -- it lives on the exporting rank's GPU, the other ranks map it through CUDA IPC and increment it with
@@ -134,7 +140,8 @@ int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned height, unsigne
  * counterpart (the reference is single-device, radiance/src/clcontext.cpp:12-40).
  *   rank 0: rd_steal_counter_export -> 64-byte handle, sent to the other ranks (any transport)
  *   others: rd_steal_counter_import
- *   every rank, every frame: rd_trace_rays_steal(width, height, frame, chunkItems) with the same arguments;
+ *   every rank, every frame: rd_trace_rays_steal(width, height, frame, chunkItems) with the same arguments,
+ *   frame = 0, 1, 2, ... (it selects the counter slot; a slot is reusable after 512 further frames);
  *   each work-item is rendered by exactly one rank, pixels of the other ranks are left untouched.
  * rd_steal_owned: the chunk ids this rank rendered in its last frame. */
 int rd_steal_counter_export(rd_platform* p, unsigned char handle[64]);

@@ -35,6 +35,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->device = device;
     p->boundModule = 0;
     p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0;
+    p->ilWorld = p->ilRank = p->ilBandRows = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
     p->launches = 0;

@@ -62,6 +62,7 @@ struct rd_platform {
     rd_module* boundModule;
     std::string sbtJson;
     long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal;
+    unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
     uint64_t launches;

@@ -397,23 +397,29 @@ static std::string generate_steal_kernel(const std::vector<RaygenParam>& P)
         "struct RdStealArgs { unsigned int* counter; unsigned int* owned; unsigned int numChunks, chunkItems, first, count, tileW, pad; };\n"
         "namespace rd_ls {\n"
         "extern \"C\" __global__ void rd_raygen_steal(" + plist + "RdStealArgs a)\n{\n"
-        "    __shared__ unsigned int chunkShared;\n"
+        "    // Every warp works on its own: lane 0 takes a chunk (a run of 8x4 tiles) from the job-wide counter with one\n"
+        "    // system-scope atomic -- remote over NVLink for every rank but the owner -- and the NEXT chunk is requested\n"
+        "    // before the current one is rendered, so the round trip hides behind the tracing.\n"
+        "    const unsigned int lane = threadIdx.x & 31u;\n"
+        "    unsigned int chunk = 0;\n"
+        "    if (lane == 0) chunk = atomicAdd_system(a.counter, 1u);\n"
         "    for (;;) {\n"
-        "        if (threadIdx.x == 0) {\n"
-        "            chunkShared = atomicAdd_system(a.counter, 1u);\n"
-        "            if (chunkShared < a.numChunks && a.owned) a.owned[1u + atomicAdd(a.owned, 1u)] = chunkShared;\n"
+        "        unsigned int next = 0;\n"
+        "        if (lane == 0 && chunk < a.numChunks) {\n"
+        "            next = atomicAdd_system(a.counter, 1u);\n"
+        "            if (a.owned) a.owned[1u + atomicAdd(a.owned, 1u)] = chunk;\n"
         "        }\n"
-        "        __syncthreads();\n"
-        "        const unsigned int chunk = chunkShared;\n"
-        "        __syncthreads();\n"
-        "        if (chunk >= a.numChunks) break;\n"
-        "        for (unsigned int w = threadIdx.x; w < a.chunkItems; w += blockDim.x) {\n"
-        "            const unsigned int t = chunk * a.chunkItems + w;\n"
+        "        const unsigned int cur = __shfl_sync(0xffffffffu, chunk, 0);\n"
+        "        if (cur >= a.numChunks) break;\n"
+        "        for (unsigned int w = lane; w < a.chunkItems; w += 32u) {\n"
+        "            const unsigned int t = cur * a.chunkItems + w;\n"
         "            if (t < a.count) {\n"
         "                rd_wf_gid[threadIdx.x] = rd_wf_global_id(a.first + t, a.tileW);\n"
         "                raygen(" + names + ");\n"
         "            }\n"
+        "            __syncwarp();\n"
         "        }\n"
+        "        chunk = next;\n"
         "    }\n"
         "}\n}  // namespace rd_ls\n";
     return s;
@@ -654,7 +660,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     if (rc) return rc;
     CUdeviceptr dinfo; size_t infoBytes = 0;
     RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
-    const unsigned info[4] = {(unsigned)first, total, S.tileW, 1u};
+    const unsigned info[8] = {(unsigned)first, total, S.tileW, 1u, 0u, 0u, 0u, 0u};
     RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
     std::vector<uint64_t> args(p->boundArgs);
     args.push_back((uint64_t)(uintptr_t)B.dstate);
@@ -704,13 +710,13 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
     const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     const unsigned full = (unsigned)(count / block), tail = (unsigned)(count % block);
     if (full) {
-        const unsigned info[4] = {(unsigned)first, (unsigned)total, tileW, 0u};
+        const unsigned info[8] = {(unsigned)first, (unsigned)total, tileW, 0u, p->ilWorld, p->ilRank, p->ilBandRows, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         RD_CU(cuLaunchKernel(m->raygen, full, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
     if (tail) {
-        const unsigned info[4] = {(unsigned)first + full * block, (unsigned)total, tileW, 0u};
+        const unsigned info[8] = {(unsigned)first + full * block, (unsigned)total, tileW, 0u, p->ilWorld, p->ilRank, p->ilBandRows, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         RD_CU(cuLaunchKernel(m->raygen, 1, 1, 1, tail, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
@@ -722,7 +728,8 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
 // ---- multi-GPU chunk stealing -------------------------------------------------------------------
 // One array of frame counters lives on the GPU of the exporting rank; the other ranks (one process per GPU)
 // map it with CUDA IPC and increment it with system-scope atomics from their persistent raygen blocks.
-// Frame f uses counter f % slots, the owner clears the slot half a ring ahead, so frames need no reset
+// Frame f uses counter f % slots (callers pass f = 0, 1, 2, ... , the same on every rank), the owner clears
+// the slot half a ring ahead, so frames need no reset
 // round trip; the per-frame collective of the caller keeps the ranks within a frame of each other.
 #define RD_STEAL_SLOTS 1024u
 struct RdStealArgsHost { unsigned* counter; unsigned* owned; unsigned numChunks, chunkItems, first, count, tileW, pad; };
@@ -768,7 +775,9 @@ extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned heig
         if (rc) return rc;
     }
     const unsigned long long total = (unsigned long long)width * height;
-    if (!total || !chunkItems || total > 0xffffffffull) { rd_set_error("rd_trace_rays_steal: bad size"); return RD_E_ARG; }
+    if (!total || !chunkItems || (chunkItems & 31u) || total > 0xffffffffull) {
+        rd_set_error("rd_trace_rays_steal: chunkItems must be a positive multiple of 32"); return RD_E_ARG;
+    }
     const unsigned numChunks = (unsigned)((total + chunkItems - 1) / chunkItems);
     if (p->stealOwnedCap < numChunks + 1) {
         if (p->stealOwned) cudaFree(p->stealOwned);
@@ -781,7 +790,7 @@ extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned heig
     CUdeviceptr dinfo; size_t infoBytes = 0;
     RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
     const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
-    const unsigned info[4] = {0u, (unsigned)total, tileW, 1u};
+    const unsigned info[8] = {0u, (unsigned)total, tileW, 1u, 0u, 0u, 0u, 0u};
     RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
     RdStealArgsHost a;
     a.counter = p->stealCounters + (frame % p->stealSlots); a.owned = p->stealOwned;
@@ -790,8 +799,9 @@ extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned heig
     for (size_t i = 0; i < p->boundArgs.size(); ++i) argv[i] = &p->boundArgs[i];
     argv[p->boundArgs.size()] = &a;
     const unsigned block = (unsigned)p->optBlock;
+    const unsigned warpsPerBlock = block / 32u;
     unsigned blocks = (unsigned)p->smCount * 8u;
-    if (blocks > numChunks) blocks = numChunks;
+    if (blocks > (numChunks + warpsPerBlock - 1) / warpsPerBlock) blocks = (numChunks + warpsPerBlock - 1) / warpsPerBlock;
     RD_CU(cuLaunchKernel(m->stealRaygen, blocks, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
     p->launches += 1;
     return RD_OK;
@@ -822,6 +832,30 @@ extern "C" int rd_ray_count(rd_platform* p, uint64_t* out, int reset)
     if (reset) RD_CUDA(cudaMemset(p->dstatus + 2, 0, 8));
     *out = v;
     return RD_OK;
+}
+
+// Multi-GPU static partition without load imbalance: the frame's 8x4-tile rows are dealt to the ranks in bands
+// of `bandTileRows` rows, round robin (band b belongs to rank b % world); one launch renders all bands of
+// `rank`. Needs the tile mapping (width % 8 == 0, height % 4 == 0). Asynchronous on the platform stream.
+extern "C" int rd_trace_rays_interleaved(rd_platform* p, unsigned width, unsigned height, unsigned rank, unsigned world,
+                                         unsigned bandTileRows)
+{
+    if (!p) { rd_set_error("null platform"); return RD_E_ARG; }
+    if (!world || rank >= world || !bandTileRows || (width % 8u) || (height % 4u) || !p->optTile) {
+        rd_set_error("rd_trace_rays_interleaved: needs rank < world, bandTileRows > 0, width %% 8 == 0, height %% 4 == 0, option tile");
+        return RD_E_ARG;
+    }
+    const unsigned tileRows = height / 4u;
+    unsigned owned = 0;
+    for (unsigned b = rank; b * bandTileRows < tileRows; b += world) {
+        const unsigned r0 = b * bandTileRows, r1 = r0 + bandTileRows < tileRows ? r0 + bandTileRows : tileRows;
+        owned += r1 - r0;
+    }
+    if (!owned) return RD_OK;
+    p->ilWorld = world; p->ilRank = rank; p->ilBandRows = bandTileRows;
+    const int rc = rd_trace_rays_range(p, width, height, 0, (unsigned long long)owned * 4u * width);
+    p->ilWorld = 0; p->ilRank = 0; p->ilBandRows = 0;
+    return rc;
 }
 
 extern "C" int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height)

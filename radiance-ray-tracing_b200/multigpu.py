@@ -1,7 +1,9 @@
 """Host-side plumbing of the multi-GPU path: one process per GPU, the scene replicated,
 the frame sharded by screen tiles, ONE collective per frame (the framebuffer gather to rank 0).
 
-Two partitions:
+Three partitions:
+  interleave  bands of 8x4-tile rows dealt round robin (rd_trace_rays_interleaved): a static partition that
+           spreads the expensive screen regions over all ranks; frame = byte-wise SUM over ranks (NCCL reduce)
   static   contiguous runs of 8x4-tile rows per rank (rd_trace_rays_range) + NCCL send/recv of each rank's rows
   steal    dynamic chunk stealing from one counter shared over CUDA IPC / NVLink (rd_trace_rays_steal); every
            rank zeroes its framebuffer, renders the chunks it wins, and the frame is the byte-wise SUM over
@@ -19,6 +21,17 @@ def tile_row_range(rank, world, width, height, tile_h=4):
         r1 = tile_rows
     y0, y1 = r0 * tile_h, (height if rank == world - 1 else r1 * tile_h)
     return y0 * width, (y1 - y0) * width, y0, y1 - y0
+
+
+def interleaved_rows(rank, world, height, band_tile_rows=1, tile_h=4):
+    """Pixel-row runs (y0, rows) owned by `rank` under the interleaved band partition."""
+    tile_rows, out, b = height // tile_h, [], rank
+    while b * band_tile_rows < tile_rows:
+        r0 = b * band_tile_rows
+        r1 = min(r0 + band_tile_rows, tile_rows)
+        out.append((r0 * tile_h, (r1 - r0) * tile_h))
+        b += world
+    return out
 
 
 def gather_rows(image, rank, world, width, height, dist, channels=4):

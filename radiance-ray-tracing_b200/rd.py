@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
-    "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned",
+    "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
 ]
 
 
@@ -76,7 +76,7 @@ def lib():
             "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
-            "rd_steal_owned": [vp, vp, u, C.POINTER(u)],
+            "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
             "rd_tlas_save": [vp, vp, C.c_char_p], "rd_tlas_save_memory": [vp, vp, C.POINTER(vp), C.POINTER(sz)],
         }
         L.rd_free_host.argtypes, L.rd_free_host.restype = [vp], None
@@ -155,6 +155,11 @@ class BottomAccelStruct:
         _check(lib().rd_blas_stats(self.handle, out))
         return {"nodes": out[0], "triangles": out[1], "levels": out[2], "bytes": out[3]}
 
+    def free(self):
+        if self.handle:
+            lib().rd_blas_free(self.plt.handle, self.handle)
+            self.handle = None
+
 
 class Handle:
     """Buffer / Image / ImageArray / Sampler / TopAccelStruct descriptor handle."""
@@ -201,8 +206,12 @@ def StealCounterImport(plt, handle):
     _check(lib().rd_steal_counter_import(plt.handle, h.ctypes.data))
 
 
-def TraceRaysSteal(plt, width, height, frame, chunk_items=1024):
+def TraceRaysSteal(plt, width, height, frame, chunk_items=32):
     _check(lib().rd_trace_rays_steal(plt.handle, width, height, frame, chunk_items))
+
+
+def TraceRaysInterleaved(plt, width, height, rank, world, band_tile_rows=1):
+    _check(lib().rd_trace_rays_interleaved(plt.handle, width, height, rank, world, band_tile_rows))
 
 
 def StealOwned(plt, capacity=1 << 20):

@@ -381,7 +381,7 @@ RD_F rd_uint4 convert_uint4(const rd_float4& a) { return rd_uint4((uint)a.x, (ui
 #if RD_DEVICE_BUILD
 // Set by the launcher before each launch: first global id of this launch, total work-items,
 // and the image width used for the optional 8x4 pixel-tile remap (0 = identity mapping).
-extern "C" { __constant__ unsigned int rd_launch_info[4]; }
+extern "C" { __constant__ unsigned int rd_launch_info[8]; }
 // Wavefront stages (csrc/rd_wavefront.h) run a path on whatever thread its queue entry lands on; the
 // stage stores the path's work-item id here before calling user code and sets rd_launch_info[3].
 __shared__ unsigned int rd_wf_gid[256];
@@ -396,6 +396,13 @@ RD_F size_t get_global_id(uint dim)
         unsigned int tilesX = w >> 3;
         unsigned int tile = t >> 5, lane = t & 31u;
         unsigned int ty = tile / tilesX, tx = tile - ty * tilesX;
+        // multi-GPU interleaved partition (rd_trace_rays_interleaved): this rank's local tile row ty is
+        // row (band * world + rank) * bandRows + ty % bandRows of the frame, band = ty / bandRows
+        const unsigned int world = rd_launch_info[4];
+        if (world > 1u) {
+            const unsigned int bandRows = rd_launch_info[6], band = ty / bandRows;
+            ty = (band * world + rd_launch_info[5]) * bandRows + (ty - band * bandRows);
+        }
         unsigned int px = (tx << 3) + (lane & 7u), py = (ty << 2) + (lane >> 3);
         return (size_t)py * w + px;
     }

@@ -316,3 +316,31 @@ def test_chunk_stealing_renders_every_pixel_once(pkg, plt):
         owned = rd.StealOwned(plt)
         assert np.array_equal(np.sort(owned), np.arange(w * h // 512))
     assert np.array_equal(ds.read_image(), plain)
+
+
+def test_interleaved_partition_renders_every_pixel_once(pkg, plt):
+    """rd_trace_rays_interleaved: the bands of all ranks together are the plain frame (ranks run one after the
+    other on this GPU into one framebuffer), and one rank alone leaves the other ranks' rows untouched."""
+    rd, scenes, mg = pkg.rd, pkg.scenes, pkg.multigpu
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 320, 240
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 1, 2, 0))
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    plain = ds.read_image()
+    for world, band in ((2, 1), (3, 2), (8, 1), (4, 7)):
+        rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
+        rd.TraceRaysInterleaved(plt, w, h, world - 1, world, band)
+        plt.sync()
+        part = ds.read_image()
+        mine = np.zeros(h, bool)
+        for y0, ny in mg.interleaved_rows(world - 1, world, h, band):
+            mine[y0:y0 + ny] = True
+        assert np.array_equal(part[mine], plain[mine]) and (part[~mine] == 0).all()
+        for r in range(world - 1):
+            rd.TraceRaysInterleaved(plt, w, h, r, world, band)
+        plt.sync()
+        assert np.array_equal(ds.read_image(), plain)

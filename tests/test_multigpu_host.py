@@ -65,6 +65,12 @@ def test_row_partition_covers_every_row_once():
                 _, _, y0, ny = mg.tile_row_range(r, world, 1920, h)
                 rows[y0:y0 + ny] += 1
             assert (rows == 1).all(), (world, h)
+            for band in (1, 2, 7):
+                rows = np.zeros(h - h % 4, np.int32)
+                for r in range(world):
+                    for y0, ny in mg.interleaved_rows(r, world, h, band):
+                        rows[y0:y0 + ny] += 1
+                assert (rows == 1).all(), (world, h, band)
     # the chunk -> pixel map is a bijection of the frame
     px = np.concatenate([mg.chunk_pixels(c, 1024, 64, 36) for c in range((64 * 36 + 1023) // 1024)])
     assert np.array_equal(np.sort(px), np.arange(64 * 36))

@@ -58,7 +58,7 @@ for mode in ("steal", "static"):
             e0.record(stream)
             if mode == "steal":
                 image_t.zero_()
-                rd.TraceRaysSteal(plt, W, H, frame, 1024)
+                rd.TraceRaysSteal(plt, W, H, frame, int(os.environ.get('RD_CHUNK', '32')))
                 e1.record(stream)
                 mg.combine_sum(image_t, world, dist)
             else:
