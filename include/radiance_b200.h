@@ -155,7 +155,8 @@ int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, unsigned* c
  * All four are buffer handles. flags: RD_TRACE_* below. Asynchronous on the platform stream. */
 #define RD_TRACE_TERMINATE_ON_FIRST_HIT 1u
 #define RD_TRACE_COUNTERS 2u   /* also count node / triangle fetches (see rd_trace_counters) */
-#define RD_TRACE_STATIC_BATCHES 4u   /* 32-ray batches per warp without dynamic re-fetch (ablation) */
+#define RD_TRACE_STATIC_BATCHES 4u   /* 32-ray batches per warp (the default; flag kept for compatibility) */
+#define RD_TRACE_DYNAMIC_FETCH 8u    /* ablation: persistent warps that re-fetch rays for idle lanes (slower) */
 int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA, rd_handle rayB, rd_handle hitA,
                       rd_handle hitB, size_t n, unsigned flags);
 /* totals of the last RD_TRACE_COUNTERS launch: [0] wide nodes fetched, [1] triangle records fetched,

@@ -86,6 +86,13 @@ namespace ref_groups {
 #include "groups.cl"
 #include "groups_dispatch.inc"
 }  // namespace ref_groups
+#undef DATA_CL
+#undef MATH_CL
+#undef PI
+namespace ref_textured {
+#include "textured.cl"
+#include "textured_dispatch.inc"
+}  // namespace ref_textured
 
 // ----------------------------------------------------------------------------------------
 template <class F>
@@ -197,7 +204,7 @@ void ref_generate_ray(const void* cam48, const unsigned int* rand3, size_t index
     (float*)args[9], (NS::Material*)args[10], (image2d_array_t)args[11], (sampler_t)(uintptr_t)args[12], \
     (NS::AccelStruct*)args[13]
 
-// program: 0 = samples/shader.cl, 1 = programs/primary.cl, 2 = programs/path.cl, 3 = programs/groups.cl
+// program: 0 = samples/shader.cl, 1 = programs/primary.cl, 2 = programs/path.cl, 3 = programs/groups.cl, 4 = programs/textured.cl
 void ref_raygen(int program, void* const* args, size_t globalSize, size_t first, size_t count, int nthreads)
 {
     rd_host_global_size = globalSize;
@@ -208,6 +215,7 @@ void ref_raygen(int program, void* const* args, size_t globalSize, size_t first,
             else if (program == 1) ref_primary::raygen(RD_RAYGEN_ARGS(ref_primary));
             else if (program == 2) ref_path::raygen(RD_RAYGEN_ARGS(ref_path));
             else if (program == 3) ref_groups::raygen(RD_RAYGEN_ARGS(ref_groups));
+            else if (program == 4) ref_textured::raygen(RD_RAYGEN_ARGS(ref_textured));
         }
     });
 }

@@ -158,7 +158,7 @@ def raygen_shader1(args, global_size, first=0, count=None, nthreads=None):
                              nthreads or os.cpu_count() or 1)
 
 
-PROGRAMS = {"shader": 0, "primary": 1, "path": 2, "groups": 3}
+PROGRAMS = {"shader": 0, "primary": 1, "path": 2, "groups": 3, "textured": 4}
 
 
 def raygen(program, args, global_size, first=0, count=None, nthreads=None):

@@ -61,7 +61,7 @@ struct rd_platform {
     std::vector<int> boundKinds;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic;
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
@@ -104,7 +104,7 @@ int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride);
 void rd_wf_release(rd_platform* p);
 int rd_wf_upload_state(rd_platform* p, const RdWfState* host);
 int rd_wf_advance(rd_platform* p, unsigned op, unsigned a);
-int rd_wf_trace(rd_platform* p, const void* scene);
+int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch);
 int rd_wf_sort(rd_platform* p, unsigned count);
 
 #endif

@@ -672,7 +672,8 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
         RD_CU(cuLaunchKernel(m->wfGenerate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
         for (unsigned d = 0; d < rt[2]; ++d) {
-            rc = rd_wf_trace(p, scene); if (rc) return rc;
+            // primary rays are coherent (static batches); bounce rays are not (dynamic fetch), option wf_dynamic: 0 never, 1 bounces, 2 always
+            rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) return rc;
             if (S.sortOn) { rc = rd_wf_sort(p, (unsigned)count); if (rc) return rc; }
             RD_CU(cuLaunchKernel(m->wfShade, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
             p->launches += 1;

@@ -9,7 +9,7 @@
 // Each warp grabs 32 consecutive rays at a time from a global counter (lane 0 atomics + shuffle),
 // so the grid is sized to the machine (SM count x resident blocks), not to the ray count.
 template <int MODE>   // 0 closest hit, 1 first hit, 2 closest + counters, 3 first + counters
-__global__ void __launch_bounds__(128) rd_k_trace(const RdScene* __restrict__ scene, const float4* __restrict__ rayA,
+__global__ void __launch_bounds__(128, 7) rd_k_trace(const RdScene* __restrict__ scene, const float4* __restrict__ rayA,
                                                    const float4* __restrict__ rayB, float4* __restrict__ hitA,
                                                    rd_u32* __restrict__ hitB, unsigned long long n,
                                                    unsigned long long* __restrict__ counters)
@@ -125,7 +125,7 @@ extern "C" int rd_trace_ray_list(rd_platform* p, rd_handle tlas, rd_handle rayA,
     const RdScene* S = (const RdScene*)T->dptr;
     const float4 *a = (const float4*)A->dptr, *b = (const float4*)B->dptr;
     float4* ha = (float4*)HA->dptr; rd_u32* hb = (rd_u32*)HB->dptr;
-    if (flags & RD_TRACE_STATIC_BATCHES) {
+    if (!(flags & RD_TRACE_DYNAMIC_FETCH)) {   // static 32-ray batches measured faster (4.0 vs 2.9 Grays/s on C2)
         switch (mode) {
             case 0: rd_k_trace<0><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;
             case 1: rd_k_trace<1><<<blocks, 128, 0, p->stream>>>(S, a, b, ha, hb, n, p->dcounters); break;

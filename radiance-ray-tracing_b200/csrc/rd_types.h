@@ -78,6 +78,7 @@ struct RD_ALIGN(16) RdScene {
 // rd_trace flags
 #define RD_TRACE_TERMINATE_ON_FIRST_HIT 1u
 #define RD_TRACE_COUNTERS 2u
-#define RD_TRACE_STATIC_BATCHES 4u
+#define RD_TRACE_STATIC_BATCHES 4u   // default behaviour, kept for source compatibility
+#define RD_TRACE_DYNAMIC_FETCH 8u
 
 #endif

@@ -14,7 +14,7 @@
 // the shade stage's sort key: (hit group row, capped at 255) * 4 + (instanceCustomIndex & 3), where
 // the row is instanceSBTOffset + sbtRecordOffset for hits (radiance.cl:23-28 dispatch rule) and the
 // miss index for misses.
-__global__ void __launch_bounds__(128) rd_k_wf_trace(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
+__global__ void __launch_bounds__(128, 7) rd_k_wf_trace(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
 {
     const RdWfState wf = *wfp;
     const unsigned n = wf.counts[wf.cur];
@@ -39,6 +39,64 @@ __global__ void __launch_bounds__(128) rd_k_wf_trace(const RdScene* __restrict__
                 row = I->sbtOffset + (unsigned)wf.sbtRecordOffset; mat = I->customID & 3u;
             }
             wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
+        }
+    }
+}
+
+
+// Same stage with dynamic ray fetch (Aila & Laine 2009): bounce rays are incoherent and their walk lengths are
+// heavy-tailed, so a warp that waits for the slowest ray of a fixed batch runs with 7 of 32 lanes active (ncu,
+// profiles/README_r1.md). Here finished lanes do not wait: whenever at least RD_WF_FETCH_MIN lanes are idle the warp
+// takes that many new entries with one atomic and the idle lanes re-arm; every lane keeps its ray's state in an
+// RdTraversal between steps.
+#ifndef RD_WF_FETCH_MIN
+#define RD_WF_FETCH_MIN 8
+#endif
+__device__ __forceinline__ void rd_wf_store_hit(const RdScene* scene, const RdWfState& wf, unsigned j, const RdHitRec& h)
+{
+    ((float4*)wf.hitA)[j] = make_float4(h.t, h.b1, h.b2, __uint_as_float(h.prim));
+    wf.hitB[j] = h.inst;
+    unsigned row = (unsigned)wf.missIndex, mat = 0u;
+    if (h.t < RD_MISS_T) {
+        const RdInstance* I = scene->instances + h.inst;
+        row = I->sbtOffset + (unsigned)wf.sbtRecordOffset; mat = I->customID & 3u;
+    }
+    wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
+}
+
+__global__ void __launch_bounds__(128, 7) rd_k_wf_trace_dyn(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
+{
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    const unsigned lane = threadIdx.x & 31u, ltMask = (1u << lane) - 1u;
+    const float4* __restrict__ rayA = (const float4*)wf.rayA[wf.cur];
+    const float4* __restrict__ rayB = (const float4*)wf.rayB[wf.cur];
+    RdStackEntry stackMemory[RD_STACK_ALLOC];
+    RdTraversal T;
+    RdNoAnyHit cb;
+    bool active = false, exhausted = false;
+    unsigned mine = 0;
+    for (;;) {
+        unsigned act = __ballot_sync(0xffffffffu, active);
+        if (!exhausted && __popc(act) <= 32 - RD_WF_FETCH_MIN) {
+            const unsigned idle = ~act, cnt = (unsigned)__popc(idle);
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&wf.counts[2], cnt);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (!active) {
+                const unsigned j = base + (unsigned)__popc(idle & ltMask);
+                if (j < n) {
+                    const float4 a = __ldg(&rayA[j]), b = __ldg(&rayB[j]);
+                    T.begin(stackMemory, scene, a.x, a.y, a.z, b.x, b.y, b.z, a.w, b.w);
+                    active = true; mine = j;
+                }
+            }
+            if (base + cnt >= n) exhausted = true;
+            act = __ballot_sync(0xffffffffu, active);
+        }
+        if (act == 0u) break;
+        if (active) {
+            if (!T.step(scene, cb)) { rd_wf_store_hit(scene, wf, mine, T.hit); active = false; }
         }
     }
 }
@@ -157,9 +215,12 @@ int rd_wf_advance(rd_platform* p, unsigned op, unsigned a)
     return RD_OK;
 }
 
-int rd_wf_trace(rd_platform* p, const void* scene)
+int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
 {
-    rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+    if (dynamicFetch)
+        rd_k_wf_trace_dyn<<<(unsigned)p->smCount * 6u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+    else
+        rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
     p->launches += 1;
     RD_CUDA(cudaGetLastError());
     return RD_OK;

@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libradiance_b200.so")
 
 RD_ADDRESS_CLAMP_TO_EDGE, RD_ADDRESS_CLAMP, RD_ADDRESS_REPEAT, RD_ADDRESS_MIRRORED_REPEAT = 0x1131, 0x1132, 0x1133, 0x1134
 RD_FILTER_NEAREST, RD_FILTER_LINEAR = 0x1140, 0x1141
-TRACE_TERMINATE_ON_FIRST_HIT, TRACE_COUNTERS, TRACE_STATIC_BATCHES = 1, 2, 4
+TRACE_TERMINATE_ON_FIRST_HIT, TRACE_COUNTERS, TRACE_STATIC_BATCHES, TRACE_DYNAMIC_FETCH = 1, 2, 4, 8
 
 # every symbol include/radiance_b200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [

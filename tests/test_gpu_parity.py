@@ -344,3 +344,54 @@ def test_interleaved_partition_renders_every_pixel_once(pkg, plt):
             rd.TraceRaysInterleaved(plt, w, h, r, world, band)
         plt.sync()
         assert np.array_equal(ds.read_image(), plain)
+
+
+def test_textured_material_matches_reference_runtime(pkg, plt, ref):
+    """RD::CreateImageArray / WriteImage / CreateSampler + read_imageui (samples/shader2.cl:255-265): layered RGBA8,
+    REPEAT + LINEAR, normalised coordinates, uv outside [0,1]. GPU image against the same program built against the
+    reference runtime on the host; WriteImage / ReadImage round trip per layer."""
+    import ctypes as C
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    for k in range(len(b.materials)):
+        b.materials[k]["albedoTex"] = k % 2          # every mesh textured, two layers
+    b.uvData[:, :2] *= 1.7                            # coordinates leave [0,1]: REPEAT wraps them
+    tw, th, layers = 32, 16, 2
+    yy, xx = np.meshgrid(np.arange(th), np.arange(tw), indexing="ij")
+    tex = np.zeros((layers, th, tw, 4), np.uint8)
+    tex[0, ..., 0], tex[0, ..., 1], tex[0, ..., 2] = (xx * 8) % 256, (yy * 16) % 256, ((xx ^ yy) & 1) * 255
+    tex[1, ..., 0], tex[1, ..., 1], tex[1, ..., 2] = 255 - (yy * 16) % 256, ((xx // 4 + yy // 4) & 1) * 200 + 30, (xx * 5 + yy * 3) % 256
+    tex[..., 3] = 255
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 256, 192
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 1, 1, 0))
+    ds.rdTextures = rd.CreateImageArray(plt, tw, th, layers)
+    for layer in range(layers):
+        rd.WriteImage(plt, ds.rdTextures, tw, th, layer, tex[layer])
+    back = np.zeros((th, tw, 4), np.uint8)
+    rd.ReadImage(plt, ds.rdTextures, tw, th, 1, back)
+    assert np.array_equal(back, tex[1])
+    ds.descriptors[11] = ds.rdTextures
+    pipe, _ = scenes.make_pipeline(plt, "textured")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    img = ds.read_image()
+
+    class Desc(C.Structure):   # rd_image_array_desc of shader/compat/cl_compat.h (host flavour)
+        _fields_ = [("texels", C.c_void_p), ("width", C.c_uint), ("height", C.c_uint), ("layers", C.c_uint), ("pad", C.c_uint)]
+    flat = np.ascontiguousarray(tex)
+    desc = Desc(flat.ctypes.data, tw, th, layers, 0)
+    sampler = rd.RD_ADDRESS_REPEAT | (rd.RD_FILTER_LINEAR << 16) | (1 << 32)
+    cam = np.array(b.camera).reshape(()).copy()
+    cam["widthPixel"], cam["heightPixel"] = w, h
+    n = w * h
+    scratch, image = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
+    tl = scenes.build_reference_scene(ref, b)
+    args = [np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1), scratch, image, cam.reshape(1), np.array(b.scene).reshape(1),
+            b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData, b.materials, C.addressof(desc), sampler, tl.blob]
+    ref.raygen("textured", args, n)
+    exp = image.reshape(h, w, 4)
+    d = img[..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+    assert np.sqrt((d * d).mean()) <= IMAGE_RMSE_U8, "RMSE %g" % np.sqrt((d * d).mean())
+    assert img[..., :3].std() > 30 and len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 2000   # the texture is visible

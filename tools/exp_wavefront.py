@@ -45,7 +45,7 @@ for n_grid in [int(a) for a in sys.argv[1:]] or [708]:
     t_gen = timed(lambda: rd.GeneratePrimaryRays(plt, cam, 0, 0, W, H, ra, rb))
     print("  primary ray generation %.4f ms" % t_gen, flush=True)
     res = {}
-    for name, flags in [("static", rd.TRACE_STATIC_BATCHES), ("dynamic", 0), ("static_first", rd.TRACE_STATIC_BATCHES | 1), ("dynamic_first", 1)]:
+    for name, flags in [("static", 0), ("dynamic", rd.TRACE_DYNAMIC_FETCH), ("static_first", 1), ("dynamic_first", rd.TRACE_DYNAMIC_FETCH | 1)]:
         t = timed(lambda: rd.TraceRayList(plt, tlas, ra, rb, ha, hb, n, flags))
         out = np.zeros(n, rd.HIT_DTYPE)
         rd.ReadBuffer(plt, ha, n * 16, out)

@@ -23,7 +23,11 @@ rd.BindPipeline(plt, pipe)
 rd.BindDescriptorSet(plt, ds.descriptors)
 plt.set_option("wavefront", 1)
 plt.set_option("wf_sort", sort)
-for _ in range(2):
+plt.set_option("wf_dynamic", int(os.environ.get("RD_WF_DYNAMIC", "1")))
+import time
+for _ in range(3):
     ds.set_rtprop(0, spp, depth)
+    t0 = time.perf_counter()
     rd.TraceRays(plt, 0, 0, 0, W, H)
+    print("frame %.2f ms" % ((time.perf_counter() - t0) * 1e3))
 print("done", ds.read_image()[..., :3].mean())
