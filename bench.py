@@ -27,6 +27,9 @@ import __graft_entry__ as entry  # noqa: E402
 WIDTH, HEIGHT, GRID_N = 1920, 1080, 708
 WORKLOAD = "C2: primary-ray closest-hit, 1920x1080, 1 spp, height-field n=708 (1002528 triangles), programs/primary.cl"
 NODE_BYTES, TRI_BYTES, RAY_BYTES, HIT_BYTES = 80, 48, 32, 16
+# dram__bytes_read.sum + dram__bytes_write.sum of one raygen launch of this workload, from the ncu --set full capture
+# summarised in profiles/ncu_r1c_primary.txt (93.44 MB + 29.40 MB); re-measured whenever the kernel changes
+NCU_DRAM_BYTES_PER_LAUNCH = 122.85e6
 
 
 def measured_peaks():
@@ -361,7 +364,8 @@ def main():
             "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 16,
                     "d2h_bytes_per_step": n * 4 if world > 1 else count * 4, "ms_per_step": e2e_ms},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",
+                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None, "traffic_unit": "bytes per launch (ncu dram read + write)",
+                         "algorithmic_bytes_per_launch": rays_per_launch * bytes_per_ray, "peak_kind": peak_kind, "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",
                          "kernel_ms": kern_ms, "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray,
                          "tris_per_ray": tris_per_ray},
         }
