@@ -395,3 +395,50 @@ def test_textured_material_matches_reference_runtime(pkg, plt, ref):
     d = img[..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
     assert np.sqrt((d * d).mean()) <= IMAGE_RMSE_U8, "RMSE %g" % np.sqrt((d * d).mean())
     assert img[..., :3].std() > 30 and len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 2000   # the texture is visible
+
+
+def test_ragged_frame_sizes_in_every_launch_mode(pkg, plt):
+    """Frame sizes that are not multiples of the 8x4 tile or of the block: inline (full + tail launch), wavefront
+    and chunk-stealing launches must all render the same image; a zero-sized frame is a no-op."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    plt.set_option("stealing", 1)
+    try:
+        pipe, _ = scenes.make_pipeline(plt, "path")
+    finally:
+        plt.set_option("stealing", 0)
+    for w, h in ((203, 151), (8, 4), (1, 1), (129, 3)):
+        ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 2, 3, 0))
+        rd.BindPipeline(plt, pipe)
+        rd.BindDescriptorSet(plt, ds.descriptors)
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        inline = ds.read_image()
+        assert (inline[..., 3] == 255).all()
+        plt.set_option("wavefront", 1)
+        try:
+            ds.set_rtprop(0, 2, 3)
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+        finally:
+            plt.set_option("wavefront", 0)
+        wave = ds.read_image()
+        d = wave[..., :3].astype(np.float64) - inline[..., :3].astype(np.float64)
+        assert np.sqrt((d * d).mean()) <= 0.5, (w, h)
+        rd.WriteBuffer(plt, ds.rdImage, inline.nbytes, np.zeros_like(inline))
+        ds.set_rtprop(0, 2, 3)
+        rd.TraceRaysSteal(plt, w, h, 900 + w, 64)
+        plt.sync()
+        assert np.array_equal(ds.read_image(), inline), (w, h)
+    rd.TraceRays(plt, 0, 0, 0, 0, 0)
+    # an empty scene renders the miss shader everywhere in both modes
+    et = rd.BuildAccelStruct(plt, [])
+    ds = scenes.DeviceScene(plt, b, et, 64, 32, scenes.rtprop(0, 1, 2, 0))
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, 64, 32)
+    sky = ds.read_image()
+    plt.set_option("wavefront", 1)
+    try:
+        rd.TraceRays(plt, 0, 0, 0, 64, 32)
+    finally:
+        plt.set_option("wavefront", 0)
+    assert np.array_equal(ds.read_image(), sky) and sky[..., 2].min() > 100
