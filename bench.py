@@ -200,6 +200,75 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
     return out
 
 
+def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bundle, w, h, spp, depth, frames=3):
+    """Path tracing across all ranks with dynamic chunk stealing: frame ms (max over ranks, device events, gather
+    included) and Mrays/s with the rays of one frame counted on rank 0 by a count_rays build."""
+    rd, scenes, mg = pkg.rd, pkg.scenes, pkg.multigpu
+    tlas, blas = scenes.build_scene(plt, bundle)
+    ds = scenes.DeviceScene(plt, bundle, tlas, w, h, scenes.rtprop(0, spp, depth, 0))
+    n = w * h
+    image_t = torch.zeros(n * 4, dtype=torch.uint8, device="cuda")
+    ds.rdImage = rd.WrapBuffer(plt, image_t.data_ptr(), n * 4, owner=image_t)
+    ds.descriptors[2] = ds.rdImage
+    rays = 0
+    if rank == 0:
+        plt.set_option("count_rays", 1)
+        try:
+            pipe, _ = scenes.make_pipeline(plt, "path")
+        finally:
+            plt.set_option("count_rays", 0)
+        rd.BindPipeline(plt, pipe)
+        rd.BindDescriptorSet(plt, ds.descriptors)
+        plt.ray_count()
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        rays = plt.ray_count()
+    plt.set_option("stealing", 1)
+    mg.exchange_steal_handle(rd, plt, rank, world, dist, "cuda")
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+
+    def timed(render):
+        ms = []
+        for f in range(frames + 1):
+            torch.cuda.synchronize()
+            dist.barrier()
+            with torch.cuda.stream(stream):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream)
+                image_t.zero_()
+                render(f)
+                mg.combine_sum(image_t, world, dist)
+                e1.record(stream)
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms.append(float(t[0]))
+        return float(np.median(ms[1:]))
+
+    steal_ms = timed(lambda f: rd.TraceRaysSteal(plt, w, h, 600 + f, 32))
+    owned = torch.tensor([len(rd.StealOwned(plt))], device="cuda")
+    allc = [torch.zeros_like(owned) for _ in range(world)]
+    dist.all_gather(allc, owned)
+    # wavefront stages on the interleaved band partition
+    plt.set_option("wavefront", 1)
+    try:
+        def wave(f):
+            ds.set_rtprop(0, spp, depth)
+            rd.TraceRaysInterleaved(plt, w, h, rank, world, 1)
+        wave_ms = timed(wave)
+    finally:
+        plt.set_option("wavefront", 0)
+    for hnd in [tlas] + list(blas):
+        hnd.free()
+    best = min(steal_ms, wave_ms)
+    return {"workload": name, "triangles": bundle.triangle_count(), "spp": spp, "depth": depth, "rays_per_frame": rays,
+            "frame_ms": best, "value": rays / best / 1e3 if rays else None, "unit": "Mrays/s",
+            "inline_stealing": {"frame_ms": steal_ms, "partition": "dynamic chunk stealing + NCCL sum-reduce",
+                                "chunks_per_rank": [int(c) for c in allc]},
+            "wavefront_interleaved": {"frame_ms": wave_ms, "partition": "interleaved tile-row bands + NCCL sum-reduce"}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -337,6 +406,18 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t[0])
 
+    multi = {}
+    if world > 1 and not args.no_extra:
+        # frame ms of the path-traced configs across the ranks (the "frame ms at 1/2/4/8 B200" half of the metric)
+        try:
+            multi["C3"] = multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world,
+                "C3: path.cl, 1080p 16 spp depth 5, blob-field n=2237", scenes.blob_field_scene(2237, WIDTH, HEIGHT), WIDTH, HEIGHT, 16, 5)
+            if args.extra == "all":
+                multi["C5"] = multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world,
+                    "C5: path.cl, 3840x2160 64 spp depth 5, 5 instances of the n=2237 height-field (50 M triangles)",
+                    scenes.replicated_scene(2237, 5, 3840, 2160), 3840, 2160, 64, 5, frames=2)
+        except Exception as e:
+            multi["error"] = repr(e)[:300]
     if rank == 0:
         # algorithmic bytes per ray: counters-on build of the same traversal over the same primary rays
         ra, rb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 16)
@@ -369,6 +450,8 @@ def main():
                          "kernel_ms": kern_ms, "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray,
                          "tris_per_ray": tris_per_ray},
         }
+        if multi:
+            out["extra"] = multi
         if world == 1 and not args.no_extra:
             # the path-tracing half of the metric ("primary + 4-bounce path"): BASELINE configs[2] (and configs[3]
             # with --extra all), wavefront mode against the inline raygen kernel of the same program

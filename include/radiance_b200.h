@@ -179,6 +179,9 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * over ray queues in HBM -- generate, trace, sort by hit group, shade, resolve -- instead of one raygen
  * launch; needs the wavefrontScene / wavefrontPrimary hooks in the program),
  * "stealing" (0/1: modules created afterwards also carry the persistent chunk-stealing raygen),
+ * "wf_dynamic" (0 never / 1 bounce stages (default) / 2 always: dynamic ray fetch in the wavefront trace stage),
+ * "wf_ray_sort" (0/1, default 0: re-sort bounce rays by direction octant and origin cell before tracing them;
+ * measured slower on C3 -- the pass costs more than the trace stage gains),
  * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow

@@ -61,7 +61,7 @@ struct rd_platform {
     std::vector<int> boundKinds;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic, optWfRaySort;
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
@@ -106,5 +106,6 @@ int rd_wf_upload_state(rd_platform* p, const RdWfState* host);
 int rd_wf_advance(rd_platform* p, unsigned op, unsigned a);
 int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch);
 int rd_wf_sort(rd_platform* p, unsigned count);
+int rd_wf_reorder_rays(rd_platform* p, const void* scene, unsigned count);
 
 #endif

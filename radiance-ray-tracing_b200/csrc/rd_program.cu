@@ -279,7 +279,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    const RdWfState wf = *wfp;\n"
          "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
          "    if (slot >= wf.count) return;\n"
-         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + slot, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    struct SceneData sd; struct Payload pl;\n"
          "    wavefrontScene(&sd, " + names + ");\n"
          "    sd.depth = 0; sd.frameID = wf.frameID;\n"
@@ -301,7 +301,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    if (jj >= n) return;\n"
          "    const unsigned j = wf.sortOn ? wf.order[jj] : jj;\n"
          "    const unsigned slot = wf.pathOf[wf.cur][j];\n"
-         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    rd_wf_gid[threadIdx.x] = gid;\n"
          "    struct SceneData sd;\n"
          "    wavefrontScene(&sd, " + names + ");\n"
@@ -360,7 +360,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    const RdWfState wf = *wfp;\n"
          "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
          "    if (slot >= wf.count) return;\n"
-         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW);\n"
+         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    const float* px = (const float*)" + P[1].name + " + 4 * (size_t)gid;\n"
          "    float3 color = {px[0], px[1], px[2]};\n"
          "    if (!wf.debug) {\n";
@@ -655,6 +655,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     S.payloadStride = stride; S.cur = 0; S.first = (unsigned)first; S.count = (unsigned)count; S.total = total;
     S.tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     S.frameID = rt[0]; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
+    S.ilWorld = p->ilWorld; S.ilRank = p->ilRank; S.ilBandRows = p->ilBandRows ? p->ilBandRows : 1u;
     S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
     rc = rd_wf_upload_state(p, &S);
     if (rc) return rc;
@@ -672,6 +673,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
         RD_CU(cuLaunchKernel(m->wfGenerate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
         for (unsigned d = 0; d < rt[2]; ++d) {
+            if (d > 0 && p->optWfRaySort) { rc = rd_wf_reorder_rays(p, scene, (unsigned)count); if (rc) return rc; }
             // primary rays are coherent (static batches); bounce rays are not (dynamic fetch), option wf_dynamic: 0 never, 1 bounces, 2 always
             rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) return rc;
             if (S.sortOn) { rc = rd_wf_sort(p, (unsigned)count); if (rc) return rc; }

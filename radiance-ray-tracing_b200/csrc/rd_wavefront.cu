@@ -158,12 +158,71 @@ __global__ void rd_k_wf_scatter(const RdWfState* __restrict__ wfp)
     wf.order[base + (unsigned)__popc(same & ((1u << lane) - 1u))] = j;
 }
 
+
+// ---- ray reordering before a bounce trace -------------------------------------------------------------
+// Bounce rays leave the shade stage in hit-group order: neighbours in the queue start anywhere and point
+// anywhere, so a warp of the trace stage touches 32 unrelated parts of the structure. This pass re-sorts the
+// queue by (direction octant, coarse origin cell) with the same counting sort: key = octant << 7 | 7-bit cell
+// code (3 + 3 bits on the two widest axes of the scene box, 1 bit on the third), rays that start in the same
+// region and head the same way become neighbours. The rays are moved (not indexed) into the idle queue buffer.
+__global__ void rd_k_wf_ray_keys(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
+{
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    // scene box from the root node of the top-level structure: origin p, 256 grid steps of 2^(e-127) per axis
+    const uint4 n0 = __ldg((const uint4*)&scene->nodes[0].w[0]);
+    const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
+    const unsigned ex = n0.w & 0xffu, ey = (n0.w >> 8) & 0xffu, ez = (n0.w >> 16) & 0xffu;
+    const float4 a = __ldg(&((const float4*)wf.rayA[wf.cur])[j]), b = __ldg(&((const float4*)wf.rayB[wf.cur])[j]);
+    // cell coordinate in [0,8) per axis
+    const float fx = (a.x - px) * __uint_as_float((254u - ex) << 23) * (1.0f / 32.0f);
+    const float fy = (a.y - py) * __uint_as_float((254u - ey) << 23) * (1.0f / 32.0f);
+    const float fz = (a.z - pz) * __uint_as_float((254u - ez) << 23) * (1.0f / 32.0f);
+    unsigned cx = (unsigned)fminf(fmaxf(fx, 0.0f), 7.0f), cy = (unsigned)fminf(fmaxf(fy, 0.0f), 7.0f), cz = (unsigned)fminf(fmaxf(fz, 0.0f), 7.0f);
+    // the axis with the smallest extent keeps one bit
+    unsigned c0, c1, c2;   // c0, c1: 3 bits each; c2: 1 bit
+    if (ey <= ex && ey <= ez) { c0 = cx; c1 = cz; c2 = cy >> 2; }
+    else if (ex <= ey && ex <= ez) { c0 = cy; c1 = cz; c2 = cx >> 2; }
+    else { c0 = cx; c1 = cy; c2 = cz >> 2; }
+    // interleave c0 / c1 (Morton order keeps neighbouring cells close in the queue)
+    unsigned m = 0;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) m |= (((c0 >> k) & 1u) << (2 * k)) | (((c1 >> k) & 1u) << (2 * k + 1));
+    const unsigned oct = (b.x < 0.0f ? 4u : 0u) | (b.y < 0.0f ? 2u : 0u) | (b.z < 0.0f ? 1u : 0u);
+    wf.keys[j] = (oct << 7) | (c2 << 6) | m;
+}
+
+__global__ void rd_k_wf_ray_scatter(const RdWfState* __restrict__ wfp)
+{
+    const RdWfState wf = *wfp;
+    const unsigned n = wf.counts[wf.cur];
+    const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned lane = threadIdx.x & 31u;
+    const bool valid = j < n;
+    const unsigned act = __ballot_sync(0xffffffffu, valid);
+    if (!valid) return;
+    const unsigned key = wf.keys[j];
+    const unsigned same = __match_any_sync(act, key);
+    const unsigned leader = (unsigned)__ffs(same) - 1u;
+    unsigned base = 0;
+    if (lane == leader) base = atomicAdd(&wf.hist[key], (unsigned)__popc(same));
+    base = __shfl_sync(same, base, leader);
+    const unsigned pos = base + (unsigned)__popc(same & ((1u << lane) - 1u));
+    const unsigned q = wf.cur, o = wf.cur ^ 1u;
+    ((float4*)wf.rayA[o])[pos] = ((const float4*)wf.rayA[q])[j];
+    ((float4*)wf.rayB[o])[pos] = ((const float4*)wf.rayB[q])[j];
+    wf.pathOf[o][pos] = wf.pathOf[q][j];
+}
+
 // per-stage state edits on the device (keeps the stage sequence free of host synchronisation)
 __global__ void rd_k_wf_advance(RdWfState* wf, unsigned op, unsigned a, unsigned b)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     if (op == 0) { wf->frameID = a; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; }                    // new sample
     else if (op == 1) { wf->counts[2] = 0; }                                                           // before trace
+    else if (op == 3) { const unsigned n = wf->counts[wf->cur]; wf->counts[wf->cur] = 0; wf->cur ^= 1u; wf->counts[wf->cur] = n; }   // after a ray reorder
     else if (op == 2) { wf->cur ^= 1u; wf->counts[wf->cur ^ 1u] = 0; wf->depth += 1; wf->counts[2] = 0; } // after shade
 }
 
@@ -222,6 +281,21 @@ int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
     else
         rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
     p->launches += 1;
+    RD_CUDA(cudaGetLastError());
+    return RD_OK;
+}
+
+int rd_wf_reorder_rays(rd_platform* p, const void* scene, unsigned count)
+{
+    const RdWfState* S = (const RdWfState*)p->wf.dstate;
+    RD_CUDA(cudaMemsetAsync(p->wf.hist, 0, RD_WF_KEY_BINS * 4, p->stream));
+    unsigned hb = (count + 255u) / 256u; if (hb > (unsigned)p->smCount * 8u) hb = (unsigned)p->smCount * 8u; if (!hb) hb = 1;
+    rd_k_wf_ray_keys<<<(count + 255u) / 256u, 256, 0, p->stream>>>((const RdScene*)scene, S);
+    rd_k_wf_hist<<<hb, 256, 0, p->stream>>>(S);
+    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, p->stream>>>(S);
+    rd_k_wf_ray_scatter<<<(count + 255u) / 256u, 256, 0, p->stream>>>(S);
+    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, 3u, 0u, 0u);
+    p->launches += 5;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
 }

@@ -34,16 +34,19 @@ struct RD_ALIGN(16) RdWfState {
     rd_u32 frameID, totalSamples; // sample being traced, RTProp->totalSamples
     rd_u32 depth, maxDepth;       // bounce index of this stage, RTProp->depth
     rd_u32 debug, sortOn;
+    rd_u32 ilWorld, ilRank, ilBandRows, pad0;   // interleaved multi-GPU partition (0 = whole frame), see rd_trace_rays_interleaved
     int sbtRecordOffset, missIndex;
     float tmin, tmax;
 };
 
 // work-item t of the launch -> global id (pixel index), same mapping as get_global_id in cl_compat.h
-RD_HD rd_u32 rd_wf_global_id(rd_u32 t, rd_u32 tileW)
+RD_HD rd_u32 rd_wf_global_id(rd_u32 t, rd_u32 tileW, rd_u32 world = 0, rd_u32 rank = 0, rd_u32 bandRows = 1)
 {
     if (!tileW) return t;
     const rd_u32 tilesX = tileW >> 3, tile = t >> 5, lane = t & 31u;
-    const rd_u32 ty = tile / tilesX, tx = tile - ty * tilesX;
+    rd_u32 ty = tile / tilesX;
+    const rd_u32 tx = tile - ty * tilesX;
+    if (world > 1u) { const rd_u32 band = ty / bandRows; ty = (band * world + rank) * bandRows + (ty - band * bandRows); }
     return ((ty << 2) + (lane >> 3)) * tileW + (tx << 3) + (lane & 7u);
 }
 

@@ -62,8 +62,9 @@ def combine_sum(image, world, dist):
 def exchange_steal_handle(rd, plt, rank, world, dist, device):
     """Rank 0 exports its chunk counter, the others import it (64-byte CUDA IPC handle, one broadcast)."""
     import torch
-    if world == 1:
+    if world == 1 or getattr(plt, "_steal_exchanged", False):
         return
+    plt._steal_exchanged = True
     h = torch.zeros(64, dtype=torch.uint8, device=device)
     if rank == 0:
         h.copy_(torch.from_numpy(rd.StealCounterExport(plt)))

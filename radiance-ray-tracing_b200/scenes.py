@@ -277,6 +277,23 @@ def groups_scene(n=2240, side=64, groups=64, width=1920, height=1080, seed=1):
     return bndl
 
 
+def replicated_scene(n=2237, copies=5, width=3840, height=2160, seed=1):
+    """C5: `copies` instances of ONE n x n height-field BLAS laid out in a row along z (50 M
+    triangles for n=2237, copies=5), 3 materials by instance, 4K camera looking down the row."""
+    hv, ht = heightfield(n, seed)
+    mats = [material((0.7, 0.6, 0.5), 0.0, 0.7), material((0.85, 0.85, 0.9), 0.9, 0.2), material((0.2, 0.5, 0.8), 0.0, 0.4)]
+    inst = [(0, translate(0.0, 0.0, -1.0 * k), 0, k % 3) for k in range(copies)]
+    b = SceneBundle([(hv, ht)], inst, mats, [0])
+    info = np.zeros(len(inst), MESHINFO_DTYPE)
+    for k, (mi, _, _, custom) in enumerate(inst):
+        info[k] = b.meshInfoData[mi]
+        info[k]["materialIndex"] = custom
+    b.meshInfoData = info
+    b.camera = camera(width, height, (0.0, 0.6, 0.9), (-0.35, 0.0, 0.0), 0.030, 0.036, 2.0, 0.0)
+    b.scene = scene_properties((-0.4, -1.0, -0.3), (6.0, 6.0, 6.0))
+    return b
+
+
 def pinhole_rays(cam, tmin=0.001, tmax=1000.0, stride=1, jitter=None):
     """Explicit primary-ray list for hit-ID parity tests (float32, host-generated once and shared
     by oracle and GPU): pinhole of samples/shader.cl:111-153 with a fixed sub-pixel offset."""

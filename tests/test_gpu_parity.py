@@ -344,6 +344,20 @@ def test_interleaved_partition_renders_every_pixel_once(pkg, plt):
             rd.TraceRaysInterleaved(plt, w, h, r, world, band)
         plt.sync()
         assert np.array_equal(ds.read_image(), plain)
+    # the same partition through the wavefront stages
+    plt.set_option("wavefront", 1)
+    try:
+        ds.set_rtprop(0, 1, 2)
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        whole = ds.read_image()
+        rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
+        for r in range(3):
+            ds.set_rtprop(0, 1, 2)
+            rd.TraceRaysInterleaved(plt, w, h, r, 3, 2)
+        plt.sync()
+        assert np.array_equal(ds.read_image(), whole)
+    finally:
+        plt.set_option("wavefront", 0)
 
 
 def test_textured_material_matches_reference_runtime(pkg, plt, ref):

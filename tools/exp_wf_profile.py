@@ -24,6 +24,7 @@ rd.BindDescriptorSet(plt, ds.descriptors)
 plt.set_option("wavefront", 1)
 plt.set_option("wf_sort", sort)
 plt.set_option("wf_dynamic", int(os.environ.get("RD_WF_DYNAMIC", "1")))
+plt.set_option("wf_ray_sort", int(os.environ.get("RD_WF_RAYSORT", "1")))
 import time
 for _ in range(3):
     ds.set_rtprop(0, spp, depth)
