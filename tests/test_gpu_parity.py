@@ -456,3 +456,69 @@ def test_ragged_frame_sizes_in_every_launch_mode(pkg, plt):
     finally:
         plt.set_option("wavefront", 0)
     assert np.array_equal(ds.read_image(), sky) and sky[..., 2].min() > 100
+
+
+def _brute_force_hits(verts, tris, rays, tmin=0.001, tmax=1000.0):
+    """Moeller-Trumbore over every triangle in float64 (numpy), reference accept rule (radiance.cl:221-240, :90-91)."""
+    v0, v1, v2 = (verts[tris[:, k]].astype(np.float64) for k in range(3))
+    e1, e2 = v1 - v0, v2 - v0
+    out = []
+    for r in rays:
+        o, d = r[0:3].astype(np.float64), r[4:7].astype(np.float64)
+        p = np.cross(d, e2)
+        det = (e1 * p).sum(1)
+        ok = det != 0
+        inv = np.where(ok, 1.0 / np.where(ok, det, 1.0), 0.0)
+        s = o - v0
+        u = inv * (s * p).sum(1)
+        q = np.cross(s, e1)
+        v = inv * (q @ d)
+        t = inv * (e2 * q).sum(1)
+        hit = ok & (u >= 0) & (u <= 1) & (v >= 0) & (u + v <= 1) & (t > tmin) & (t < tmax)
+        if hit.any():
+            k = np.where(hit)[0][np.argmin(t[hit])]
+            out.append((int(k), float(t[k])))
+        else:
+            out.append((-1, np.inf))
+    return out
+
+
+def test_c2_full_size_hits_match_reference(pkg, plt, ref):
+    """BASELINE configs[1] at full size (1 002 528 triangles, the bench scene): 2^16 of the frame's own primary rays
+    against the reference's traceRay over the reference's own SAH BVH."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = scenes.heightfield_scene(708, 1920, 1080)
+    tlas, blas = scenes.build_scene(plt, b)
+    rays = scenes.pinhole_rays(b.camera, jitter=(0.37, 0.61))
+    rng = np.random.default_rng(7)
+    rays = rays[rng.choice(len(rays), 1 << 16, replace=False)]
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    exp = scenes.build_reference_scene(ref, b).trace(rays)
+    assert compare_hits(hitA, hitB, exp) > 30000
+
+
+def test_c3_full_size_properties(pkg, plt):
+    """BASELINE configs[2] scene at full size (10 069 778 triangles, 4 instances): properties that need no 5-minute
+    reference build -- brute force over all triangles for a few rays, closest-hit vs first-hit consistency,
+    static vs dynamic-fetch kernels, determinism."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = scenes.blob_field_scene(2237, 1920, 1080)
+    tlas, blas = scenes.build_scene(plt, b)
+    assert blas[0].stats()["triangles"] == 2 * 2237 * 2237
+    rays = scenes.pinhole_rays(b.camera, jitter=(0.37, 0.61))
+    rng = np.random.default_rng(11)
+    rays = rays[rng.choice(len(rays), 1 << 15, replace=False)]
+    hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+    hitA2, hitB2 = rd.trace_host_rays(plt, tlas, rays, rd.TRACE_DYNAMIC_FETCH)
+    assert np.array_equal(hitA["t"], hitA2["t"]) and np.array_equal(hitA["prim"], hitA2["prim"]) and np.array_equal(hitB, hitB2)
+    first, _ = rd.trace_host_rays(plt, tlas, rays, rd.TRACE_TERMINATE_ON_FIRST_HIT)
+    assert np.array_equal(first["t"] < 3e38, hitA["t"] < 3e38)          # occluded <=> a closest hit exists
+    assert (first["t"][first["t"] < 3e38] >= hitA["t"][first["t"] < 3e38]).all()
+    # brute force: rays that hit the height-field instance (identity transform), all 10 M triangles each
+    hv, ht = b.meshes[0]
+    pick = np.where((hitB == 0) & (hitA["t"] < 3e38))[0][:12]
+    for i, (k, t) in zip(pick, _brute_force_hits(hv, ht, rays[pick])):
+        assert k == int(hitA["prim"][i]) and abs(t - hitA["t"][i]) <= 1e-5 * t, (i, k, t, hitA[i])
+    miss = np.where(hitA["t"] > 3e38)[0][:4]
+    for k, t in _brute_force_hits(hv, ht, rays[miss]):
+        assert k == -1
