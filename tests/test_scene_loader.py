@@ -1,0 +1,146 @@
+"""glTF / GLB ingestion (`scene_loader.Scene.Load`, the mirror of RD::Scene::Load, tools/sceneBuilder.cpp:27-315).
+
+CPU: the parsed descriptor arrays against arrays computed by the fixture writer; malformed containers fail loudly.
+GPU: the loaded scene rendered by programs/textured.cl against the same program on the reference runtime fed with
+the SAME parsed arrays, and the `<path>.cache` blob written in the reference's format read back."""
+import ctypes as C
+import json
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import gltf_fixture  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def asset(pkg, tmp_path_factory):
+    d = tmp_path_factory.mktemp("gltf")
+    doc, binary, expected = gltf_fixture.build_asset(pkg.scenes)
+    glb, gltf = str(d / "scene.glb"), str(d / "scene.gltf")
+    gltf_fixture.write_glb(glb, doc, binary)
+    gltf_fixture.write_gltf(gltf, doc, binary)
+    return {"glb": glb, "gltf": gltf, "doc": doc, "binary": binary, "expected": expected, "dir": d}
+
+
+def loader(pkg):
+    import importlib
+    return importlib.import_module("radiance_b200.scene_loader")
+
+
+def test_parse_glb_descriptor_arrays(pkg, asset):
+    sl, e = loader(pkg), asset["expected"]
+    for path in (asset["glb"], asset["gltf"]):
+        s = sl.parse_gltf(path)
+        assert len(s.meshes) == 3 and len(s.materials) == 3            # one mesh per primitive, +1 default material
+        vo = io = 0
+        for k, (v, t) in enumerate(e["meshes"]):
+            assert np.array_equal(s.meshes[k][0], v) and np.array_equal(s.meshes[k][1], t)
+            info = s.meshInfoPerMesh[k]
+            assert (info["vertexOffset"], info["indexOffset"], info["uvOffset"], info["normalOffset"]) == (vo * 3, io * 3, vo * 3, vo * 3)
+            assert info["materialIndex"] == e["mesh_material"][k]
+            assert np.array_equal(s.vertexData[vo:vo + len(v)], v)
+            assert np.array_equal(s.indexData[io:io + len(t)], t)           # mesh-local indices
+            assert np.allclose(s.normalData[vo:vo + len(v)], e["normals"][k], atol=2e-6)
+            assert np.array_equal(s.uvData[vo:vo + len(v)], e["uv"][k])     # stride 3, v flipped
+            vo, io = vo + len(v), io + len(t)
+        assert s.vertexData.shape == (vo, 3) and s.indexData.shape == (io, 3)
+        assert len(s.instances) == len(e["instances"]) == len(s.meshInfoData)
+        for k, inst in enumerate(s.instances):       # the table the shaders index by instanceIndex
+            assert s.meshInfoData[k] == s.meshInfoPerMesh[inst[0]]
+        for got, (mesh, tf, material) in zip(s.instances, e["instances"]):
+            assert got[0] == mesh and got[2] == 0 and got[3] == material
+            assert np.allclose(got[1], tf, atol=1e-6)
+        m = s.materials
+        assert m[0]["albedoTex"] == 0 and m[0]["metallicTex"] == -1 and m[0]["normalTex"] == -1
+        assert np.isclose(m[0]["roughness"], 0.7) and m[0]["metallic"] == 0
+        assert m[1]["albedoTex"] == -1 and np.allclose(m[1]["albedo"], [0.9, 0.3, 0.2, 1.0])
+        assert np.isclose(m[1]["transmission"], 0.25) and np.isclose(m[1]["ior"], 1.33)
+        assert np.allclose(m[2]["albedo"], 1.0) and m[2]["metallic"] == 1 and m[2]["roughness"] == 1 and np.isclose(m[2]["ior"], 1.45)
+        assert len(s.images) == 1
+        assert np.array_equal(sl.decode_texture(s.images[0], 16), e["pixels"])
+        big = sl.decode_texture(s.images[0], 64)
+        assert big.shape == (64, 64, 4) and big[..., 3].min() == 255
+
+
+def test_malformed_assets_fail_loudly(pkg, asset):
+    sl = loader(pkg)
+    d = asset["dir"]
+    raw = open(asset["glb"], "rb").read()
+    cases = {"short.glb": raw[: len(raw) // 2], "v1.glb": raw[:4] + (1).to_bytes(4, "little") + raw[8:]}
+    for name, data in cases.items():
+        p = str(d / name)
+        open(p, "wb").write(data)
+        with pytest.raises(sl.SceneFormatError):
+            sl.parse_gltf(p)
+
+    def variant(name, edit):
+        doc = json.loads(json.dumps(asset["doc"]))
+        edit(doc)
+        p = str(d / name)
+        gltf_fixture.write_glb(p, doc, asset["binary"])
+        return p
+    with pytest.raises(sl.SceneFormatError, match="mode"):
+        sl.parse_gltf(variant("lines.glb", lambda doc: doc["meshes"][0]["primitives"][0].update(mode=1)))
+    with pytest.raises(sl.SceneFormatError, match="past the end"):
+        sl.parse_gltf(variant("overrun.glb", lambda doc: doc["accessors"][0].update(count=100000)))
+    with pytest.raises(sl.SceneFormatError, match="cycle"):
+        sl.parse_gltf(variant("cycle.glb", lambda doc: doc["nodes"][1].update(children=[0])))
+    with pytest.raises(sl.SceneFormatError, match="index"):
+        sl.parse_gltf(variant("badindex.glb", lambda doc: doc["meshes"][1]["primitives"][0]["attributes"].update(POSITION=doc["meshes"][0]["primitives"][1]["attributes"]["POSITION"])))
+    with pytest.raises(sl.SceneFormatError, match="no mesh"):
+        sl.parse_gltf(variant("empty.glb", lambda doc: doc["scenes"][0].update(nodes=[])))
+
+
+@pytest.mark.gpu
+def test_loaded_scene_renders_like_reference_runtime(pkg, plt, ref, asset):
+    rd, scenes, sl = pkg.rd, pkg.scenes, loader(pkg)
+    tex_dim = 64
+    scene = sl.Scene.Load(asset["glb"], plt, tex_dim=tex_dim)
+    p = scene.parsed
+    assert os.path.getsize(asset["glb"] + ".cache") > 1000
+    w, h = 320, 240
+    cam = scenes.camera(w, h, (0.02, 0.9, 2.2), (-0.3, 0.0, 0.0))
+    light = scenes.scene_properties()
+    n = w * h
+
+    def buf(arr):
+        hnd = rd.CreateBuffer(plt, max(16, arr.nbytes))
+        rd.WriteBuffer(plt, hnd, arr.nbytes, arr)
+        return hnd
+    rt = np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1)
+    image = rd.CreateImage(plt, w, h)
+    head = [buf(rt), rd.CreateBuffer(plt, n * 16), image, buf(np.array(cam).reshape(1)), buf(np.array(light).reshape(1))]
+    pipe, _ = scenes.make_pipeline(plt, "textured")
+    rd.BindPipeline(plt, pipe)
+
+    def render(tlas):
+        ds = scene.descriptors()
+        ds[8] = tlas
+        rd.BindDescriptorSet(plt, rd.CreateDescriptorSet(head + ds))
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        out = np.zeros((h, w, 4), np.uint8)
+        rd.ReadBuffer(plt, image, out.nbytes, out)
+        return out
+    img = render(scene.topAccelStruct)
+    # the cache the loader wrote (reference blob format), read back: same picture
+    cached = sl.Scene.Load(asset["glb"], plt, loadFromCache=True, tex_dim=tex_dim)
+    assert np.array_equal(render(cached.topAccelStruct), img)
+
+    class Desc(C.Structure):
+        _fields_ = [("texels", C.c_void_p), ("width", C.c_uint), ("height", C.c_uint), ("layers", C.c_uint), ("pad", C.c_uint)]
+    texels = np.ascontiguousarray(np.stack([sl.decode_texture(e, tex_dim) for e in p.images]))
+    desc = Desc(texels.ctypes.data, tex_dim, tex_dim, len(p.images), 0)
+    sampler = rd.RD_ADDRESS_REPEAT | (rd.RD_FILTER_LINEAR << 16) | (1 << 32)
+    blas = [ref.RefBlas(v, t) for (v, t) in p.meshes]
+    tl = ref.RefTlas([(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in p.instances])
+    scratch, out = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
+    args = [rt, scratch, out, np.array(cam).reshape(1), np.array(light).reshape(1), p.meshInfoData, p.vertexData, p.indexData,
+            p.uvData, p.normalData, p.materials, C.addressof(desc), sampler, tl.blob]
+    ref.raygen("textured", args, n)
+    exp = out.reshape(h, w, 4)
+    d = img[..., :3].astype(np.float64) - exp[..., :3].astype(np.float64)
+    assert np.sqrt((d * d).mean()) <= 1.0, "RMSE %g" % np.sqrt((d * d).mean())
+    assert img[..., :3].std() > 20 and len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 500
