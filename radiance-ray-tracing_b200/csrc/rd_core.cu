@@ -34,7 +34,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     rd_platform* p = new rd_platform();
     p->device = device;
     p->boundModule = 0;
-    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0;
+    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 25;
     p->ilWorld = p->ilRank = p->ilBandRows = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
@@ -228,6 +228,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     else if (!strcmp(key, "wf_sort")) p->optWfSort = value;
     else if (!strcmp(key, "wf_dynamic")) p->optWfDynamic = value;
     else if (!strcmp(key, "wf_ray_sort")) p->optWfRaySort = value;
+    else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)
     else if (!strcmp(key, "stealing")) p->optSteal = value;
     else if (!strcmp(key, "max_trace_depth")) { if (value < 1 || value > 8) { rd_set_error("max_trace_depth must be in [1,8]"); return RD_E_ARG; } p->optMaxDepth = value; }
     else if (!strcmp(key, "block")) { if (value < 32 || value > 1024 || (value & 31)) { rd_set_error("block must be a multiple of 32 in [32,1024]"); return RD_E_ARG; } p->optBlock = value; }

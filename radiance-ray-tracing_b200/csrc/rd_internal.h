@@ -39,7 +39,7 @@ struct rd_blas {
 struct rd_module {
     CUmodule mod; CUfunction raygen;
     CUfunction stealRaygen;                      // persistent raygen with chunk stealing (option "stealing")
-    CUfunction wfGenerate, wfShade, wfResolve;   // 0 when the program has no wavefront hooks
+    CUfunction wfGenerate, wfShade, wfAccumulate, wfResolve;   // 0 when the program has no wavefront hooks
     unsigned wfPayloadSize; float wfRay[4];      // sizeof(struct Payload); sbtRecordOffset, missIndex, Tmin, Tmax
     int numRegs; int localBytes;
     std::string ptxInfo;
@@ -61,7 +61,7 @@ struct rd_platform {
     std::vector<int> boundKinds;
     rd_module* boundModule;
     std::string sbtJson;
-    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic, optWfRaySort;
+    long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic, optWfRaySort, optWfPaths;
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
@@ -103,7 +103,7 @@ struct RdWfState;
 int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride);
 void rd_wf_release(rd_platform* p);
 int rd_wf_upload_state(rd_platform* p, const RdWfState* host);
-int rd_wf_advance(rd_platform* p, unsigned op, unsigned a);
+int rd_wf_advance(rd_platform* p, unsigned op, unsigned a, unsigned b = 0u);
 int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch);
 int rd_wf_sort(rd_platform* p, unsigned count);
 int rd_wf_reorder_rays(rd_platform* p, const void* scene, unsigned count);

@@ -278,12 +278,13 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
     s += "extern \"C\" __global__ void rd_wf_generate(" + plist + "const RdWfState* wfp)\n{\n"
          "    const RdWfState wf = *wfp;\n"
          "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
-         "    if (slot >= wf.count) return;\n"
-         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + slot, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
+         "    if (slot >= wf.count * wf.samples) return;\n"
+         "    const unsigned sample = slot / wf.count, item = slot - sample * wf.count, frameID = wf.frameID + sample;\n"
+         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + item, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    struct SceneData sd; struct Payload pl;\n"
          "    wavefrontScene(&sd, " + names + ");\n"
-         "    sd.depth = 0; sd.frameID = wf.frameID;\n"
-         "    wavefrontPrimary(&pl, &sd, wf.frameID, wf.totalSamples);\n"
+         "    sd.depth = 0; sd.frameID = frameID;\n"
+         "    wavefrontPrimary(&pl, &sd, frameID, wf.totalSamples);\n"
          "    pl.hit = false;\n"
          "    *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride) = pl;\n"
          "    RdF4 a, b, one, zero;\n"
@@ -292,7 +293,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    one.x = one.y = one.z = one.w = 1.0f; zero.x = zero.y = zero.z = zero.w = 0.0f;\n"
          "    wf.rayA[wf.cur][slot] = a; wf.rayB[wf.cur][slot] = b; wf.pathOf[wf.cur][slot] = slot;\n"
          "    wf.color[slot] = zero; wf.contrib[slot] = one;\n"
-         "    if (slot == 0) { wf.counts[wf.cur] = wf.count; wf.counts[wf.cur ^ 1u] = 0u; }\n"
+         "    if (slot == 0) { wf.counts[wf.cur] = wf.count * wf.samples; wf.counts[wf.cur ^ 1u] = 0u; }\n"
          "}\n\n";
     s += "extern \"C\" __global__ void rd_wf_shade(" + plist + "const RdWfState* wfp)\n{\n"
          "    const RdWfState wf = *wfp;\n"
@@ -301,11 +302,11 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    if (jj >= n) return;\n"
          "    const unsigned j = wf.sortOn ? wf.order[jj] : jj;\n"
          "    const unsigned slot = wf.pathOf[wf.cur][j];\n"
-         "    const unsigned gid = rd_wf_global_id(wf.first + slot, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
-         "    rd_wf_gid[threadIdx.x] = gid;\n"
+         "    const unsigned sample = slot / wf.count, item = slot - sample * wf.count;\n"
+         "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + item, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    struct SceneData sd;\n"
          "    wavefrontScene(&sd, " + names + ");\n"
-         "    sd.depth = wf.depth; sd.frameID = wf.frameID;\n"
+         "    sd.depth = wf.depth; sd.frameID = wf.frameID + sample;\n"
          "    struct Payload pl = *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride);\n"
          "    const RdF4 ha = wf.hitA[j];\n"
          "    if (ha.x < RD_MISS_T) {\n"
@@ -346,15 +347,28 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "        *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride) = pl;\n"
          "        wf.color[slot] = col; wf.contrib[slot] = con;\n"
          "    } else {\n"
-         "        // the sample is complete: running mean of samples/shader.cl:262-279\n"
-         "        float* px = (float*)" + P[1].name + " + 4 * (size_t)gid;\n"
-         "        if (wf.frameID == 0) { px[0] = col.x; px[1] = col.y; px[2] = col.z; }\n"
+         "        wf.color[slot] = col;   // the sample is complete; the accumulate stage folds it into imageScratch in frame order\n"
+         "    }\n"
+         "}\n\n";
+    // running mean of samples/shader.cl:262-279 over the samples of this pass, in frame order
+    s += "extern \"C\" __global__ void rd_wf_accumulate(" + plist + "const RdWfState* wfp)\n{\n"
+         "    const RdWfState wf = *wfp;\n"
+         "    const unsigned item = blockIdx.x * blockDim.x + threadIdx.x;\n"
+         "    if (item >= wf.count) return;\n"
+         "    const unsigned gid = rd_wf_global_id(wf.first + item, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
+         "    float* px = (float*)" + P[1].name + " + 4 * (size_t)gid;\n"
+         "    float r = px[0], g = px[1], b = px[2];\n"
+         "    for (unsigned k = 0; k < wf.samples; ++k) {\n"
+         "        const RdF4 col = wf.color[(size_t)k * wf.count + item];\n"
+         "        const unsigned frameID = wf.frameID + k;\n"
+         "        if (frameID == 0) { r = col.x; g = col.y; b = col.z; }\n"
          "        else {\n"
-         "            px[0] = (wf.frameID * px[0] + col.x) / (wf.frameID + 1);\n"
-         "            px[1] = (wf.frameID * px[1] + col.y) / (wf.frameID + 1);\n"
-         "            px[2] = (wf.frameID * px[2] + col.z) / (wf.frameID + 1);\n"
+         "            r = (frameID * r + col.x) / (frameID + 1);\n"
+         "            g = (frameID * g + col.y) / (frameID + 1);\n"
+         "            b = (frameID * b + col.z) / (frameID + 1);\n"
          "        }\n"
          "    }\n"
+         "    px[0] = r; px[1] = g; px[2] = b;\n"
          "}\n\n";
     s += "extern \"C\" __global__ void rd_wf_resolve(" + plist + "const RdWfState* wfp)\n{\n"
          "    const RdWfState wf = *wfp;\n"
@@ -564,9 +578,10 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     m->stealRaygen = 0;
     if (p->optSteal && cuModuleGetFunction(&m->stealRaygen, m->mod, "rd_raygen_steal") != CUDA_SUCCESS) m->stealRaygen = 0;
     // wavefront stages exist when the program defines the hooks (generate_wavefront_kernels)
-    m->wfGenerate = m->wfShade = m->wfResolve = 0; m->wfPayloadSize = 0;
+    m->wfGenerate = m->wfShade = m->wfAccumulate = m->wfResolve = 0; m->wfPayloadSize = 0;
     if (cuModuleGetFunction(&m->wfGenerate, m->mod, "rd_wf_generate") == CUDA_SUCCESS &&
         cuModuleGetFunction(&m->wfShade, m->mod, "rd_wf_shade") == CUDA_SUCCESS &&
+        cuModuleGetFunction(&m->wfAccumulate, m->mod, "rd_wf_accumulate") == CUDA_SUCCESS &&
         cuModuleGetFunction(&m->wfResolve, m->mod, "rd_wf_resolve") == CUDA_SUCCESS) {
         // sizeof(struct Payload) and the WAVEFRONT_* ray constants are known to the compiled program only
         CUfunction query = 0; float* dq = 0; float hq[5] = {0, 0, 0, 0, 0};
@@ -641,7 +656,14 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     RD_CUDA(cudaMemcpyAsync(rt, (const void*)p->boundArgs[0], 16, cudaMemcpyDeviceToHost, p->stream));
     RD_CUDA(cudaStreamSynchronize(p->stream));
     const unsigned stride = (m->wfPayloadSize + 15u) & ~15u;
-    int rc = rd_wf_reserve(p, (unsigned)count, stride);
+    // samples in flight per pass: as many as option wf_paths allows (HBM: ~200 B per path)
+    unsigned long long inFlight = (unsigned long long)p->optWfPaths / count;
+    if (inFlight < 1) inFlight = 1;
+    if (inFlight > rt[1]) inFlight = rt[1] ? rt[1] : 1;
+    if (rt[3]) inFlight = 1;                       // debug views stop after one bounce of one sample at a time
+    while (inFlight * count > 0x7fffffffull) --inFlight;
+    const unsigned paths = (unsigned)(inFlight * count);
+    int rc = rd_wf_reserve(p, paths, stride);
     if (rc) return rc;
     // the scene header is whichever descriptor is a top-level structure
     const void* scene = 0;
@@ -654,7 +676,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     S.hitA = (RdF4*)B.hitA; S.hitB = B.hitB; S.keys = B.keys; S.order = B.order; S.counts = B.counts; S.hist = B.hist;
     S.payloadStride = stride; S.cur = 0; S.first = (unsigned)first; S.count = (unsigned)count; S.total = total;
     S.tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
-    S.frameID = rt[0]; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
+    S.frameID = rt[0]; S.samples = 1; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
     S.ilWorld = p->ilWorld; S.ilRank = p->ilRank; S.ilBandRows = p->ilBandRows ? p->ilBandRows : 1u;
     S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
     rc = rd_wf_upload_state(p, &S);
@@ -668,20 +690,24 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     std::vector<void*> argv(args.size());
     for (size_t i = 0; i < argv.size(); ++i) argv[i] = &args[i];
     const unsigned blocks = (unsigned)((count + 127) / 128);
-    for (unsigned k = 0; k < rt[1]; ++k) {
-        rc = rd_wf_advance(p, 0u, rt[0] + k); if (rc) return rc;
-        RD_CU(cuLaunchKernel(m->wfGenerate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+    for (unsigned k = 0; k < rt[1]; k += (unsigned)inFlight) {
+        const unsigned samples = rt[1] - k < (unsigned)inFlight ? rt[1] - k : (unsigned)inFlight;
+        const unsigned live = samples * (unsigned)count, pathBlocks = (live + 127u) / 128u;
+        rc = rd_wf_advance(p, 0u, rt[0] + k, samples); if (rc) return rc;
+        RD_CU(cuLaunchKernel(m->wfGenerate, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
         for (unsigned d = 0; d < rt[2]; ++d) {
-            if (d > 0 && p->optWfRaySort) { rc = rd_wf_reorder_rays(p, scene, (unsigned)count); if (rc) return rc; }
+            if (d > 0 && p->optWfRaySort) { rc = rd_wf_reorder_rays(p, scene, live); if (rc) return rc; }
             // primary rays are coherent (static batches); bounce rays are not (dynamic fetch), option wf_dynamic: 0 never, 1 bounces, 2 always
             rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) return rc;
-            if (S.sortOn) { rc = rd_wf_sort(p, (unsigned)count); if (rc) return rc; }
-            RD_CU(cuLaunchKernel(m->wfShade, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+            if (S.sortOn) { rc = rd_wf_sort(p, live); if (rc) return rc; }
+            RD_CU(cuLaunchKernel(m->wfShade, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
             p->launches += 1;
             rc = rd_wf_advance(p, 2u, 0u); if (rc) return rc;
             if (rt[3]) break;
         }
+        RD_CU(cuLaunchKernel(m->wfAccumulate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+        p->launches += 1;
     }
     RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
     p->launches += 1;

@@ -64,7 +64,8 @@ __device__ __forceinline__ void rd_wf_store_hit(const RdScene* scene, const RdWf
     wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
 }
 
-__global__ void __launch_bounds__(128, 7) rd_k_wf_trace_dyn(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
+template <int MINB>
+__global__ void __launch_bounds__(128, MINB) rd_k_wf_trace_dyn(const RdScene* __restrict__ scene, const RdWfState* __restrict__ wfp)
 {
     const RdWfState wf = *wfp;
     const unsigned n = wf.counts[wf.cur];
@@ -220,7 +221,7 @@ __global__ void rd_k_wf_ray_scatter(const RdWfState* __restrict__ wfp)
 __global__ void rd_k_wf_advance(RdWfState* wf, unsigned op, unsigned a, unsigned b)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    if (op == 0) { wf->frameID = a; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; }                    // new sample
+    if (op == 0) { wf->frameID = a; wf->samples = b; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; }   // new pass: first frame id, samples in flight
     else if (op == 1) { wf->counts[2] = 0; }                                                           // before trace
     else if (op == 3) { const unsigned n = wf->counts[wf->cur]; wf->counts[wf->cur] = 0; wf->cur ^= 1u; wf->counts[wf->cur] = n; }   // after a ray reorder
     else if (op == 2) { wf->cur ^= 1u; wf->counts[wf->cur ^ 1u] = 0; wf->depth += 1; wf->counts[2] = 0; } // after shade
@@ -266,9 +267,9 @@ int rd_wf_upload_state(rd_platform* p, const RdWfState* host)
     return RD_OK;
 }
 
-int rd_wf_advance(rd_platform* p, unsigned op, unsigned a)
+int rd_wf_advance(rd_platform* p, unsigned op, unsigned a, unsigned b)
 {
-    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, op, a, 0u);
+    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, op, a, b);
     p->launches += 1;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
@@ -276,8 +277,17 @@ int rd_wf_advance(rd_platform* p, unsigned op, unsigned a)
 
 int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
 {
-    if (dynamicFetch)
-        rd_k_wf_trace_dyn<<<(unsigned)p->smCount * 6u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+    if (dynamicFetch) {
+        static int perSm = -1, minb = 7;
+        if (perSm < 0) {
+            const char* e = getenv("RD_WF_BLOCKS_PER_SM"); perSm = e ? atoi(e) : 6;
+            const char* m = getenv("RD_WF_MINB"); minb = m ? atoi(m) : 7;
+        }
+        if (minb >= 8)
+            rd_k_wf_trace_dyn<8><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+        else
+            rd_k_wf_trace_dyn<7><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+    }
     else
         rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
     p->launches += 1;

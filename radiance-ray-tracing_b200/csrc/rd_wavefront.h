@@ -3,9 +3,13 @@
 //
 // Wavefront mode runs the sample loop and the bounce loop that the reference spells out inside its
 // raygen kernel (samples/shader.cl:196-281) as a sequence of stage launches over queues in HBM:
-//   generate -> [ trace -> sort by hit group / material -> shade ] x depth -> (next sample) -> resolve
-// A path owns one slot (its launch-local work-item index); the user's `struct Payload` lives in the
-// payload array of that slot between stages. Ray / hit queues are structure-of-arrays, 16-byte
+//   [ generate -> [ trace -> sort by hit group / material -> shade ] x depth -> accumulate ] x passes -> resolve
+// A pass carries `samples` samples of every work-item at once (option wf_paths caps paths in flight;
+// HBM holds tens of millions of paths, and the number of stage launches -- each of which ends with the
+// tail of its longest rays -- shrinks by that factor). A path owns one slot = sample * count +
+// launch-local work-item index; the user's `struct Payload` lives in the payload array of that slot
+// between stages. Finished samples stay in `color` and are folded into imageScratch in frame order
+// by the accumulate stage, so the running mean is the same float sequence as the reference's loop. Ray / hit queues are structure-of-arrays, 16-byte
 // records, compacted every bounce (only live paths are traced and shaded).
 #ifndef RD_WAVEFRONT_H
 #define RD_WAVEFRONT_H
@@ -34,7 +38,8 @@ struct RD_ALIGN(16) RdWfState {
     rd_u32 frameID, totalSamples; // sample being traced, RTProp->totalSamples
     rd_u32 depth, maxDepth;       // bounce index of this stage, RTProp->depth
     rd_u32 debug, sortOn;
-    rd_u32 ilWorld, ilRank, ilBandRows, pad0;   // interleaved multi-GPU partition (0 = whole frame), see rd_trace_rays_interleaved
+    rd_u32 ilWorld, ilRank, ilBandRows;   // interleaved multi-GPU partition (0 = whole frame), see rd_trace_rays_interleaved
+    rd_u32 samples;               // samples in flight in this pass: path slot = sample * count + work-item, frame id = frameID + sample
     int sbtRecordOffset, missIndex;
     float tmin, tmax;
 };

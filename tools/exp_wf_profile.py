@@ -24,7 +24,9 @@ rd.BindDescriptorSet(plt, ds.descriptors)
 plt.set_option("wavefront", 1)
 plt.set_option("wf_sort", sort)
 plt.set_option("wf_dynamic", int(os.environ.get("RD_WF_DYNAMIC", "1")))
-plt.set_option("wf_ray_sort", int(os.environ.get("RD_WF_RAYSORT", "1")))
+plt.set_option("wf_ray_sort", int(os.environ.get("RD_WF_RAYSORT", "0")))
+if "RD_WF_PATHS" in os.environ:
+    plt.set_option("wf_paths", int(os.environ["RD_WF_PATHS"]))
 import time
 for _ in range(3):
     ds.set_rtprop(0, spp, depth)
