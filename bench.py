@@ -186,15 +186,17 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
     out = {"workload": name, "triangles": bundle.triangle_count(), "instances": len(bundle.instances), "spp": spp, "depth": depth,
            "rays_per_frame": rays, "build_ms_incl_upload": build_ms, "unit": "Mrays/s"}
     try:
-        for mode, wf, srt in modes:
+        for mode, wf, srt, paths in modes:
             plt.set_option("wavefront", wf)
             plt.set_option("wf_sort", srt)
+            plt.set_option("wf_paths", paths)
             l0 = plt.launch_count()
             ms = time_frames(torch, plt, rd, stream, flush, WIDTH, HEIGHT)
             out[mode] = {"value": rays / ms / 1e3, "ms_per_frame": ms, "launches_per_frame": (plt.launch_count() - l0) // 4}
     finally:
         plt.set_option("wavefront", 0)
         plt.set_option("wf_sort", 1)
+        plt.set_option("wf_paths", 1 << 25)
     for h in [tlas] + list(blas):
         h.free()
     return out
@@ -455,7 +457,9 @@ def main():
         if world == 1 and not args.no_extra:
             # the path-tracing half of the metric ("primary + 4-bounce path"): BASELINE configs[2] (and configs[3]
             # with --extra all), wavefront mode against the inline raygen kernel of the same program
-            modes = (("inline", 0, 1), ("wavefront_sorted", 1, 1), ("wavefront_unsorted", 1, 0))
+            inflight = 1 << 25   # paths in flight per wavefront pass (all 16 samples of a 1080p frame); 1 = one sample per pass
+            modes = (("inline", 0, 1, inflight), ("wavefront_sorted", 1, 1, inflight), ("wavefront_unsorted", 1, 0, inflight),
+                     ("wavefront_sorted_one_sample_per_pass", 1, 1, 1))
             out["extra"] = {}
             try:
                 out["extra"]["C3"] = extra_config(torch, pkg, plt, stream, flush,

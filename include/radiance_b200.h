@@ -182,7 +182,10 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wf_dynamic" (0 never / 1 bounce stages (default) / 2 always: dynamic ray fetch in the wavefront trace stage),
  * "wf_ray_sort" (0/1, default 0: re-sort bounce rays by direction octant and origin cell before tracing them;
  * measured slower on C3 -- the pass costs more than the trace stage gains),
- * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading) */
+ * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading),
+ * "wf_paths" (default 2^25: paths in flight per wavefront pass -- RTProp.batchSize samples of every work-item are
+ * generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path; 1 = one sample
+ * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */

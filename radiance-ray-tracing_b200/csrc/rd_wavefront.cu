@@ -280,7 +280,7 @@ int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
     if (dynamicFetch) {
         static int perSm = -1, minb = 7;
         if (perSm < 0) {
-            const char* e = getenv("RD_WF_BLOCKS_PER_SM"); perSm = e ? atoi(e) : 6;
+            const char* e = getenv("RD_WF_BLOCKS_PER_SM"); perSm = e ? atoi(e) : 7;
             const char* m = getenv("RD_WF_MINB"); minb = m ? atoi(m) : 7;
         }
         if (minb >= 8)
