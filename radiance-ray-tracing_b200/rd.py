@@ -11,7 +11,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libradiance_b200.so")
+LIB_PATH = os.environ.get("RADIANCE_B200_LIB") or os.path.join(_HERE, "libradiance_b200.so")   # developer knob: ablation builds
 
 RD_ADDRESS_CLAMP_TO_EDGE, RD_ADDRESS_CLAMP, RD_ADDRESS_REPEAT, RD_ADDRESS_MIRRORED_REPEAT = 0x1131, 0x1132, 0x1133, 0x1134
 RD_FILTER_NEAREST, RD_FILTER_LINEAR = 0x1140, 0x1141
