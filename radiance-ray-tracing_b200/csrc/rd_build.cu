@@ -1,8 +1,10 @@
-// rd_build.cu -- GPU acceleration-structure build: LBVH (Morton -> radix sort -> Karras -> refit)
-// followed by a level-synchronous collapse into 8-wide quantised nodes. Replaces the host SAH
+// rd_build.cu -- GPU acceleration-structure build: Morton codes -> radix sort -> binary hierarchy by
+// parallel locally-ordered clustering (PLOC; Karras' LBVH + refit kept as option) -> SAH-optimal
+// level-synchronous collapse into 8-wide quantised nodes. Replaces the host SAH
 // builder of the reference (radiance/src/bvh.cpp:46-597) and its blob packers
 // (radiance/src/radiance.cpp:318-425). The per-element logic lives in rd_build.h.
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 #include <float.h>
 #include <string.h>
 #include <stdlib.h>
@@ -91,6 +93,79 @@ __global__ void rd_k_refit(RdBinTree T)
     if (i < T.n) rd_refit_from_leaf(T, i);
 }
 
+
+// ---- PLOC: parallel locally-ordered clustering (Meister & Bittner 2018) ---------------------------
+// The clusters start as the primitives in Morton order. Every round each cluster looks at its
+// RD_PLOC radius neighbours on either side in the array and picks the one with which its merged box
+// has the smallest surface area; pairs that pick each other merge into a new inner node that takes the
+// left partner's place; the array is compacted in order. Unlike the Karras tree, whose topology is
+// fixed by the Morton bits, merges are chosen by surface area, which is what the SAH counts.
+// Inner node ids are handed out downwards from n-2 so that the last merge is node 0, the root.
+// Boxes, primitive counts and the collapse DP costs of a new node are final when it is created (its
+// children are older), so no refit pass is needed.
+struct RdPlocSide { rd_u32* ref; RdF4* lo; RdF4* hi; };
+
+__global__ void rd_k_ploc_init(RdBinTree T, RdPlocSide A)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= T.n) return;
+    A.ref[i] = RD_BIN_LEAF | i;
+    A.lo[i] = T.lo[T.n - 1 + i];
+    A.hi[i] = T.hi[T.n - 1 + i];
+}
+
+__global__ void rd_k_ploc_nearest(RdPlocSide A, rd_u32 m, int radius, rd_u32* nearest)
+{
+    const rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const RdF4 l = A.lo[i], h = A.hi[i];
+    const int j0 = (int)i - radius < 0 ? 0 : (int)i - radius;
+    const int j1 = (int)i + radius >= (int)m ? (int)m - 1 : (int)i + radius;
+    float best = 3.0e38f; rd_u32 bj = i;
+    for (int j = j0; j <= j1; ++j) {
+        if (j == (int)i) continue;
+        const RdF4 a = A.lo[j], b = A.hi[j];
+        const float ex = fmaxf(h.x, b.x) - fminf(l.x, a.x), ey = fmaxf(h.y, b.y) - fminf(l.y, a.y),
+                    ez = fmaxf(h.z, b.z) - fminf(l.z, a.z);
+        const float area = ex * ey + ey * ez + ez * ex;
+        // the same pair must score the same from both ends and ties must resolve the same way for a merge to be
+        // mutual: area is symmetric, ties go to the lower index
+        if (area < best) { best = area; bj = (rd_u32)j; }
+    }
+    nearest[i] = bj;
+}
+
+__global__ void rd_k_ploc_merge(RdBinTree T, RdPlocSide A, rd_u32 m, const rd_u32* nearest, rd_u32* nextId, rd_u32* keep)
+{
+    const rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const rd_u32 j = nearest[i];
+    if (j == i || nearest[j] != i) { keep[i] = 1u; return; }
+    if (j < i) { keep[i] = 0u; return; }          // the right partner disappears
+    const rd_u32 id = atomicSub(nextId, 1u) - 1u;
+    const rd_u32 L = A.ref[i], R = A.ref[j];
+    const RdF4 la = A.lo[i], ha = A.hi[i], lb = A.lo[j], hb = A.hi[j];
+    RdF4 l, h;
+    l.x = fminf(la.x, lb.x); l.y = fminf(la.y, lb.y); l.z = fminf(la.z, lb.z); l.w = 0.0f;
+    h.x = fmaxf(ha.x, hb.x); h.y = fmaxf(ha.y, hb.y); h.z = fmaxf(ha.z, hb.z); h.w = 0.0f;
+    T.left[id] = L; T.right[id] = R;
+    T.parent[rd_bin_slot(T, L)] = id; T.parent[rd_bin_slot(T, R)] = id;
+    if (id == 0u) T.parent[0] = RD_INVALID;
+    T.lo[id] = l; T.hi[id] = h;
+    T.count[id] = ((L & RD_BIN_LEAF) ? 1u : T.count[L]) + ((R & RD_BIN_LEAF) ? 1u : T.count[R]);
+    if (T.cost) rd_dp_node(T, id, l, h);
+    A.ref[i] = id; A.lo[i] = l; A.hi[i] = h;
+    keep[i] = 1u;
+}
+
+__global__ void rd_k_ploc_compact(RdPlocSide A, RdPlocSide B, rd_u32 m, const rd_u32* keep, const rd_u32* pos, rd_u32* outCount)
+{
+    const rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    if (keep[i]) { const rd_u32 k = pos[i]; B.ref[k] = A.ref[i]; B.lo[k] = A.lo[i]; B.hi[k] = A.hi[i]; }
+    if (i == m - 1) *outCount = pos[i] + keep[i];
+}
+
 __global__ void rd_k_collapse(RdBinTree T, RdCollapseOut O, const RdCollapseItem* items, rd_u32 count)
 {
     rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -152,7 +227,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     T.n = n; T.keys = keysB; T.prim = valsB;
     RD_CUDA(tmp.alloc(&T.left, ni)); RD_CUDA(tmp.alloc(&T.right, ni));
     RD_CUDA(tmp.alloc(&T.first, ni)); RD_CUDA(tmp.alloc(&T.last, ni));
-    RD_CUDA(tmp.alloc(&T.parent, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.arrive, ni));
+    RD_CUDA(tmp.alloc(&T.parent, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.arrive, ni)); RD_CUDA(tmp.alloc(&T.count, ni));
     RD_CUDA(tmp.alloc(&T.lo, 2 * (size_t)n)); RD_CUDA(tmp.alloc(&T.hi, 2 * (size_t)n));
     T.cost = 0; T.dec = 0;
     if (!getenv("RD_BUILD_GREEDY")) {   // developer knob: greedy collapse instead of the SAH dynamic program
@@ -162,10 +237,40 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     rd_k_leaf_boxes<<<rd_grid(n), RD_BT, 0, st>>>(T, dlo, dhi);
     p->launches += 1;
     RdCollapseItem rootItem; rootItem.wide = 0; rootItem.bin = (n == 1) ? (RD_BIN_LEAF | 0u) : 0u;
-    if (n > 1) {
+    if (n > 1 && getenv("RD_BUILD_LBVH")) {   // developer knob: Karras' LBVH topology instead of PLOC
         rd_k_karras<<<rd_grid(n - 1), RD_BT, 0, st>>>(T);
         rd_k_refit<<<rd_grid(n), RD_BT, 0, st>>>(T);
         p->launches += 2;
+    } else if (n > 1) {
+        int radius = 16;
+        if (const char* e = getenv("RD_PLOC_RADIUS")) { radius = atoi(e); if (radius < 1) radius = 1; }
+        RdPlocSide A, B;
+        RD_CUDA(tmp.alloc(&A.ref, n)); RD_CUDA(tmp.alloc(&A.lo, n)); RD_CUDA(tmp.alloc(&A.hi, n));
+        RD_CUDA(tmp.alloc(&B.ref, n)); RD_CUDA(tmp.alloc(&B.lo, n)); RD_CUDA(tmp.alloc(&B.hi, n));
+        rd_u32 *nearest, *keep, *pos, *pc;
+        RD_CUDA(tmp.alloc(&nearest, n)); RD_CUDA(tmp.alloc(&keep, n)); RD_CUDA(tmp.alloc(&pos, n)); RD_CUDA(tmp.alloc(&pc, 4));
+        size_t scanBytes = 0;
+        cub::DeviceScan::ExclusiveSum(0, scanBytes, keep, pos, (int)n, st);
+        char* dscan;
+        RD_CUDA(tmp.alloc(&dscan, scanBytes));
+        const rd_u32 pc0[2] = {n - 1u, n};   // [0] next inner id + 1 (ids are handed out downwards), [1] clusters
+        RD_CUDA(cudaMemcpyAsync(pc, pc0, sizeof(pc0), cudaMemcpyHostToDevice, st));
+        rd_k_ploc_init<<<rd_grid(n), RD_BT, 0, st>>>(T, A);
+        p->launches += 1;
+        rd_u32 m = n, rounds = 0;
+        while (m > 1) {
+            rd_k_ploc_nearest<<<rd_grid(m), RD_BT, 0, st>>>(A, m, radius, nearest);
+            rd_k_ploc_merge<<<rd_grid(m), RD_BT, 0, st>>>(T, A, m, nearest, pc, keep);
+            RD_CUDA(cub::DeviceScan::ExclusiveSum(dscan, scanBytes, keep, pos, (int)m, st));
+            rd_k_ploc_compact<<<rd_grid(m), RD_BT, 0, st>>>(A, B, m, keep, pos, pc + 1);
+            p->launches += 3;
+            rd_u32 next = 0;
+            RD_CUDA(cudaMemcpyAsync(&next, pc + 1, sizeof(next), cudaMemcpyDeviceToHost, st));
+            RD_CUDA(cudaStreamSynchronize(st));
+            if (next >= m || next == 0 || ++rounds > 100000u) { rd_set_error("rd_build_wide_bvh: clustering made no progress (%u -> %u clusters)", m, next); return RD_E_CUDA; }
+            m = next;
+            RdPlocSide t = A; A = B; B = t;
+        }
     }
     // collapse, one launch per level of the wide tree
     RdNode8* wide; rd_u32* counters; RdCollapseItem *itemsA, *itemsB;

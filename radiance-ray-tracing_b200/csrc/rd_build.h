@@ -30,7 +30,7 @@ static inline rd_u32 rd_host_atomic_add_(rd_u32* p, rd_u32 v) { rd_u32 o = *p; *
 #define RD_LEAF_MAX 3            // primitives per leaf slot (unary count in 3 meta bits)
 #define RD_BIN_LEAF 0x80000000u  // binary child reference: top bit = leaf, low bits = sorted position
 
-// Binary (Karras) hierarchy over n sorted primitives: n-1 inner nodes [0, n-2], node 0 = root.
+// Binary hierarchy over n sorted primitives (Karras 2012 or PLOC, rd_build.cu): n-1 inner nodes [0, n-2], node 0 = root.
 struct RdBinTree {
     rd_u32 n;               // primitives
     const rd_u64* keys;     // sorted Morton codes
@@ -41,6 +41,7 @@ struct RdBinTree {
     rd_u32* last;           // [n-1]
     rd_u32* parent;         // [2n-1] parent inner node of inner i (slot i) / leaf pos (slot n-1+pos)
     rd_u32* arrive;         // [n-1] refit arrival counters (zeroed)
+    rd_u32* count;          // [n-1] primitives below inner node i (subtrees need not be contiguous in sorted order: PLOC)
     RdF4* lo;               // [2n-1] boxes: inner i -> slot i, leaf pos -> slot n-1+pos
     RdF4* hi;
     float* cost;            // [8(n-1)] cost[8i + k-1] = SAH cost of subtree i laid out in at most k slots of its parent
@@ -160,7 +161,7 @@ RD_HD void rd_dp_node(const RdBinTree& T, rd_u32 cur, const RdF4& l, const RdF4&
         dist[j] = best; split[j] = bi;
     }
     const float A = rd_half_area(l, h);
-    const rd_u32 prims = T.last[cur] - T.first[cur] + 1u;
+    const rd_u32 prims = T.count[cur];
     const float cLeaf = prims <= RD_LEAF_MAX ? A * (float)prims * RD_SAH_PRIM : inf;
     const float cNode = A * RD_SAH_NODE + dist[8];
     float* outc = T.cost + 8u * (size_t)cur;
@@ -196,6 +197,15 @@ RD_HD void rd_refit_from_leaf(const RdBinTree& T, rd_u32 pos)
         l.x = fminf(la.x, lb.x); l.y = fminf(la.y, lb.y); l.z = fminf(la.z, lb.z); l.w = 0.0f;
         h.x = fmaxf(ha.x, hb.x); h.y = fmaxf(ha.y, hb.y); h.z = fmaxf(ha.z, hb.z); h.w = 0.0f;
         T.lo[cur] = l; T.hi[cur] = h;
+        {
+#ifdef __CUDA_ARCH__
+            const volatile rd_u32* vc = (const volatile rd_u32*)T.count;
+#else
+            const rd_u32* vc = T.count;
+#endif
+            const rd_u32 L = T.left[cur], R = T.right[cur];
+            T.count[cur] = ((L & RD_BIN_LEAF) ? 1u : vc[L]) + ((R & RD_BIN_LEAF) ? 1u : vc[R]);
+        }
         if (T.cost) rd_dp_node(T, cur, l, h);
         cur = T.parent[cur];
     }
@@ -203,11 +213,7 @@ RD_HD void rd_refit_from_leaf(const RdBinTree& T, rd_u32 pos)
 
 RD_HD rd_u32 rd_bin_count(const RdBinTree& T, rd_u32 ref)
 {
-    return (ref & RD_BIN_LEAF) ? 1u : (T.last[ref] - T.first[ref] + 1u);
-}
-RD_HD rd_u32 rd_bin_first(const RdBinTree& T, rd_u32 ref)
-{
-    return (ref & RD_BIN_LEAF) ? (ref & ~RD_BIN_LEAF) : T.first[ref];
+    return (ref & RD_BIN_LEAF) ? 1u : T.count[ref];
 }
 
 struct RdCollapseItem { rd_u32 wide, bin; };   // wide node index <- binary subtree reference
@@ -341,9 +347,16 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
             O.next[nextBase + innerRank] = nx;
             innerRank++;
         } else {
-            const rd_u32 cnt = rd_bin_count(T, c), first = rd_bin_first(T, c);
+            const rd_u32 cnt = rd_bin_count(T, c);
             meta[s] = (rd_u8)((((1u << cnt) - 1u) << 5) | leafOff);
-            for (rd_u32 j = 0; j < cnt; ++j) O.leafPrim[primBase + leafOff + j] = T.prim[first + j];
+            // the <= RD_LEAF_MAX primitives of the subtree, left to right
+            rd_u32 walk[RD_LEAF_MAX + 1]; int wp = 0; rd_u32 j = 0;
+            walk[wp++] = c;
+            while (wp > 0) {
+                const rd_u32 r = walk[--wp];
+                if (r & RD_BIN_LEAF) { O.leafPrim[primBase + leafOff + j] = T.prim[r & ~RD_BIN_LEAF]; ++j; }
+                else { walk[wp++] = T.right[r]; walk[wp++] = T.left[r]; }
+            }
             leafOff += cnt;
         }
     }

@@ -44,11 +44,11 @@ static void emu_build(const std::vector<RdF4>& plo, const std::vector<RdF4>& phi
     std::vector<rd_u64> keys(n); std::vector<rd_u32> prim(n);
     for (rd_u32 i = 0; i < n; ++i) { keys[i] = kv[i].first; prim[i] = kv[i].second; }
     const rd_u32 ni = n > 1 ? n - 1 : 1;
-    std::vector<rd_u32> left(ni), right(ni), first(ni), last(ni), parent(2 * n), arrive(ni, 0);
+    std::vector<rd_u32> left(ni), right(ni), first(ni), last(ni), parent(2 * n), arrive(ni, 0), count(ni, 0);
     std::vector<RdF4> lo(2 * n), hi(2 * n);
     std::vector<float> cost(8 * (size_t)ni); std::vector<rd_u8> dec(8 * (size_t)ni);
     RdBinTree T; T.cost = cost.data(); T.dec = dec.data(); T.n = n; T.keys = keys.data(); T.prim = prim.data(); T.left = left.data(); T.right = right.data();
-    T.first = first.data(); T.last = last.data(); T.parent = parent.data(); T.arrive = arrive.data(); T.lo = lo.data(); T.hi = hi.data();
+    T.first = first.data(); T.last = last.data(); T.parent = parent.data(); T.arrive = arrive.data(); T.count = count.data(); T.lo = lo.data(); T.hi = hi.data();
     for (rd_u32 i = 0; i < n; ++i) { lo[n - 1 + i] = plo[prim[i]]; hi[n - 1 + i] = phi[prim[i]]; }
     RdCollapseItem rootItem; rootItem.wide = 0;
     if (n == 1) { rootItem.bin = RD_BIN_LEAF | 0u; }

@@ -18,8 +18,13 @@ n_grid = int(sys.argv[1]) if len(sys.argv) > 1 else 708
 plt = rd.Platform.GetPlatform(0)
 stream = torch.cuda.ExternalStream(plt.stream(), device=0)
 bundle = scenes.heightfield_scene(n_grid, W, H)
+import time
 tlas, blas = scenes.build_scene(plt, bundle)
-print("bvh", blas[0].stats(), flush=True)
+plt.sync()
+t0 = time.perf_counter()
+tlas, blas = scenes.build_scene(plt, bundle)
+plt.sync()
+print("bvh", blas[0].stats(), "build_ms(2nd, incl upload) %.1f" % ((time.perf_counter() - t0) * 1e3), flush=True)
 ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, int(os.environ.get('RD_EXP_SPP', '1')), int(os.environ.get('RD_EXP_DEPTH', '1')), 0))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 VARIANTS = json.loads(os.environ.get("RD_EXP_VARIANTS", "null")) or [
