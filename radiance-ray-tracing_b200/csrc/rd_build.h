@@ -49,8 +49,12 @@ struct RdBinTree {
 };
 
 // SAH constants of the wide-node cost model: one 8-wide node test vs one triangle test
+#ifndef RD_SAH_NODE
 #define RD_SAH_NODE 1.0f
+#endif
+#ifndef RD_SAH_PRIM
 #define RD_SAH_PRIM 0.35f
+#endif
 
 RD_HD rd_u64 rd_expand21(rd_u32 v)
 {
