@@ -166,6 +166,85 @@ __global__ void rd_k_ploc_compact(RdPlocSide A, RdPlocSide B, rd_u32 m, const rd
     if (i == m - 1) *outCount = pos[i] + keep[i];
 }
 
+// Small inputs (the 4096 patch meshes of C4 have 2450 triangles each): all rounds in ONE block, the cluster arrays in
+// global memory, rounds separated by __syncthreads -- no launch / host round trip per round.
+#define RD_PLOC_SMALL_MAX 8192u
+__global__ void __launch_bounds__(1024) rd_k_ploc_small(RdBinTree T, RdPlocSide A, RdPlocSide B, rd_u32* nearest, int radius)
+{
+    __shared__ rd_u32 warpSum[32];
+    __shared__ rd_u32 sBase, sNext;
+    const rd_u32 tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    for (rd_u32 i = tid; i < T.n; i += blockDim.x) { A.ref[i] = RD_BIN_LEAF | i; A.lo[i] = T.lo[T.n - 1 + i]; A.hi[i] = T.hi[T.n - 1 + i]; }
+    if (tid == 0) sNext = T.n - 1u;
+    __syncthreads();
+    rd_u32 m = T.n;
+    while (m > 1u) {
+        for (rd_u32 i = tid; i < m; i += blockDim.x) {
+            const RdF4 l = A.lo[i], h = A.hi[i];
+            const int j0 = (int)i - radius < 0 ? 0 : (int)i - radius;
+            const int j1 = (int)i + radius >= (int)m ? (int)m - 1 : (int)i + radius;
+            float best = 3.0e38f; rd_u32 bj = i;
+            for (int j = j0; j <= j1; ++j) {
+                if (j == (int)i) continue;
+                const RdF4 a = A.lo[j], b = A.hi[j];
+                const float ex = fmaxf(h.x, b.x) - fminf(l.x, a.x), ey = fmaxf(h.y, b.y) - fminf(l.y, a.y),
+                            ez = fmaxf(h.z, b.z) - fminf(l.z, a.z);
+                const float area = ex * ey + ey * ez + ez * ex;
+                if (area < best) { best = area; bj = (rd_u32)j; }
+            }
+            nearest[i] = bj;
+        }
+        if (tid == 0) sBase = 0u;
+        __syncthreads();
+        for (rd_u32 c = 0; c < m; c += blockDim.x) {
+            const rd_u32 i = c + tid;
+            rd_u32 keep = 0u, ref = 0u;
+            RdF4 l, h;
+            l.x = l.y = l.z = l.w = 0.0f; h = l;
+            if (i < m) {
+                const rd_u32 j = nearest[i];
+                if (j == i || nearest[j] != i) { keep = 1u; ref = A.ref[i]; l = A.lo[i]; h = A.hi[i]; }
+                else if (j > i) {
+                    const rd_u32 id = atomicSub(&sNext, 1u) - 1u;
+                    const rd_u32 L = A.ref[i], R = A.ref[j];
+                    const RdF4 la = A.lo[i], ha = A.hi[i], lb = A.lo[j], hb = A.hi[j];
+                    l.x = fminf(la.x, lb.x); l.y = fminf(la.y, lb.y); l.z = fminf(la.z, lb.z);
+                    h.x = fmaxf(ha.x, hb.x); h.y = fmaxf(ha.y, hb.y); h.z = fmaxf(ha.z, hb.z);
+                    T.left[id] = L; T.right[id] = R;
+                    T.parent[rd_bin_slot(T, L)] = id; T.parent[rd_bin_slot(T, R)] = id;
+                    if (id == 0u) T.parent[0] = RD_INVALID;
+                    T.lo[id] = l; T.hi[id] = h;
+                    const volatile rd_u32* vc = (const volatile rd_u32*)T.count;
+                    T.count[id] = ((L & RD_BIN_LEAF) ? 1u : vc[L]) + ((R & RD_BIN_LEAF) ? 1u : vc[R]);
+                    if (T.cost) rd_dp_node(T, id, l, h);
+                    keep = 1u; ref = id;
+                }
+            }
+            // ordered compaction: block-wide exclusive scan of keep
+            rd_u32 x = keep;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const rd_u32 y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= (rd_u32)o) x += y; }
+            if (lane == 31u) warpSum[warp] = x;
+            __syncthreads();
+            if (warp == 0) {
+                rd_u32 s = warpSum[lane];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const rd_u32 y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= (rd_u32)o) s += y; }
+                warpSum[lane] = s;
+            }
+            __syncthreads();
+            const rd_u32 pos = sBase + (x - keep) + (warp ? warpSum[warp - 1] : 0u);
+            if (keep) { B.ref[pos] = ref; B.lo[pos] = l; B.hi[pos] = h; }
+            __syncthreads();
+            if (tid == 0) sBase += warpSum[31];
+            __syncthreads();
+        }
+        m = sBase;
+        RdPlocSide t = A; A = B; B = t;
+        __syncthreads();
+    }
+}
+
 __global__ void rd_k_collapse(RdBinTree T, RdCollapseOut O, const RdCollapseItem* items, rd_u32 count)
 {
     rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -178,13 +257,17 @@ __global__ void rd_k_gather_tris(const float* verts, const rd_u32* idx, const rd
     if (r < n) rd_gather_tri(verts, idx, leafPrim, out, r);
 }
 
-struct RdTmp {   // scoped device scratch
+struct RdTmp {   // scoped device scratch, stream-ordered: freed blocks go back to the device's memory pool
+                 // (release threshold raised in rd_platform_create), so a second build -- or the 4096 bottom-level
+                 // builds of C4 -- reuses them without a cudaMalloc / synchronising cudaFree per buffer
     std::vector<void*> ptrs;
-    ~RdTmp() { for (void* q : ptrs) cudaFree(q); }
+    cudaStream_t st;
+    explicit RdTmp(cudaStream_t s) : st(s) {}
+    ~RdTmp() { for (void* q : ptrs) cudaFreeAsync(q, st); }
     template <class T> cudaError_t alloc(T** out, size_t count)
     {
         void* q = 0;
-        cudaError_t e = cudaMalloc(&q, count * sizeof(T) ? count * sizeof(T) : 16);
+        cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) ? count * sizeof(T) : 16, st);
         if (e == cudaSuccess) ptrs.push_back(q);
         *out = (T*)q;
         return e;
@@ -205,7 +288,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
         out->nodeCount = 1;
         return RD_OK;
     }
-    RdTmp tmp;
+    RdTmp tmp(st);
     unsigned* dbounds; rd_u64 *keysA, *keysB; rd_u32 *valsA, *valsB;
     RD_CUDA(tmp.alloc(&dbounds, 8));
     RD_CUDA(tmp.alloc(&keysA, n)); RD_CUDA(tmp.alloc(&keysB, n));
@@ -248,7 +331,12 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
         RD_CUDA(tmp.alloc(&A.ref, n)); RD_CUDA(tmp.alloc(&A.lo, n)); RD_CUDA(tmp.alloc(&A.hi, n));
         RD_CUDA(tmp.alloc(&B.ref, n)); RD_CUDA(tmp.alloc(&B.lo, n)); RD_CUDA(tmp.alloc(&B.hi, n));
         rd_u32 *nearest, *keep, *pos, *pc;
-        RD_CUDA(tmp.alloc(&nearest, n)); RD_CUDA(tmp.alloc(&keep, n)); RD_CUDA(tmp.alloc(&pos, n)); RD_CUDA(tmp.alloc(&pc, 4));
+        RD_CUDA(tmp.alloc(&nearest, n));
+        if (n <= RD_PLOC_SMALL_MAX) {
+            rd_k_ploc_small<<<1, 1024, 0, st>>>(T, A, B, nearest, radius);
+            p->launches += 1;
+        } else {
+        RD_CUDA(tmp.alloc(&keep, n)); RD_CUDA(tmp.alloc(&pos, n)); RD_CUDA(tmp.alloc(&pc, 4));
         size_t scanBytes = 0;
         cub::DeviceScan::ExclusiveSum(0, scanBytes, keep, pos, (int)n, st);
         char* dscan;
@@ -270,6 +358,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
             if (next >= m || next == 0 || ++rounds > 100000u) { rd_set_error("rd_build_wide_bvh: clustering made no progress (%u -> %u clusters)", m, next); return RD_E_CUDA; }
             m = next;
             RdPlocSide t = A; A = B; B = t;
+        }
         }
     }
     // collapse, one launch per level of the wide tree
@@ -317,7 +406,7 @@ extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigne
     if (!p || !out || (nt && (!dverts || !didx))) { rd_set_error("rd_blas_build: null argument"); return RD_E_ARG; }
     RD_CUDA(cudaSetDevice(p->device));
     cudaStream_t st = p->stream;
-    RdTmp tmp;
+    RdTmp tmp(st);
     RdF4 *plo, *phi;
     RD_CUDA(tmp.alloc(&plo, nt)); RD_CUDA(tmp.alloc(&phi, nt));
     if (nt) { rd_k_tri_boxes<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, nt, plo, phi); p->launches += 1; }
@@ -343,7 +432,7 @@ extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, co
     RD_CUDA(cudaSetDevice(p->device));
     for (size_t k = 0; k < (size_t)nt * 3; ++k)
         if (idx[k] >= nv) { rd_set_error("rd_blas_build: index %u out of range (nv=%u)", idx[k], nv); return RD_E_ARG; }
-    RdTmp tmp;
+    RdTmp tmp(p->stream);
     float* dv; uint32_t* di;
     RD_CUDA(tmp.alloc(&dv, (size_t)nv * 3)); RD_CUDA(tmp.alloc(&di, (size_t)nt * 3));
     if (nv) RD_CUDA(cudaMemcpyAsync(dv, verts, (size_t)nv * 12, cudaMemcpyHostToDevice, p->stream));
@@ -388,7 +477,7 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
         RdF4 bl, bh; bl.x = b->lo[0]; bl.y = b->lo[1]; bl.z = b->lo[2]; bl.w = 0; bh.x = b->hi[0]; bh.y = b->hi[1]; bh.z = b->hi[2]; bh.w = 0;
         rd_instance_world_box(I.fwd, bl, bh, &lo[i], &hi[i]);
     }
-    RdTmp tmp;
+    RdTmp tmp(st);
     RdF4 *dlo, *dhi;
     RD_CUDA(tmp.alloc(&dlo, n)); RD_CUDA(tmp.alloc(&dhi, n));
     if (n) {

@@ -40,6 +40,10 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     memset(&p->wf, 0, sizeof(p->wf));
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    {   // build scratch is stream-ordered (RdTmp in rd_build.cu): keep freed blocks in the pool instead of returning them to the OS
+        cudaMemPool_t pool; unsigned long long keep = ~0ull;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     RD_CUDA(cudaMalloc(&p->dstatus, 64));
     RD_CUDA(cudaMemset(p->dstatus, 0, 64));
     RD_CUDA(cudaMalloc(&p->dcounters, 64));
@@ -57,6 +61,7 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     cudaSetDevice(p->device);
     cudaStreamSynchronize(p->stream);
     rd_wf_release(p);
+    { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
     cudaFree(p->dstatus);
     cudaFree(p->dcounters);
     cudaStreamDestroy(p->stream);

@@ -21,10 +21,11 @@ bundle = scenes.heightfield_scene(n_grid, W, H)
 import time
 tlas, blas = scenes.build_scene(plt, bundle)
 plt.sync()
-t0 = time.perf_counter()
-tlas, blas = scenes.build_scene(plt, bundle)
-plt.sync()
-print("bvh", blas[0].stats(), "build_ms(2nd, incl upload) %.1f" % ((time.perf_counter() - t0) * 1e3), flush=True)
+for _k in range(3):
+    t0 = time.perf_counter()
+    tlas, blas = scenes.build_scene(plt, bundle)
+    plt.sync()
+    print("bvh", blas[0].stats(), "build_ms(rebuild %d, incl upload) %.1f" % (_k, (time.perf_counter() - t0) * 1e3), flush=True)
 ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, int(os.environ.get('RD_EXP_SPP', '1')), int(os.environ.get('RD_EXP_DEPTH', '1')), 0))
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 VARIANTS = json.loads(os.environ.get("RD_EXP_VARIANTS", "null")) or [
