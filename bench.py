@@ -180,15 +180,16 @@ def time_frames(torch, plt, rd, stream, flush, w, h, reps=3):
     return float(np.median(ms[1:]))
 
 
-def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, depth, modes):
+def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, depth, modes, width=None, height=None):
     """Path-tracing configs (BASELINE configs[2], configs[3]) through RD::TraceRays: rays per frame counted by a
     count_rays build of the same program, then each mode timed. Returns a dict for the JSON line."""
     rd, scenes = pkg.rd, pkg.scenes
+    w, h = width or WIDTH, height or HEIGHT
     t0 = time.perf_counter()
     tlas, blas = scenes.build_scene(plt, bundle)
     plt.sync()
     build_ms = (time.perf_counter() - t0) * 1e3
-    ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, spp, depth, 0))
+    ds = scenes.DeviceScene(plt, bundle, tlas, w, h, scenes.rtprop(0, spp, depth, 0))
     plt.set_option("count_rays", 1)
     try:
         pipe, _ = scenes.make_pipeline(plt, program)
@@ -197,7 +198,7 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
     plt.ray_count()
-    rd.TraceRays(plt, 0, 0, 0, WIDTH, HEIGHT)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
     rays = plt.ray_count()
     pipe, module = scenes.make_pipeline(plt, program)
     rd.BindPipeline(plt, pipe)
@@ -209,7 +210,7 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
             plt.set_option("wf_sort", srt)
             plt.set_option("wf_paths", paths)
             l0 = plt.launch_count()
-            ms = time_frames(torch, plt, rd, stream, flush, WIDTH, HEIGHT)
+            ms = time_frames(torch, plt, rd, stream, flush, w, h, reps=3 if w * h * spp < (1 << 28) else 2)
             out[mode] = {"value": rays / ms / 1e3, "ms_per_frame": ms, "launches_per_frame": (plt.launch_count() - l0) // 4}
     finally:
         plt.set_option("wavefront", 0)
@@ -496,6 +497,10 @@ def main():
                     "C3: 4-bounce path tracing (depth 5) with any-hit shadow rays, 1080p 16 spp, blob-field n=2237, programs/path.cl",
                     scenes.blob_field_scene(2237, WIDTH, HEIGHT), "path", 16, 5, modes)
                 if args.extra == "all":
+                    # single-GPU leg of BASELINE configs[4] (4K, 64 spp, 50 M triangles): the denominator of its 2/4/8-GPU frame ms
+                    out["extra"]["C5"] = extra_config(torch, pkg, plt, stream, flush,
+                        "C5: path.cl, 3840x2160 64 spp depth 5, 5 instances of the n=2237 height-field (50 M triangles)",
+                        scenes.replicated_scene(2237, 5, 3840, 2160), "path", 64, 5, (("wavefront_sorted", 1, 1, inflight),), 3840, 2160)
                     out["extra"]["C4"] = extra_config(torch, pkg, plt, stream, flush,
                         "C4: 64 SBT hit groups, 4096 instances, n=2240 height-field, 1080p 16 spp depth 5, programs/groups.cl",
                         scenes.groups_scene(2240, 64, 64, WIDTH, HEIGHT), "groups", 16, 5, modes)

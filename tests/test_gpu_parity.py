@@ -522,3 +522,35 @@ def test_c3_full_size_properties(pkg, plt):
     miss = np.where(hitA["t"] > 3e38)[0][:4]
     for k, t in _brute_force_hits(hv, ht, rays[miss]):
         assert k == -1
+
+
+def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
+    """Option wf_paths: 1 sample per pass, 2 of 5 (ragged last pass), all 5 at once -- the float scratch and the image
+    are bit-identical, also when the frame continues an accumulation (totalSamples > 0)."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 168, 100
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 5, 4, 0))
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    out = []
+    plt.set_option("wavefront", 1)
+    try:
+        for paths in (1, 2 * w * h, 1 << 25):
+            plt.set_option("wf_paths", paths)
+            ds.set_rtprop(0, 5, 4)
+            l0 = plt.launch_count()
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+            first = ds.read_scratch()
+            ds.set_rtprop(5, 5, 4)                      # second call continues the running mean
+            rd.TraceRays(plt, 0, 0, 0, w, h)
+            out.append((first, ds.read_scratch(), ds.read_image(), plt.launch_count() - l0))
+    finally:
+        plt.set_option("wavefront", 0)
+        plt.set_option("wf_paths", 1 << 25)
+    for first, second, image, _ in out[1:]:
+        assert np.array_equal(first, out[0][0]) and np.array_equal(second, out[0][1]) and np.array_equal(image, out[0][2])
+    assert out[0][3] > out[1][3] > out[2][3]            # 5, 3 and 1 passes per call
+    assert not np.array_equal(out[0][0], out[0][1])
