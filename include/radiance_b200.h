@@ -190,6 +190,11 @@ int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */
 int rd_ray_count(rd_platform* p, uint64_t* out, int reset);
+/* diagnostics: the build's own radix sort (stable, LSD, 8 bits per pass over the low `bits` key bits; csrc/rd_sort.h
+ * replaces a library sort in the reference-free GPU build that stands in for radiance/src/bvh.cpp:46-341) and its
+ * exclusive scan, run on host arrays in place. The parity tests compare them with numpy. */
+int rd_debug_sort_pairs(rd_platform* p, uint64_t* keys, uint32_t* vals, unsigned n, int bits);
+int rd_debug_exclusive_scan(rd_platform* p, uint32_t* data, unsigned n, uint32_t* total);
 /* number of kernels this library launched since platform creation */
 uint64_t rd_launch_count(rd_platform* p);
 

@@ -1,15 +1,14 @@
-// rd_build.cu -- GPU acceleration-structure build: Morton codes -> radix sort -> binary hierarchy by
+// rd_build.cu -- GPU acceleration-structure build: Morton codes -> radix sort (rd_sort.h) -> binary hierarchy by
 // parallel locally-ordered clustering (PLOC; Karras' LBVH + refit kept as option) -> SAH-optimal
 // level-synchronous collapse into 8-wide quantised nodes. Replaces the host SAH
 // builder of the reference (radiance/src/bvh.cpp:46-597) and its blob packers
 // (radiance/src/radiance.cpp:318-425). The per-element logic lives in rd_build.h.
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
 #include <float.h>
 #include <string.h>
 #include <stdlib.h>
 #include "rd_internal.h"
 #include "rd_build.h"
+#include "rd_sort.h"
 
 #define RD_BT 256
 static inline unsigned rd_grid(size_t n) { return (unsigned)((n + RD_BT - 1) / RD_BT); }
@@ -158,12 +157,11 @@ __global__ void rd_k_ploc_merge(RdBinTree T, RdPlocSide A, rd_u32 m, const rd_u3
     keep[i] = 1u;
 }
 
-__global__ void rd_k_ploc_compact(RdPlocSide A, RdPlocSide B, rd_u32 m, const rd_u32* keep, const rd_u32* pos, rd_u32* outCount)
+__global__ void rd_k_ploc_compact(RdPlocSide A, RdPlocSide B, rd_u32 m, const rd_u32* keep, const rd_u32* pos)
 {
     const rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) return;
     if (keep[i]) { const rd_u32 k = pos[i]; B.ref[k] = A.ref[i]; B.lo[k] = A.lo[i]; B.hi[k] = A.hi[i]; }
-    if (i == m - 1) *outCount = pos[i] + keep[i];
 }
 
 // Small inputs (the 4096 patch meshes of C4 have 2450 triangles each): all rounds in ONE block, the cluster arrays in
@@ -299,11 +297,15 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     rd_k_centroid_bounds<<<rb, RD_BT, 0, st>>>(dlo, dhi, n, dbounds);
     rd_k_morton<<<rd_grid(n), RD_BT, 0, st>>>(dlo, dhi, n, dbounds, keysA, valsA);
     p->launches += 2;
-    size_t sortBytes = 0;
-    cub::DeviceRadixSort::SortPairs(0, sortBytes, keysA, keysB, valsA, valsB, (int)n, 0, 63, st);
-    char* dsort;
-    RD_CUDA(tmp.alloc(&dsort, sortBytes));
-    RD_CUDA(cub::DeviceRadixSort::SortPairs(dsort, sortBytes, keysA, keysB, valsA, valsB, (int)n, 0, 63, st));
+    RdSortScratch sortScratch;
+    const size_t tableCount = 256u * (size_t)rd_sort_blocks(n);
+    RD_CUDA(tmp.alloc(&sortScratch.hist, 8 * 256)); RD_CUDA(tmp.alloc(&sortScratch.table, tableCount));
+    RD_CUDA(tmp.alloc(&sortScratch.scan, rd_scan_scratch_count(tableCount))); RD_CUDA(tmp.alloc(&sortScratch.where, 4));
+    unsigned long long sortLaunches = 0;
+    const int sortedSide = rd_radix_sort_pairs(st, keysA, valsA, keysB, valsB, n, 63, sortScratch, p->smCount, &sortLaunches);
+    p->launches += sortLaunches;
+    if (sortedSide < 0) { rd_set_error("rd_build_wide_bvh: radix sort failed: %s", cudaGetErrorString(cudaGetLastError())); return RD_E_CUDA; }
+    if (sortedSide == 0) { rd_u64* tk = keysA; keysA = keysB; keysB = tk; rd_u32* tv = valsA; valsA = valsB; valsB = tv; }   // sorted pairs are (keysB, valsB) below
 
     const rd_u32 ni = n > 1 ? n - 1 : 1;
     RdBinTree T;
@@ -337,10 +339,8 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
             p->launches += 1;
         } else {
         RD_CUDA(tmp.alloc(&keep, n)); RD_CUDA(tmp.alloc(&pos, n)); RD_CUDA(tmp.alloc(&pc, 4));
-        size_t scanBytes = 0;
-        cub::DeviceScan::ExclusiveSum(0, scanBytes, keep, pos, (int)n, st);
-        char* dscan;
-        RD_CUDA(tmp.alloc(&dscan, scanBytes));
+        rd_u32* scanScratch;
+        RD_CUDA(tmp.alloc(&scanScratch, rd_scan_scratch_count(n)));
         const rd_u32 pc0[2] = {n - 1u, n};   // [0] next inner id + 1 (ids are handed out downwards), [1] clusters
         RD_CUDA(cudaMemcpyAsync(pc, pc0, sizeof(pc0), cudaMemcpyHostToDevice, st));
         rd_k_ploc_init<<<rd_grid(n), RD_BT, 0, st>>>(T, A);
@@ -349,9 +349,10 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
         while (m > 1) {
             rd_k_ploc_nearest<<<rd_grid(m), RD_BT, 0, st>>>(A, m, radius, nearest);
             rd_k_ploc_merge<<<rd_grid(m), RD_BT, 0, st>>>(T, A, m, nearest, pc, keep);
-            RD_CUDA(cub::DeviceScan::ExclusiveSum(dscan, scanBytes, keep, pos, (int)m, st));
-            rd_k_ploc_compact<<<rd_grid(m), RD_BT, 0, st>>>(A, B, m, keep, pos, pc + 1);
-            p->launches += 3;
+            unsigned long long scanLaunches = 0;
+            rd_exclusive_scan_u32(st, keep, pos, m, scanScratch, pc + 1, &scanLaunches);   // pc[1] = clusters that remain
+            rd_k_ploc_compact<<<rd_grid(m), RD_BT, 0, st>>>(A, B, m, keep, pos);
+            p->launches += 3 + scanLaunches;
             rd_u32 next = 0;
             RD_CUDA(cudaMemcpyAsync(&next, pc + 1, sizeof(next), cudaMemcpyDeviceToHost, st));
             RD_CUDA(cudaStreamSynchronize(st));
@@ -502,5 +503,54 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
     o->size = sizeof(RdScene);
     o->arg = (uint64_t)(uintptr_t)o->dptr;
     *out = o;
+    return RD_OK;
+}
+
+// ---- diagnostics: the build's sort and scan on host arrays (tests/test_gpu_parity.py checks them against numpy) ----
+extern "C" int rd_debug_sort_pairs(rd_platform* p, uint64_t* keys, uint32_t* vals, unsigned n, int bits)
+{
+    if (!p || (n && (!keys || !vals)) || bits < 1 || bits > 64) { rd_set_error("rd_debug_sort_pairs: bad argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    RdTmp tmp(st);
+    rd_u64 *ka, *kb; rd_u32 *va, *vb;
+    RD_CUDA(tmp.alloc(&ka, n)); RD_CUDA(tmp.alloc(&kb, n)); RD_CUDA(tmp.alloc(&va, n)); RD_CUDA(tmp.alloc(&vb, n));
+    RdSortScratch S;
+    const size_t tableCount = 256u * (size_t)rd_sort_blocks(n);
+    RD_CUDA(tmp.alloc(&S.hist, 8 * 256)); RD_CUDA(tmp.alloc(&S.table, tableCount));
+    RD_CUDA(tmp.alloc(&S.scan, rd_scan_scratch_count(tableCount))); RD_CUDA(tmp.alloc(&S.where, 4));
+    if (n) {
+        RD_CUDA(cudaMemcpyAsync(ka, keys, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        RD_CUDA(cudaMemcpyAsync(va, vals, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    }
+    unsigned long long launches = 0;
+    const int side = rd_radix_sort_pairs(st, ka, va, kb, vb, n, bits, S, p->smCount, &launches);
+    p->launches += launches;
+    if (side < 0) { rd_set_error("rd_debug_sort_pairs: %s", cudaGetErrorString(cudaGetLastError())); return RD_E_CUDA; }
+    if (n) {
+        RD_CUDA(cudaMemcpyAsync(keys, side ? kb : ka, (size_t)n * 8, cudaMemcpyDeviceToHost, st));
+        RD_CUDA(cudaMemcpyAsync(vals, side ? vb : va, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    }
+    RD_CUDA(cudaStreamSynchronize(st));
+    return RD_OK;
+}
+
+extern "C" int rd_debug_exclusive_scan(rd_platform* p, uint32_t* data, unsigned n, uint32_t* total)
+{
+    if (!p || (n && !data)) { rd_set_error("rd_debug_exclusive_scan: bad argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    RdTmp tmp(st);
+    rd_u32 *d, *scratch, *dt;
+    RD_CUDA(tmp.alloc(&d, n)); RD_CUDA(tmp.alloc(&scratch, rd_scan_scratch_count(n))); RD_CUDA(tmp.alloc(&dt, 4));
+    RD_CUDA(cudaMemsetAsync(dt, 0, 4, st));
+    if (n) RD_CUDA(cudaMemcpyAsync(d, data, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    unsigned long long launches = 0;
+    rd_exclusive_scan_u32(st, d, d, n, scratch, dt, &launches);
+    p->launches += launches;
+    if (n) RD_CUDA(cudaMemcpyAsync(data, d, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    if (total) RD_CUDA(cudaMemcpyAsync(total, dt, 4, cudaMemcpyDeviceToHost, st));
+    RD_CUDA(cudaStreamSynchronize(st));
+    RD_CUDA(cudaGetLastError());
     return RD_OK;
 }

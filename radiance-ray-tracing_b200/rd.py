@@ -28,6 +28,7 @@ ABI_SYMBOLS = [
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
+    "rd_debug_sort_pairs", "rd_debug_exclusive_scan",
 ]
 
 
@@ -77,6 +78,7 @@ def lib():
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
+            "rd_debug_sort_pairs": [vp, vp, vp, u, C.c_int], "rd_debug_exclusive_scan": [vp, vp, u, C.POINTER(u)],
             "rd_tlas_save": [vp, vp, C.c_char_p], "rd_tlas_save_memory": [vp, vp, C.POINTER(vp), C.POINTER(sz)],
         }
         L.rd_free_host.argtypes, L.rd_free_host.restype = [vp], None
@@ -384,6 +386,20 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("b1", "<f4"), ("b2", "<f4"), ("prim", "<u4"
 
 def TraceRayList(plt, tlas, rayA, rayB, hitA, hitB, n, flags=0):
     _check(lib().rd_trace_ray_list(plt.handle, tlas.handle, rayA.handle, rayB.handle, hitA.handle, hitB.handle, int(n), flags))
+
+
+def debug_sort_pairs(plt, keys, vals, bits=64):
+    """The build's radix sort on host arrays (uint64 keys, uint32 values), returns sorted copies."""
+    k, v = np.ascontiguousarray(keys, np.uint64).copy(), np.ascontiguousarray(vals, np.uint32).copy()
+    _check(lib().rd_debug_sort_pairs(plt.handle, k.ctypes.data, v.ctypes.data, k.size, bits))
+    return k, v
+
+
+def debug_exclusive_scan(plt, data):
+    d = np.ascontiguousarray(data, np.uint32).copy()
+    total = C.c_uint(0)
+    _check(lib().rd_debug_exclusive_scan(plt.handle, d.ctypes.data, d.size, C.byref(total)))
+    return d, int(total.value)
 
 
 def TraceCounters(plt):

@@ -554,3 +554,40 @@ def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
         assert np.array_equal(first, out[0][0]) and np.array_equal(second, out[0][1]) and np.array_equal(image, out[0][2])
     assert out[0][3] > out[1][3] > out[2][3]            # 5, 3 and 1 passes per call
     assert not np.array_equal(out[0][0], out[0][1])
+
+
+def test_build_sort_and_scan_match_numpy(pkg, plt):
+    """csrc/rd_sort.h: stable LSD radix sort of (u64 key, u32 value) pairs and the exclusive scan, against numpy, at
+    sizes on both sides of the single-block / multi-block switch, with heavy key duplication (stability) and with key
+    bytes that are constant (skipped passes)."""
+    rd = pkg.rd
+    rng = np.random.default_rng(5)
+    for n in (0, 1, 2, 31, 1000, 8192, 8193, 100003, 1 << 20):
+        for kind in ("random63", "dups", "lowbits"):
+            if kind == "random63":
+                keys = rng.integers(0, 1 << 63, n, dtype=np.uint64)
+            elif kind == "dups":
+                keys = rng.integers(0, 37, n, dtype=np.uint64) << np.uint64(20)
+            else:
+                keys = rng.integers(0, 1 << 16, n, dtype=np.uint64) | np.uint64(0x1200000000000000)
+            vals = np.arange(n, dtype=np.uint32)
+            k, v = rd.debug_sort_pairs(plt, keys, vals, 63)
+            order = np.argsort(keys, kind="stable")
+            assert np.array_equal(k, keys[order]), (n, kind)
+            assert np.array_equal(v, vals[order]), (n, kind)          # stable: equal keys keep their input order
+    for n in (0, 1, 255, 2048, 2049, 70001, 5000000):
+        d = rng.integers(0, 5, n, dtype=np.uint32)
+        out, total = rd.debug_exclusive_scan(plt, d)
+        exp = np.concatenate([[0], np.cumsum(d, dtype=np.uint64)[:-1]]).astype(np.uint32) if n else d
+        assert np.array_equal(out, exp) and total == int(d.sum()), n
+
+
+def test_build_is_deterministic_and_keeps_its_shape(pkg, plt):
+    """Same mesh, two builds: identical statistics (stable sort, deterministic clustering up to the order in which inner
+    ids are handed out); the C2-size numbers are pinned so that a change of the builder shows up here."""
+    scenes = pkg.scenes
+    b = scenes.heightfield_scene(224, 640, 360)
+    s1 = scenes.build_scene(plt, b)[1][0].stats()
+    s2 = scenes.build_scene(plt, b)[1][0].stats()
+    assert s1 == s2 and s1["triangles"] == 2 * 224 * 224
+    assert 0.08 * s1["triangles"] < s1["nodes"] < 0.13 * s1["triangles"]      # ~0.10 wide nodes per triangle (PLOC + DP collapse)
