@@ -12,10 +12,10 @@ CPP = os.path.join(ROOT, "tests", "cpp")
 PROG = os.path.join(ROOT, "radiance-ray-tracing_b200", "programs")
 
 
-def build_sample():
+def build_sample(name="sample_shim"):
     r = subprocess.run(["make", "-C", CPP], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert r.returncode == 0, r.stdout
-    return os.path.join(CPP, "sample_shim")
+    return os.path.join(CPP, name)
 
 
 def test_shim_compiles_and_has_no_cpu_path(pkg):
@@ -72,3 +72,85 @@ def test_cpp_sample_matches_python_mirror(pkg, plt, tmp_path):
     img_py = ds.read_image()
     assert img_cpp[..., :3].std() > 10
     assert np.array_equal(img_cpp, img_py)
+
+
+def _asset(pkg, tmp_path):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    import gltf_fixture
+    doc, binary, expected = gltf_fixture.build_asset(pkg.scenes)
+    glb = str(tmp_path / "scene.glb")
+    gltf_fixture.write_glb(glb, doc, binary)
+    return glb, expected
+
+
+def test_cpp_scene_builder_rejects_a_broken_asset(pkg, tmp_path):
+    """include/sceneBuilder.h aborts (prints, exit code != 0) on a truncated container. Without a GPU the platform
+    singleton aborts first ("no CPU path"): either way the program must not continue."""
+    exe = build_sample("sample_scene")
+    glb, _ = _asset(pkg, tmp_path)
+    bad = str(tmp_path / "short.glb")
+    open(bad, "wb").write(open(glb, "rb").read()[:200])
+    r = subprocess.run([exe, bad, os.path.join(PROG, "textured.cl"), os.path.join(PROG, "textured_sbt.json"), str(tmp_path / "x")],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    import torch
+    assert r.returncode != 0 and ("RD::Scene::Load" if torch.cuda.is_available() else "no CPU path") in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+def test_cpp_scene_builder_and_render_loop_match_python(pkg, plt, tmp_path):
+    """RD::Scene::Load (include/sceneBuilder.h) + renderLoop (include/inspector.h) in a C++ host program: the descriptor
+    arrays equal the Python loader's, the rendered frame equals the Python mirror's, the PNG written by the loop
+    decodes to the frame, the <scene>.cache blob renders the same image (checked inside the program)."""
+    import importlib
+    rd, scenes = pkg.rd, pkg.scenes
+    sl = importlib.import_module("radiance_b200.scene_loader")
+    exe = build_sample("sample_scene")
+    glb, _ = _asset(pkg, tmp_path)
+    prefix = str(tmp_path / "cpp")
+    w, h, dim = 320, 240, 16            # dim = the PNG's own size: no resampling on either side
+    r = subprocess.run([exe, glb, os.path.join(PROG, "textured.cl"), os.path.join(PROG, "textured_sbt.json"), prefix, str(dim), str(w), str(h)],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    p = sl.parse_gltf(glb)
+    raw = open(prefix + ".arrays", "rb").read()
+    at, arrays = 0, []
+    while at < len(raw):
+        n = int(np.frombuffer(raw, np.uint64, 1, at)[0])
+        arrays.append(raw[at + 8: at + 8 + n])
+        at += 8 + n
+    info, verts, tris, uvs, normals, mats, inst = arrays
+    assert info == p.meshInfoData.tobytes() and verts == p.vertexData.tobytes() and tris == p.indexData.tobytes()
+    assert uvs == p.uvData.tobytes() and mats == p.materials.tobytes()
+    assert np.allclose(np.frombuffer(normals, np.float32), p.normalData.reshape(-1), atol=2e-6)
+    inst = np.frombuffer(inst, np.float32).reshape(-1, 18)
+    assert len(inst) == len(p.instances)
+    for row, (mesh, tf, sbt, custom) in zip(inst, p.instances):
+        assert int(row[0]) == mesh and int(row[1]) == custom and np.allclose(row[2:].reshape(4, 4), tf, atol=1e-6)
+    img_cpp = np.fromfile(prefix + ".rgba", np.uint8).reshape(h, w, 4)
+    from PIL import Image
+    assert np.array_equal(np.asarray(Image.open(prefix + "_1.png")), img_cpp)
+    assert os.path.exists(prefix + "_0.png")
+    # the same frames through the Python loader and mirror (two callbacks of one sample each)
+    scene = sl.Scene.Load(glb, plt, tex_dim=dim)
+    n = w * h
+
+    def buf(arr):
+        hnd = rd.CreateBuffer(plt, max(16, arr.nbytes))
+        rd.WriteBuffer(plt, hnd, arr.nbytes, arr)
+        return hnd
+    image = rd.CreateImage(plt, w, h)
+    rt = buf(np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1))
+    head = [rt, rd.CreateBuffer(plt, n * 16), image, buf(np.array(scenes.camera(w, h, (0.02, 0.9, 2.2), (-0.3, 0.0, 0.0))).reshape(1)),
+            buf(np.array(scenes.scene_properties()).reshape(1))]
+    pipe, _ = scenes.make_pipeline(plt, "textured")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, rd.CreateDescriptorSet(head + scene.descriptors()))
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    rd.WriteBuffer(plt, rt, 16, np.array(scenes.rtprop(1, 1, 1, 0)).reshape(1))
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    img_py = np.zeros((h, w, 4), np.uint8)
+    rd.ReadBuffer(plt, image, img_py.nbytes, img_py)
+    assert img_cpp[..., :3].std() > 20
+    d = img_cpp[..., :3].astype(np.float64) - img_py[..., :3].astype(np.float64)
+    assert np.sqrt((d * d).mean()) <= 0.25 and (np.abs(d).max(axis=-1) > 2).mean() < 1e-3   # normals differ by float rounding only
