@@ -84,23 +84,23 @@ def sample_rows(ref, host, n, cores):
     return max(60, min(HEIGHT, rows - rows % 4))
 
 
-class stdout_to_stderr:
-    """The reference's builder prints to the C stdout ("Max BVH depth ...", radiance/src/bvh.cpp); this process's stdout
-    carries ONE JSON line, so the file descriptor is pointed at stderr while reference code runs."""
+_REAL_STDOUT = None
 
-    def __enter__(self):
+
+def claim_stdout():
+    """This process's stdout carries ONE JSON line. Libraries print there too -- the reference's builder ("Max BVH depth
+    ...", radiance/src/bvh.cpp), NCCL ("NCCL version ...") -- so file descriptor 1 is pointed at stderr for the whole run
+    and the line is written to a private duplicate of the original stdout by emit()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
         sys.stdout.flush()
-        self.saved = os.dup(1)
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
         os.dup2(2, 1)
 
-    def __exit__(self, *exc):
-        try:
-            import ctypes
-            ctypes.CDLL(None).fflush(None)
-        except Exception:
-            pass
-        os.dup2(self.saved, 1)
-        os.close(self.saved)
+
+def emit(line):
+    _REAL_STDOUT.write(line + "\n")
+    _REAL_STDOUT.flush()
 
 
 def reference_arm(args, rank, world):
@@ -305,13 +305,13 @@ def main():
     ap.add_argument("--extra", default="c3", choices=["c3", "all"], help="extra configs measured at N=1: C3, or C3 and C4")
     ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C4 wavefront measurements (N=1 only)")
     args = ap.parse_args()
+    claim_stdout()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        with stdout_to_stderr():
-            line = reference_arm(args, rank, world)
+        line = reference_arm(args, rank, world)
         if line:
-            print(line)
+            emit(line)
         return
 
     import torch
@@ -509,12 +509,11 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             ref = entry.load_oracle()
             if ref.available():
-                with stdout_to_stderr():
-                    out["cpu_baseline"] = cpu_baseline_leg(pkg, ref, bundle)
+                out["cpu_baseline"] = cpu_baseline_leg(pkg, ref, bundle)
             else:
                 out["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": 0, "kind": "reference",
                                        "sample": "oracle/_ref not built on this box"}
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
 

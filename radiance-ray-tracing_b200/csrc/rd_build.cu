@@ -327,7 +327,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
         rd_k_refit<<<rd_grid(n), RD_BT, 0, st>>>(T);
         p->launches += 2;
     } else if (n > 1) {
-        int radius = 16;
+        int radius = 32;   // 8 / 16 / 32 / 64 on C2: 4346 / 4345 / 4365 / 4272 Mrays/s, slowest tile row 0.257 / 0.260 / 0.226 / 0.228 ms
         if (const char* e = getenv("RD_PLOC_RADIUS")) { radius = atoi(e); if (radius < 1) radius = 1; }
         RdPlocSide A, B;
         RD_CUDA(tmp.alloc(&A.ref, n)); RD_CUDA(tmp.alloc(&A.lo, n)); RD_CUDA(tmp.alloc(&A.hi, n));

@@ -276,6 +276,11 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 // once.
 struct RdStackEntry { rd_u32 x, y; };
 
+#ifndef RD_PREFETCH
+#define RD_PREFETCH 0      // ablation: prefetch the next node and the group's last triangle record when a node exposes
+                           // triangles. Measured on C2: 4364 -> 4272 Mrays/s, slowest tile row alone 0.228 -> 0.234 ms: a warp on
+                           // its own is bound by dependent ALU latency, not by these loads (profiles/README_r1.md)
+#endif
 #ifndef RD_PEND_MAX
 #define RD_PEND_MAX 1      // pending triangle groups per lane before it must flush
 #endif
@@ -343,7 +348,22 @@ struct RdTraversal {
             const rd_u32 leafBits = hm & 0x00ffffffu;
             if (leafBits) {
                 if (blasSp < 0) { tg.x = n1.y; tg.y = leafBits; }
-                else { pend[np].x = n1.y; pend[np].y = leafBits; ++np; }
+                else {
+                    pend[np].x = n1.y; pend[np].y = leafBits; ++np;
+#if defined(__CUDA_ARCH__) && RD_PREFETCH
+                    // The triangle phase runs before the next node is needed: start that node's fetch now, and the fetch of
+                    // the last triangle record of this group (the first one is loaded at once). A warp on its own -- the tail
+                    // of a frame, a frame split over several GPUs -- is bound by exactly this chain of dependent loads.
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(tris + (n1.y + (31u - (rd_u32)RD_CLZ(leafBits)))));
+                    if (ng.y > 0x00ffffffu) {
+                        const rd_u32 nbit = 31u - (rd_u32)RD_CLZ(ng.y);
+                        const rd_u32 nslot = (nbit - 24u) ^ (f.octinv4 & 0xffu);
+                        const RdNode8* nx = nodes + (ng.x + (rd_u32)RD_POPC((ng.y & 0xffu) & ~(0xffffffffu << nslot)));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(nx));
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"((const char*)nx + 64));
+                    }
+#endif
+                }
             }
         } else if (ng.y) {
             tg = ng; ng.x = 0; ng.y = 0;   // a parked top-level instance group came off the stack
