@@ -29,7 +29,7 @@ WORKLOAD = "C2: primary-ray closest-hit, 1920x1080, 1 spp, height-field n=708 (1
 NODE_BYTES, TRI_BYTES, RAY_BYTES, HIT_BYTES = 80, 48, 32, 16
 # dram__bytes_read.sum + dram__bytes_write.sum of one raygen launch of this workload, from the ncu --set full capture
 # summarised in profiles/ncu_r1c_primary.txt (93.44 MB + 29.40 MB); re-measured whenever the kernel changes
-NCU_DRAM_BYTES_PER_LAUNCH = 121.70e6
+NCU_DRAM_BYTES_PER_LAUNCH = 124.57e6   # profiles/ncu_r1g_primary.txt: dram read 93.56 MB + write 31.01 MB
 
 
 def measured_peaks():
