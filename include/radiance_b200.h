@@ -185,7 +185,9 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading),
  * "wf_paths" (default 2^25: paths in flight per wavefront pass -- RTProp.batchSize samples of every work-item are
  * generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path; 1 = one sample
- * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order) */
+ * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order),
+ * "trim_pool" (any value: releases what the library keeps between calls -- the stream-ordered build scratch held in the
+ * device's memory pool and the wavefront queues, up to ~200 B x wf_paths -- they are allocated again on demand) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */

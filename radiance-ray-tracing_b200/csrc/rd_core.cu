@@ -233,6 +233,13 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     else if (!strcmp(key, "wf_sort")) p->optWfSort = value;
     else if (!strcmp(key, "wf_dynamic")) p->optWfDynamic = value;
     else if (!strcmp(key, "wf_ray_sort")) p->optWfRaySort = value;
+    else if (!strcmp(key, "trim_pool")) {   // give the build scratch and the wavefront queues back to the driver (value ignored)
+        cudaSetDevice(p->device);
+        cudaStreamSynchronize(p->stream);
+        rd_wf_release(p);
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+    }
     else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)
     else if (!strcmp(key, "stealing")) p->optSteal = value;
     else if (!strcmp(key, "max_trace_depth")) { if (value < 1 || value > 8) { rd_set_error("max_trace_depth must be in [1,8]"); return RD_E_ARG; } p->optMaxDepth = value; }

@@ -554,6 +554,15 @@ def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
         assert np.array_equal(first, out[0][0]) and np.array_equal(second, out[0][1]) and np.array_equal(image, out[0][2])
     assert out[0][3] > out[1][3] > out[2][3]            # 5, 3 and 1 passes per call
     assert not np.array_equal(out[0][0], out[0][1])
+    # option trim_pool drops the queues and the build scratch; the next frame allocates them again and is unchanged
+    plt.set_option("trim_pool", 1)
+    plt.set_option("wavefront", 1)
+    try:
+        ds.set_rtprop(0, 5, 4)
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        assert np.array_equal(ds.read_scratch(), out[0][0])
+    finally:
+        plt.set_option("wavefront", 0)
 
 
 def test_build_sort_and_scan_match_numpy(pkg, plt):
