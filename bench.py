@@ -303,6 +303,8 @@ def main():
     ap.add_argument("--band", type=int, default=1, help="tile rows per band of the interleaved partition")
     ap.add_argument("--chunk", type=int, default=32, help="work-items per stolen chunk (multiple of 32)")
     ap.add_argument("--extra", default="c3", choices=["c3", "all"], help="extra configs measured at N=1: C3, or C3 and C4")
+    ap.add_argument("--readback-bands", type=int, default=24,
+                    help="N=1 end-to-end leg: bands of the streamed read-back (rd_buffer_stream_to_host); 0 = plain ReadBuffer")
     ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C4 wavefront measurements (N=1 only)")
     args = ap.parse_args()
     claim_stdout()
@@ -347,6 +349,9 @@ def main():
     image_t = torch.zeros(n * 4, dtype=torch.uint8, device="cuda")
     ds.rdImage = rd.WrapBuffer(plt, image_t.data_ptr(), n * 4, owner=image_t)
     ds.descriptors[2] = ds.rdImage
+    streamed = world == 1 and args.readback_bands > 0
+    if streamed:   # the module also gets the band-reporting raygen; it only runs once a host mirror is registered (e2e leg)
+        plt.set_option("stream_image", 1)
     pipe, module = scenes.make_pipeline(plt, "primary")
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
@@ -425,6 +430,9 @@ def main():
         else:
             plt.sync()
     host_full = torch.zeros(n * 4, dtype=torch.uint8).pin_memory()
+    if streamed:
+        # same two API calls per frame; the bands of the frame travel to host_full while the later bands render
+        rd.StreamBufferToHost(plt, ds.rdImage, host_full.data_ptr(), 4, args.readback_bands)
     for _ in range(3):
         e2e_step()
     barrier()
@@ -433,6 +441,14 @@ def main():
         e2e_step()
     barrier()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    if streamed:
+        rd.StreamBufferToHost(plt, None, None)
+        with torch.cuda.stream(stream):   # the streamed frame must be the frame the plain path delivers
+            render_and_gather()
+        check = torch.zeros(n * 4, dtype=torch.uint8).pin_memory()
+        rd.ReadBuffer(plt, ds.rdImage, n * 4, check.data_ptr(), 0)
+        if not torch.equal(check, host_full):
+            raise SystemExit("bench: streamed read-back delivered a different frame than TraceRays + ReadBuffer")
     t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -476,7 +492,9 @@ def main():
                        "bvh": blas[0].stats(), "raygen": module.info()},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 16,
-                    "d2h_bytes_per_step": n * 4 if world > 1 else count * 4, "ms_per_step": e2e_ms},
+                    "d2h_bytes_per_step": n * 4 if world > 1 else count * 4, "ms_per_step": e2e_ms,
+                    "readback": ("streamed in %d bands while the frame renders (rd_buffer_stream_to_host)" % args.readback_bands)
+                    if streamed else "ReadBuffer after the frame"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None, "traffic_unit": "bytes per launch (ncu dram read + write)",
                          "algorithmic_bytes_per_launch": rays_per_launch * bytes_per_ray, "peak_kind": peak_kind, "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",

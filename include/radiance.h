@@ -227,6 +227,14 @@ inline void ReadBuffer(Platform* platform, Buffer handle, size_t size, void* dat
     _check(rd_buffer_read(platform->impl, handle, size, data, offset), "ReadBuffer");
 }
 
+// B200 extension (no reference counterpart): frames traced after this call are copied into `host` band by band while
+// they render, so the ReadBuffer(handle, size, host) that follows TraceRays only waits for the last band. Needs
+// rd_set_option(platform->impl, "stream_image", 1) before CreateShaderModule; host must be page-locked.
+inline void StreamBufferToHost(Platform* platform, Buffer handle, void* host, unsigned int itemBytes = 4, unsigned int bands = 4)
+{
+    _check(rd_buffer_stream_to_host(platform->impl, handle, host, itemBytes, bands), "StreamBufferToHost");
+}
+
 inline void WriteBuffer(Platform* platform, Buffer handle, size_t size, void* data, size_t offset = 0)
 {
     _check(rd_buffer_write(platform->impl, handle, size, data, offset), "WriteBuffer");

@@ -63,6 +63,15 @@ int rd_sampler_create(rd_platform* p, uint32_t addressingMode, uint32_t filterMo
 /* RD::WriteBuffer / RD::ReadBuffer (blocking), radiance/src/radiance.cpp:186-199 */
 int rd_buffer_write(rd_platform* p, rd_handle h, size_t size, const void* data, size_t offset);
 int rd_buffer_read(rd_platform* p, rd_handle h, size_t size, void* data, size_t offset);
+/* Streamed read-back for the TraceRays + ReadBuffer pair of the reference's render loop (samples/sample1.cpp:466-490,
+ * radiance/src/radiance.cpp:186-199, 242-267). Registers `host` (page-locked, at least width*height*itemBytes bytes) as
+ * the mirror of buffer `h`, which must hold itemBytes bytes per work-item in launch order (a row-major image). From then
+ * on a full-frame inline rd_trace_rays* of a module created under option "stream_image" renders the frame in `bands`
+ * (1..64) equal runs of tile rows and copies every band to `host` as soon as its blocks have finished (in whatever order
+ * they finish), overlapping PCIe with the rest of the frame; the following rd_buffer_read(p, h, size, host, 0) finds
+ * the data in place and only waits for
+ * the last band. Any other use of the buffer behaves as before. host == NULL ends the registration. */
+int rd_buffer_stream_to_host(rd_platform* p, rd_handle h, void* host, unsigned itemBytes, unsigned bands);
 /* RD::WriteImage / RD::ReadImage (one layer), radiance/src/radiance.cpp:202-224 */
 int rd_image_write(rd_platform* p, rd_handle h, unsigned width, unsigned height, size_t layer, const void* data);
 int rd_image_read(rd_platform* p, rd_handle h, unsigned width, unsigned height, size_t layer, void* data);
@@ -186,6 +195,8 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wf_paths" (default 2^25: paths in flight per wavefront pass -- RTProp.batchSize samples of every work-item are
  * generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path; 1 = one sample
  * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order),
+ * "stream_image" (default 0; modules created while it is 1 also carry the band-reporting raygen that
+ * rd_buffer_stream_to_host needs),
  * "trim_pool" (any value: releases what the library keeps between calls -- the stream-ordered build scratch held in the
  * device's memory pool and the wavefront queues, up to ~200 B x wf_paths -- they are allocated again on demand) */
 int rd_set_option(rd_platform* p, const char* key, long value);

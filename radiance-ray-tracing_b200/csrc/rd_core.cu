@@ -1,6 +1,8 @@
 // rd_core.cu -- platform, resource handles and blocking transfers of the C ABI.
 // Replaces radiance/src/clcontext.cpp:12-40 (context) and radiance/src/radiance.cpp:86-140,186-224
 // (CreateBuffer / CreateImage / CreateImageArray / CreateSampler / Read* / Write*).
+#include <time.h>
+#include <stdio.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
@@ -36,6 +38,11 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->boundModule = 0;
     p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 25;
     p->ilWorld = p->ilRank = p->ilBandRows = 0;
+    p->optStreamImage = 0;
+    p->mirrorObj = 0; p->mirrorHost = 0; p->mirrorItemBytes = 0; p->mirrorBands = 0; p->mirrorValidBytes = 0; p->mirrorFresh = 0; p->copyPending = 0;
+    p->copyStream = 0; p->bandDone = 0; p->bandDoneCap = 0;
+    p->bandLayoutW = p->bandLayoutH = p->bandLayoutN = p->bandLayoutBlock = p->bandEpoch = 0;
+    p->bandFlags = 0; p->bandFlagsDev = 0; p->bandCount = p->bandRows = p->bandTileRows = 0; p->bandCopied = 0; p->bandRowBytes = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
     p->launches = 0;
@@ -64,6 +71,9 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
     cudaFree(p->dstatus);
     cudaFree(p->dcounters);
+    if (p->copyStream) { cudaStreamSynchronize(p->copyStream); cudaStreamDestroy(p->copyStream); }
+    if (p->bandDone) cudaFree(p->bandDone);
+    if (p->bandFlags) cudaFreeHost((void*)p->bandFlags);
     cudaStreamDestroy(p->stream);
     delete p;
     return RD_OK;
@@ -156,6 +166,66 @@ static int check_range(RdHandleObj* o, size_t size, size_t offset, const char* w
     return RD_OK;
 }
 
+// developer knob RD_BAND_TRACE=1: host-clock microseconds since the launch at which each band's flag was seen, its copy
+// was queued, and the last copy had arrived (stderr, one line per frame)
+static double rd_now_us()
+{
+    timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
+    return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
+}
+double rd_band_t0 = 0.0;
+static double rd_band_seen[64];
+
+int rd_stream_bands_drain(rd_platform* p)
+{
+    if (!p->copyPending) return RD_OK;
+    static const bool trace = getenv("RD_BAND_TRACE") != 0;
+    const uint64_t all = p->bandCount >= 64u ? ~0ull : ((1ull << p->bandCount) - 1ull);
+    for (unsigned spins = 1; p->bandCopied != all; ++spins) {
+        for (unsigned b = 0; b < p->bandCount; ++b) {
+            if ((p->bandCopied >> b) & 1ull) continue;
+            if (p->bandFlags[b] != p->bandEpoch) continue;
+            const size_t r0 = (size_t)b * p->bandRows, r1 = r0 + p->bandRows < p->bandTileRows ? r0 + p->bandRows : p->bandTileRows;
+            if (trace) rd_band_seen[b] = rd_now_us() - rd_band_t0;
+            RD_CUDA(cudaMemcpyAsync((char*)p->mirrorHost + r0 * p->bandRowBytes, (const char*)p->mirrorObj->dptr + r0 * p->bandRowBytes,
+                                    (r1 - r0) * p->bandRowBytes, cudaMemcpyDeviceToHost, p->copyStream));
+            p->bandCopied |= 1ull << b;
+        }
+        if ((spins & 0xfffu) == 0u && p->bandCopied != all) {
+            // the frame's launch is the last thing on the stream: once it is done every flag must be up
+            const cudaError_t q = cudaStreamQuery(p->stream);
+            bool up = true;
+            for (unsigned b = 0; b < p->bandCount; ++b) up = up && p->bandFlags[b] == p->bandEpoch;
+            if (q == cudaSuccess && !up) {
+                rd_set_error("streamed read-back: the frame ended without completing all of its bands");
+                p->copyPending = 0; p->mirrorFresh = 0; p->bandLayoutW = 0;   // counters start over with the next frame
+                return RD_E_STATE;
+            }
+            if (q != cudaSuccess && q != cudaErrorNotReady) {
+                rd_set_error("streamed read-back: %s", cudaGetErrorString(q));
+                p->copyPending = 0; p->mirrorFresh = 0; p->bandLayoutW = 0;
+                return RD_E_CUDA;
+            }
+        }
+    }
+    return RD_OK;
+}
+
+int rd_stream_bands_finish(rd_platform* p)
+{
+    if (!p->copyPending) return RD_OK;
+    int rc = rd_stream_bands_drain(p);
+    if (rc) return rc;
+    RD_CUDA(cudaStreamSynchronize(p->copyStream));
+    p->copyPending = 0;
+    if (getenv("RD_BAND_TRACE")) {
+        fprintf(stderr, "bands:");
+        for (unsigned b = 0; b < p->bandCount; ++b) fprintf(stderr, " %u:%.0f", b, rd_band_seen[b]);
+        fprintf(stderr, " arrived %.0f us\n", rd_now_us() - rd_band_t0);
+    }
+    return RD_OK;
+}
+
 extern "C" int rd_buffer_write(rd_platform* p, rd_handle h, size_t size, const void* data, size_t offset)
 {
     RdHandleObj* o = rd_obj(h);
@@ -164,6 +234,19 @@ extern "C" int rd_buffer_write(rd_platform* p, rd_handle h, size_t size, const v
     if (rc) return rc;
     if (!size) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
+    if (o == p->mirrorObj) {   // the host mirror no longer matches; a streamed copy still in flight must read the old contents first
+        if (p->copyPending) { rc = rd_stream_bands_finish(p); if (rc) return rc; }
+        p->mirrorFresh = 0;
+    }
+    if (size <= 256 && !getenv("RD_SMALL_WRITE_SYNC")) {
+        // Per-frame parameter blocks (RTProp, camera: samples/sample1.cpp:466-470). Blocking semantics only ask that `data`
+        // may be reused on return: a copy from pageable memory returns once the driver has taken the bytes, so a stack
+        // copy makes the call safe without draining the stream; stream order puts it ahead of the next launch.
+        unsigned char staged[256];
+        memcpy(staged, data, size);
+        RD_CUDA(cudaMemcpyAsync((char*)o->dptr + offset, staged, size, cudaMemcpyHostToDevice, p->stream));
+        return RD_OK;
+    }
     RD_CUDA(cudaMemcpyAsync((char*)o->dptr + offset, data, size, cudaMemcpyHostToDevice, p->stream));
     RD_CUDA(cudaStreamSynchronize(p->stream));
     return RD_OK;
@@ -177,8 +260,49 @@ extern "C" int rd_buffer_read(rd_platform* p, rd_handle h, size_t size, void* da
     if (rc) return rc;
     if (!size) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
+    if (p->mirrorFresh && o == p->mirrorObj && data == p->mirrorHost && offset == 0 && size <= p->mirrorValidBytes) {
+        // the last TraceRays is streaming its bands into this very host buffer (rd_buffer_stream_to_host): start the
+        // copies of the bands as they complete; behind the last ray only the small last band is left to move
+        rc = rd_stream_bands_finish(p);
+        p->mirrorFresh = 0;
+        return rc;
+    }
+    if (p->copyPending) { rc = rd_stream_bands_finish(p); if (rc) return rc; p->mirrorFresh = 0; }
     RD_CUDA(cudaMemcpyAsync(data, (const char*)o->dptr + offset, size, cudaMemcpyDeviceToHost, p->stream));
     RD_CUDA(cudaStreamSynchronize(p->stream));
+    return RD_OK;
+}
+
+// Streamed read-back. The reference's render loop is TraceRays (blocking) followed by ReadBuffer of the whole image
+// (samples/sample1.cpp:466-490, radiance/src/radiance.cpp:186-199): the PCIe transfer starts when the last ray is done.
+// After this call, full-frame inline launches of a module created under option "stream_image" split the frame into
+// up to `bands` runs of tile rows; the raygen blocks count themselves off per band and the block that completes a band
+// raises a flag in host-mapped memory. The host thread -- blocked in TraceRays / ReadBuffer anyway -- watches the flags
+// and starts each finished band's copy to `host` on a second stream while the later bands are still rendering. The
+// rd_buffer_read(handle, size, host, 0) with the same pointer then only waits for the last, small band. The buffer must
+// hold itemBytes bytes per work-item in launch order (a row-major image); host should be page-locked. host == NULL ends it.
+extern "C" int rd_buffer_stream_to_host(rd_platform* p, rd_handle h, void* host, unsigned itemBytes, unsigned bands)
+{
+    if (!p) { rd_set_error("rd_buffer_stream_to_host: null platform"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    if (p->copyPending) { int frc = rd_stream_bands_finish(p); if (frc) return frc; }
+    p->mirrorFresh = 0;
+    if (!host) { p->mirrorObj = 0; p->mirrorHost = 0; return RD_OK; }
+    RdHandleObj* o = rd_obj(h);
+    if (!o || (o->kind != RD_H_BUFFER && o->kind != RD_H_IMAGE_ARRAY)) { rd_set_error("rd_buffer_stream_to_host: not a buffer handle"); return RD_E_ARG; }
+    if (!itemBytes || bands < 1 || bands > 64) { rd_set_error("rd_buffer_stream_to_host: itemBytes must be positive and bands in [1,64]"); return RD_E_ARG; }
+    if (!p->copyStream) {
+        RD_CUDA(cudaStreamCreateWithFlags(&p->copyStream, cudaStreamNonBlocking));
+        RD_CUDA(cudaMalloc(&p->bandDone, 64 * sizeof(unsigned)));
+        RD_CUDA(cudaMemset(p->bandDone, 0, 64 * sizeof(unsigned)));
+        p->bandDoneCap = 64;
+        void* flags = 0;
+        RD_CUDA(cudaHostAlloc(&flags, 64 * sizeof(unsigned), cudaHostAllocMapped));
+        memset(flags, 0, 64 * sizeof(unsigned));
+        p->bandFlags = (volatile unsigned*)flags;
+        RD_CUDA(cudaHostGetDevicePointer((void**)&p->bandFlagsDev, flags, 0));
+    }
+    p->mirrorObj = o; p->mirrorHost = host; p->mirrorItemBytes = itemBytes; p->mirrorBands = bands;
     return RD_OK;
 }
 
@@ -209,6 +333,10 @@ extern "C" int rd_handle_free(rd_platform* p, rd_handle h)
     RdHandleObj* o = rd_obj(h);
     if (!o) return RD_OK;
     if (p) cudaSetDevice(p->device);
+    if (p && o == p->mirrorObj) {   // streamed read-back ends with its buffer
+        if (p->copyPending) rd_stream_bands_finish(p);
+        p->mirrorObj = 0; p->mirrorHost = 0; p->mirrorFresh = 0; p->copyPending = 0;
+    }
     if (o->kind == RD_H_TLAS) { cudaFree(o->dnodes); cudaFree(o->dleaf); cudaFree(o->dinst); }
     if (o->dptr && !o->external) cudaFree(o->dptr);
     if (o->ddesc) cudaFree(o->ddesc);
@@ -242,6 +370,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     }
     else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)
     else if (!strcmp(key, "stealing")) p->optSteal = value;
+    else if (!strcmp(key, "stream_image")) p->optStreamImage = value;   // modules created from now on carry the band-reporting raygen
     else if (!strcmp(key, "max_trace_depth")) { if (value < 1 || value > 8) { rd_set_error("max_trace_depth must be in [1,8]"); return RD_E_ARG; } p->optMaxDepth = value; }
     else if (!strcmp(key, "block")) { if (value < 32 || value > 1024 || (value & 31)) { rd_set_error("block must be a multiple of 32 in [32,1024]"); return RD_E_ARG; } p->optBlock = value; }
     else { rd_set_error("rd_set_option: unknown key '%s'", key); return RD_E_ARG; }

@@ -39,6 +39,7 @@ struct rd_blas {
 struct rd_module {
     CUmodule mod; CUfunction raygen;
     CUfunction stealRaygen;                      // persistent raygen with chunk stealing (option "stealing")
+    CUfunction bandedRaygen;                     // raygen whose blocks report band completion (option "stream_image")
     CUfunction wfGenerate, wfShade, wfAccumulate, wfResolve;   // 0 when the program has no wavefront hooks
     unsigned wfPayloadSize; float wfRay[4];      // sizeof(struct Payload); sbtRecordOffset, missIndex, Tmin, Tmax
     int numRegs; int localBytes;
@@ -62,6 +63,13 @@ struct rd_platform {
     rd_module* boundModule;
     std::string sbtJson;
     long optFmad, optTile, optBlock, optCountRays, optMaxDepth, optWavefront, optWfSort, optSteal, optWfDynamic, optWfRaySort, optWfPaths;
+    long optStreamImage;                         // modules get the band-reporting raygen (rd_buffer_stream_to_host)
+    // streamed read-back (rd_buffer_stream_to_host): bands of the frame are copied to the host mirror while later bands render
+    RdHandleObj* mirrorObj; void* mirrorHost; unsigned mirrorItemBytes, mirrorBands; size_t mirrorValidBytes; int mirrorFresh, copyPending;
+    cudaStream_t copyStream; unsigned* bandDone; unsigned bandDoneCap;
+    unsigned bandLayoutW, bandLayoutH, bandLayoutN, bandLayoutBlock, bandEpoch;
+    volatile unsigned* bandFlags; unsigned* bandFlagsDev;   // host-mapped: band b of launch e is complete when bandFlags[b] == e
+    unsigned bandCount, bandRows, bandTileRows; uint64_t bandCopied; size_t bandRowBytes;   // bandCopied: bit b = copy of band b queued
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
@@ -70,6 +78,10 @@ struct rd_platform {
 };
 
 void rd_set_error(const char* fmt, ...);
+// rd_core.cu, streamed read-back: start the copy of every band the running frame has completed (waits for all of them);
+// finish = drain + wait for the copies, after which the image buffer is free again
+int rd_stream_bands_drain(rd_platform* p);
+int rd_stream_bands_finish(rd_platform* p);
 #define RD_CUDA(call)                                                                       \
     do {                                                                                    \
         cudaError_t _e = (call);                                                            \

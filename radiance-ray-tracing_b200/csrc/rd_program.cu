@@ -3,6 +3,7 @@
 // Replaces radiance/src/radiance.cpp:142-184 (descriptor set / pipeline objects, CreateShaderModule
 // through clBuildProgram with -I SHADER_LIB_PATH), :226-267 (BindPipeline, BindDescriptorSet,
 // TraceRays) and tools/genSBT.py (switch generation from sbt.json).
+#include <time.h>
 #include <nvrtc.h>
 #include <ctype.h>
 #include <stdio.h>
@@ -445,6 +446,32 @@ static std::string generate_steal_kernel(const std::vector<RaygenParam>& P)
     return s;
 }
 
+// Raygen for streamed read-back (rd_buffer_stream_to_host): the user's raygen body -- a device-function copy in
+// namespace rd_lb -- for one work-item per thread as in the plain launch, after which the block counts itself off in its
+// band's counter; the block that completes a band raises the band's flag in host-mapped memory. The host, which is
+// blocked in TraceRays / ReadBuffer anyway, watches the flags and starts each band's copy on the copy stream, so the
+// band's image rows go over PCIe while the rest of the frame is still being traced.
+static std::string generate_banded_kernel(const std::vector<RaygenParam>& P)
+{
+    std::string plist, names;
+    for (size_t i = 0; i < P.size(); ++i) { plist += P[i].type + " " + P[i].name + ", "; names += (i ? ", " : "") + P[i].name; }
+    return "\n// ---- band-reporting raygen, generated by the runtime ----\n"
+        "struct RdBandArgs { unsigned int* done; unsigned int* flags; unsigned int blocksPerBand, nBands, epoch, target, targetLast, pad; };\n"
+        "namespace rd_lb {\n"
+        "extern \"C\" __global__ void rd_raygen_banded(" + plist + "RdBandArgs a)\n{\n"
+        "    raygen(" + names + ");\n"
+        "    __syncthreads();\n"
+        "    if (threadIdx.x == 0) {\n"
+        "        const unsigned int b = blockIdx.x / a.blocksPerBand;\n"
+        "        __threadfence();\n"
+        "        if (atomicAdd(a.done + b, 1u) + 1u == (b + 1u == a.nBands ? a.targetLast : a.target)) {\n"
+        "            __threadfence_system();   // every block of the band has passed its fence\n"
+        "            *(volatile unsigned int*)(a.flags + b) = a.epoch;   // host-mapped memory\n"
+        "        }\n"
+        "    }\n"
+        "}\n}  // namespace rd_lb\n";
+}
+
 extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 {
     if (!p || !json_text) { rd_set_error("rd_sbt_load_json: null argument"); return RD_E_ARG; }
@@ -457,7 +484,8 @@ extern "C" int rd_sbt_load_json(rd_platform* p, const char* json_text)
 // ---- NVRTC ------------------------------------------------------------------------------------
 // OpenCL-C user program (+ optional sbt.json) -> sm_100a cubin. Needs no device.
 static int rd_compile_program(const char* code, unsigned size, const std::string& sbtJson, bool fmad,
-                              std::vector<char>* cubin, std::string* log, bool countRays = false, int maxDepth = 2, bool steal = false)
+                              std::vector<char>* cubin, std::string* log, bool countRays = false, int maxDepth = 2, bool steal = false,
+                              bool banded = false)
 {
     std::string src(code, size ? size : strlen(code));
     while (!src.empty() && src.back() == '\0') src.pop_back();
@@ -512,6 +540,14 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
             mainSrc += generate_steal_kernel(params);
         }
     }
+    if (banded) {
+        std::vector<RaygenParam> params;
+        if (parse_raygen_params(bare, &params)) {
+            mainSrc += "#undef RD_LEVEL\n#define RD_LEVEL 0\n#undef RD_LEVEL_PART_DONE\n#undef RD_NEXT_NS\n#define RD_NEXT_NS rd_l1\n#undef RD_LAST_LEVEL\n"
+                       "namespace rd_lb {\n#include \"rd_user_program.cl\"\n}\n";
+            mainSrc += generate_banded_kernel(params);
+        }
+    }
     std::vector<const char*> hdrNames(rd_embedded_names, rd_embedded_names + rd_embedded_count);
     std::vector<const char*> hdrSources(rd_embedded_sources, rd_embedded_sources + rd_embedded_count);
     hdrNames.push_back("rd_user_program.cl");
@@ -559,7 +595,7 @@ extern "C" int rd_shader_compile_check(const char* code, unsigned size, const ch
 {
     if (!code) { rd_set_error("rd_shader_compile_check: null argument"); return RD_E_ARG; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, sbt_json ? sbt_json : "", fmad != 0, &cubin, &log, false, 2, getenv("RD_CHECK_STEAL") != 0);
+    int rc = rd_compile_program(code, size, sbt_json ? sbt_json : "", fmad != 0, &cubin, &log, false, 2, getenv("RD_CHECK_STEAL") != 0, getenv("RD_CHECK_BANDED") != 0);
     if (rc) return rc;
     if (cubinSize) *cubinSize = cubin.size();
     rd_set_error("%.15000s", log.c_str());   // ptxas -v statistics of a successful build
@@ -573,7 +609,8 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     RD_CUDA(cudaSetDevice(p->device));
     { int drc = rd_driver_init(); if (drc) return drc; }
     std::vector<char> cubin; std::string log;
-    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth, p->optSteal != 0);
+    int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth, p->optSteal != 0,
+                                p->optStreamImage != 0);
     if (rc) return rc;
     rd_module* m = new rd_module();
     m->ptxInfo = log;
@@ -583,6 +620,8 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     if (cr != CUDA_SUCCESS) { rd_set_error("program has no __kernel named raygen"); cuModuleUnload(m->mod); delete m; return RD_E_COMPILE; }
     m->stealRaygen = 0;
     if (p->optSteal && cuModuleGetFunction(&m->stealRaygen, m->mod, "rd_raygen_steal") != CUDA_SUCCESS) m->stealRaygen = 0;
+    m->bandedRaygen = 0;
+    if (p->optStreamImage && cuModuleGetFunction(&m->bandedRaygen, m->mod, "rd_raygen_banded") != CUDA_SUCCESS) m->bandedRaygen = 0;
     // wavefront stages exist when the program defines the hooks (generate_wavefront_kernels)
     m->wfGenerate = m->wfShade = m->wfAccumulate = m->wfResolve = 0; m->wfPayloadSize = 0;
     if (cuModuleGetFunction(&m->wfGenerate, m->mod, "rd_wf_generate") == CUDA_SUCCESS &&
@@ -735,6 +774,11 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
     if (!count) count = total - first;
     if (!count) return RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
+    if (p->copyPending) {   // the previous frame's streamed read-back still owns the image: render after it
+        int drc = rd_stream_bands_finish(p);
+        if (drc) return drc;
+    }
+    p->mirrorFresh = 0;
     if (p->optWavefront) return rd_trace_rays_wavefront(p, width, height, first, count);
     rd_module* m = p->boundModule;
     CUdeviceptr dinfo; size_t infoBytes = 0;
@@ -744,6 +788,41 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
     const unsigned block = (unsigned)p->optBlock;
     const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     const unsigned full = (unsigned)(count / block), tail = (unsigned)(count % block);
+    // a frame that is going to be read back into a registered host mirror: bands of tile rows, copied out as they finish
+    if (p->mirrorObj && m->bandedRaygen && first == 0 && count == total && !tail && p->ilWorld <= 1u && (height % 4u) == 0 &&
+        ((4ull * width) % block) == 0 && (unsigned long long)total * p->mirrorItemBytes <= p->mirrorObj->size) {
+        const unsigned tileRows = height / 4u, blocksPerRow = (unsigned)(4ull * width / block);
+        // Equal bands of whole tile rows. Bands complete out of order -- one warp grazing a ridge keeps its band open for
+        // 0.2 ms -- so the host copies whichever band is ready (rd_stream_bands_drain) and the copy engine is busy from the
+        // first band on; what is exposed behind the last ray is one band.
+        struct { unsigned* done; unsigned* flags; unsigned blocksPerBand, nBands, epoch, target, targetLast, pad; } a;
+        const unsigned rowsPerBand = (tileRows + p->mirrorBands - 1u) / p->mirrorBands;
+        const unsigned nBands = (tileRows + rowsPerBand - 1u) / rowsPerBand;
+        // Counters only grow: a band of launch number e is complete at e * (its block count), so nothing has to be
+        // reset between frames. A new band layout starts over.
+        if (p->bandLayoutW != width || p->bandLayoutH != height || p->bandLayoutN != p->mirrorBands || p->bandLayoutBlock != block ||
+            p->bandEpoch >= 0x7fffffffu / (tileRows * blocksPerRow + 1u)) {
+            RD_CUDA(cudaStreamSynchronize(p->copyStream));
+            RD_CUDA(cudaMemsetAsync(p->bandDone, 0, 64 * sizeof(unsigned), p->stream));
+            RD_CUDA(cudaStreamSynchronize(p->stream));
+            for (unsigned b = 0; b < 64u; ++b) p->bandFlags[b] = 0u;
+            p->bandLayoutW = width; p->bandLayoutH = height; p->bandLayoutN = p->mirrorBands; p->bandLayoutBlock = block; p->bandEpoch = 0;
+        }
+        p->bandEpoch += 1;
+        a.done = p->bandDone; a.flags = p->bandFlagsDev; a.blocksPerBand = rowsPerBand * blocksPerRow; a.nBands = nBands; a.epoch = p->bandEpoch;
+        a.target = p->bandEpoch * rowsPerBand * blocksPerRow;
+        a.targetLast = p->bandEpoch * (tileRows - (nBands - 1u) * rowsPerBand) * blocksPerRow; a.pad = 0u;
+        const unsigned info[8] = {0u, (unsigned)total, tileW, 0u, 0u, 0u, 0u, 0u};
+        RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
+        argv.push_back(&a);
+        { extern double rd_band_t0; timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); rd_band_t0 = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; }
+        RD_CU(cuLaunchKernel(m->bandedRaygen, full, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+        p->launches += 1;
+        const size_t rowBytes = (size_t)4u * width * p->mirrorItemBytes;   // one row of tiles = 4 image rows
+        p->bandCount = nBands; p->bandCopied = 0; p->bandRows = rowsPerBand; p->bandTileRows = tileRows; p->bandRowBytes = rowBytes;
+        p->mirrorValidBytes = (size_t)tileRows * rowBytes; p->mirrorFresh = 1; p->copyPending = 1;
+        return RD_OK;
+    }
     if (full) {
         const unsigned info[8] = {(unsigned)first, (unsigned)total, tileW, 0u, p->ilWorld, p->ilRank, p->ilBandRows, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
@@ -804,6 +883,8 @@ extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned heig
     rd_module* m = p->boundModule;
     if (!m->stealRaygen) { rd_set_error("rd_trace_rays_steal: module was not created under option stealing"); return RD_E_STATE; }
     RD_CUDA(cudaSetDevice(p->device));
+    if (p->copyPending) { int drc = rd_stream_bands_finish(p); if (drc) return drc; }
+    p->mirrorFresh = 0;
     if (!p->stealCounters) {   // single process: a private counter
         unsigned char tmp[64];
         int rc = rd_steal_counter_export(p, tmp);
@@ -904,6 +985,7 @@ extern "C" int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned
     (void)raygenGroupIndex; (void)missGroupIndex; (void)hitGroupIndex;   // ignored by the reference too (radiance.cpp:242-247)
     int rc = rd_trace_rays_async(p, width, height);
     if (rc) return rc;
+    if (p->copyPending) { rc = rd_stream_bands_drain(p); if (rc) return rc; }   // start the band copies while waiting
     RD_CUDA(cudaStreamSynchronize(p->stream));   // blocking like clFinish (radiance.cpp:261)
     uint32_t status[2] = {0, 0};
     RD_CUDA(cudaMemcpy(status, p->dstatus, 8, cudaMemcpyDeviceToHost));

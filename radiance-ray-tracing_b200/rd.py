@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
-    "rd_debug_sort_pairs", "rd_debug_exclusive_scan",
+    "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host",
 ]
 
 
@@ -63,6 +63,7 @@ def lib():
             "rd_buffer_create": [vp, sz, C.POINTER(vp)], "rd_buffer_wrap": [vp, vp, sz, C.POINTER(vp)], "rd_image_create": [vp, u, u, C.POINTER(vp)],
             "rd_image_array_create": [vp, u, u, u, C.POINTER(vp)], "rd_sampler_create": [vp, C.c_uint32, C.c_uint32, C.POINTER(vp)],
             "rd_buffer_write": [vp, vp, sz, vp, sz], "rd_buffer_read": [vp, vp, sz, vp, sz],
+            "rd_buffer_stream_to_host": [vp, vp, vp, u, u],
             "rd_image_write": [vp, vp, u, u, sz, vp], "rd_image_read": [vp, vp, u, u, sz, vp],
             "rd_handle_free": [vp, vp], "rd_blas_build": [vp, vp, u, vp, u, C.POINTER(vp)],
             "rd_blas_build_device": [vp, vp, u, vp, u, C.POINTER(vp)], "rd_blas_free": [vp, vp],
@@ -296,6 +297,14 @@ def WriteBuffer(plt, handle, size, data, offset=0):
 
 def ReadBuffer(plt, handle, size, data, offset=0):
     _check(lib().rd_buffer_read(plt.handle, handle.handle, int(size), _host_ptr(data, size), int(offset)))
+
+
+def StreamBufferToHost(plt, handle, host_ptr, item_bytes=4, bands=4):
+    """No reference counterpart. Registers page-locked host memory as the mirror of an image buffer: full-frame
+    TraceRays of modules created under option `stream_image` then copy the frame out band by band while it renders,
+    and ReadBuffer(handle, size, host_ptr) only waits for the last band. host_ptr None / 0 ends it."""
+    _check(lib().rd_buffer_stream_to_host(plt.handle, handle.handle if handle is not None else None, host_ptr or None,
+                                          int(item_bytes), int(bands)))
 
 
 def WriteImage(plt, handle, width, height, arrayIndex, data):

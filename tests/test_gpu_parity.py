@@ -600,3 +600,59 @@ def test_build_is_deterministic_and_keeps_its_shape(pkg, plt):
     s2 = scenes.build_scene(plt, b)[1][0].stats()
     assert s1 == s2 and s1["triangles"] == 2 * 224 * 224
     assert 0.08 * s1["triangles"] < s1["nodes"] < 0.13 * s1["triangles"]      # ~0.10 wide nodes per triangle (PLOC + DP collapse)
+
+
+def test_streamed_readback_delivers_the_same_frame(pkg, plt):
+    """rd_buffer_stream_to_host: a frame copied out band by band while it renders must arrive byte-identical to
+    TraceRays + ReadBuffer, for band counts that do and do not divide the tile rows, frame after frame, and must
+    fall back to the plain read for frame sizes the banding does not cover or a different destination."""
+    import torch
+    rd, scenes = pkg.rd, pkg.scenes
+    b = scenes.heightfield_scene(96, 640, 360)
+    tlas, _ = scenes.build_scene(plt, b)
+    plt.set_option("stream_image", 1)
+    try:
+        pipe, module = scenes.make_pipeline(plt, "primary")
+    finally:
+        plt.set_option("stream_image", 0)
+    for (w, h), bands in (((640, 360), 4), ((640, 360), 7), ((640, 360), 64), ((256, 64), 1), ((203, 151), 4)):
+        ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 1, 1, 0))
+        rd.BindPipeline(plt, pipe)
+        rd.BindDescriptorSet(plt, ds.descriptors)
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        plain = ds.read_image()
+        assert (plain[..., 3] == 255).all()
+        host = torch.zeros(h * w * 4, dtype=torch.uint8).pin_memory()
+        rd.StreamBufferToHost(plt, ds.rdImage, host.data_ptr(), 4, bands)
+        try:
+            for frame in range(3):
+                host.fill_(7)
+                rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
+                launches = plt.launch_count()
+                rd.TraceRays(plt, 0, 0, 0, w, h)
+                assert plt.launch_count() - launches == (1 if (4 * w) % 128 == 0 and h % 4 == 0 else 2)
+                rd.ReadBuffer(plt, ds.rdImage, plain.nbytes, host.data_ptr())
+                assert np.array_equal(host.numpy().reshape(h, w, 4), plain), (w, h, bands, frame)
+            # a read into other memory right after a streamed frame is the plain copy
+            rd.TraceRaysAsync(plt, w, h)
+            assert np.array_equal(ds.read_image(), plain)
+            # two frames back to back without a read in between: the second waits for the first one's copies
+            rd.TraceRaysAsync(plt, w, h)
+            rd.TraceRaysAsync(plt, w, h)
+            rd.ReadBuffer(plt, ds.rdImage, plain.nbytes, host.data_ptr())
+            assert np.array_equal(host.numpy().reshape(h, w, 4), plain)
+        finally:
+            rd.StreamBufferToHost(plt, None, None)
+    # a module created without the option keeps working with a registered mirror (plain launch + plain read)
+    pipe2, _ = scenes.make_pipeline(plt, "primary")
+    ds = scenes.DeviceScene(plt, b, tlas, 640, 360, scenes.rtprop(0, 1, 1, 0))
+    rd.BindPipeline(plt, pipe2)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    host = torch.zeros(360 * 640 * 4, dtype=torch.uint8).pin_memory()
+    rd.StreamBufferToHost(plt, ds.rdImage, host.data_ptr(), 4, 4)
+    try:
+        rd.TraceRays(plt, 0, 0, 0, 640, 360)
+        rd.ReadBuffer(plt, ds.rdImage, host.numel(), host.data_ptr())
+    finally:
+        rd.StreamBufferToHost(plt, None, None)
+    assert np.array_equal(host.numpy().reshape(360, 640, 4), ds.read_image())
