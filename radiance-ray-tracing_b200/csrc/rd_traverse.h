@@ -288,6 +288,18 @@ struct RdStackEntry { rd_u32 x, y; };
 #define RD_FLUSH_DIV 1     // flush when >= 1/RD_FLUSH_DIV of the active lanes hold pending triangles; 1 = at once
                            // (measured fastest on C2: 4026 vs 3917 Mrays/s for 2..4, profiles/exp_variants_r1d.log)
 #endif
+#ifndef RD_COOP_TRI
+#define RD_COOP_TRI 0      // ablation: warp-cooperative triangle phase (rd_traverse) -- the (ray, triangle) pairs the lanes of a
+                           // warp hold are dealt out over all lanes through shared memory, one exact test per lane per round,
+                           // finished lanes keep working for the others. Same image (px_diff 0), but slower everywhere:
+                           // C2 primary 4373 -> 4091 Mrays/s (registers capped at 72; 3669 uncapped at 96), 10 M-triangle
+                           // primary 2978 -> 2885, C3 path.cl inline 773 -> 494, wavefront (shadow rays in the shade
+                           // stage) 1701 -> 1607: the ballots, three warp barriers and 3 x 16 B of staging per pair cost more
+                           // than the exact test run at 6 of 32 lanes (profiles/README_r1.md)
+#endif
+#ifndef RD_COOP_WARPS
+#define RD_COOP_WARPS 8    // warps per block the staging array is sized for (block <= 256)
+#endif
 #define RD_STACK_ALLOC (RD_STACK_ENTRIES + RD_PEND_MAX)
 
 struct RdTraversal {
@@ -437,6 +449,72 @@ struct RdTraversal {
         }
         return true;
     }
+
+#if defined(__CUDA_ARCH__) && RD_COOP_TRI
+    // step() cut in two for the warp-cooperative triangle phase of rd_traverse (RD_COOP_TRI): head() = node phase and
+    // instance entry, leaves the triangle records the node exposed in (*gbase, *gbits) and returns true when the lane
+    // entered an instance (it then skips the rest of the iteration); tail() = pop phase, false when the ray is done.
+    template <class OnCandidate>
+    RD_HD bool head(const RdScene* scene, OnCandidate& onCandidate, rd_u32* gbase, rd_u32* gbits)
+    {
+        RdStackEntry tg; tg.x = 0; tg.y = 0;
+        *gbase = 0; *gbits = 0;
+        if (ng.y > 0x00ffffffu) {
+            const rd_u32 bit = 31u - (rd_u32)RD_CLZ(ng.y);
+            const rd_u32 imask = ng.y & 0xffu;
+            ng.y &= ~(1u << bit);
+            if (ng.y > 0x00ffffffu) push(scene, ng);
+            const rd_u32 slot = (bit - 24u) ^ (f.octinv4 & 0xffu);
+            const rd_u32 rel = (rd_u32)RD_POPC(imask & ~(0xffffffffu << slot));
+            const RdNode8* n = nodes + (ng.x + rel);
+            RdU4 n0, n1, n2, n3, n4;
+            RD_LOAD_U4(n0, &n->w[0]); RD_LOAD_U4(n1, &n->w[1]); RD_LOAD_U4(n2, &n->w[2]);
+            RD_LOAD_U4(n3, &n->w[3]); RD_LOAD_U4(n4, &n->w[4]);
+            onCandidate.countNode();
+            const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
+            ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
+            const rd_u32 leafBits = hm & 0x00ffffffu;
+            if (leafBits) {
+                if (blasSp < 0) { tg.x = n1.y; tg.y = leafBits; }
+                else { *gbase = n1.y; *gbits = leafBits; }
+            }
+        } else if (ng.y) {
+            tg = ng; ng.x = 0; ng.y = 0;
+        }
+        if (blasSp < 0 && tg.y) {
+            const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
+            tg.y &= tg.y - 1u;
+            const rd_u32 ii = scene->leafInstances[tg.x + k];
+            if (tg.y) push(scene, tg);
+            if (ng.y > 0x00ffffffu) push(scene, ng);
+            blasSp = sp;
+            curInst = scene->instances + ii;
+            const float* m = curInst->inv;
+            const float lox = rd_row_dot(m + 0, wox, woy, woz, 1.0f), loy = rd_row_dot(m + 4, wox, woy, woz, 1.0f),
+                        loz = rd_row_dot(m + 8, wox, woy, woz, 1.0f);
+            const float ldx = rd_row_dot(m + 0, wdx, wdy, wdz, 0.0f), ldy = rd_row_dot(m + 4, wdx, wdy, wdz, 0.0f),
+                        ldz = rd_row_dot(m + 8, wdx, wdy, wdz, 0.0f);
+            rd_frame_set(f, lox, loy, loz, ldx, ldy, ldz);
+            nodes = curInst->nodes; tris = curInst->tris;
+            ng.x = 0; ng.y = 0x80000000u;
+            return true;
+        }
+        return false;
+    }
+
+    RD_HD bool tail(const RdScene* scene)
+    {
+        if (ng.y <= 0x00ffffffu) {
+            if (blasSp >= 0 && sp == blasSp) {
+                blasSp = -1; nodes = scene->nodes;
+                rd_frame_set(f, wox, woy, woz, wdx, wdy, wdz);
+            }
+            if (sp == 0) return false;
+            ng = stack[--sp];
+        }
+        return true;
+    }
+#endif
 };
 
 // Walks the two-level structure for one ray. Returns true iff something was accepted; `hit` holds
@@ -455,9 +533,75 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
     const unsigned together = __activemask();
 #endif
     T.begin(stackMemory, scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
+#if defined(__CUDA_ARCH__) && RD_COOP_TRI && RD_RECONVERGE
+    {
+        // slot s of a warp: [0] = {o.xyz, d.x}, [1] = {d.y, d.z, triangle address}, [2] = result {t, b1, b2, prim}
+        __shared__ float4 rdCoop[RD_COOP_WARPS][32][3];
+        float4 (*slots)[3] = rdCoop[(threadIdx.x >> 5) % RD_COOP_WARPS];
+        const unsigned lane = threadIdx.x & 31u, below = together & ((1u << lane) - 1u);
+        const unsigned worker = (unsigned)__popc(below), workers = (unsigned)__popc(together);
+        bool alive = true;
+        for (;;) {
+            rd_u32 gbase = 0, gbits = 0;
+            bool entered = false;
+            if (alive) entered = T.head(scene, onCandidate, &gbase, &gbits);
+            // ---- triangle phase, all lanes of the warp (finished ones work for the others)
+            for (;;) {
+                if (!__any_sync(together, gbits != 0u)) break;
+                unsigned nslots = 0, mine[3] = {0u, 0u, 0u}, count = 0;
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const unsigned m = __ballot_sync(together, gbits != 0u);
+                    if (m == 0u || nslots + (unsigned)__popc(m) > workers) break;
+                    if (gbits) {
+                        const rd_u32 tri = gbase + ((rd_u32)__ffs((int)gbits) - 1u);
+                        gbits &= gbits - 1u;
+                        const unsigned s = nslots + (unsigned)__popc(m & below);
+                        const unsigned long long addr = (unsigned long long)(T.tris + tri);
+                        slots[s][0] = make_float4(T.f.ox, T.f.oy, T.f.oz, T.f.dx);
+                        slots[s][1] = make_float4(T.f.dy, T.f.dz, __uint_as_float((unsigned)addr), __uint_as_float((unsigned)(addr >> 32)));
+                        mine[k] = s; count = (unsigned)k + 1u;
+                        onCandidate.countTri();
+                    }
+                    nslots += (unsigned)__popc(m);
+                }
+                __syncwarp(together);
+                if (worker < nslots) {
+                    const float4 ra = slots[worker][0], rb = slots[worker][1];
+                    const RdTri* tr = (const RdTri*)(((unsigned long long)__float_as_uint(rb.w) << 32) | __float_as_uint(rb.z));
+                    RdF4 a, b, c;
+                    RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
+                    float t, b1, b2;
+                    const bool ok = rd_intersect_triangle(ra.x, ra.y, ra.z, ra.w, rb.x, rb.y, a.x, a.y, a.z, b.x, b.y, b.z,
+                                                          c.x, c.y, c.z, &t, &b1, &b2);
+                    slots[worker][2] = make_float4(ok ? t : -1.0f, b1, b2, a.w);
+                }
+                __syncwarp(together);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    if (k < (int)count && alive) {
+                        const float4 r = slots[mine[k]][2];
+                        const float t = r.x; const rd_u32 prim = RD_F2U(r.w);
+                        if (t > 0.0f && t > T.tmin && t < T.tmax &&
+                            (t < T.hit.t || (t == T.hit.t && (T.curInst->instanceID < T.hit.inst ||
+                                                              (T.curInst->instanceID == T.hit.inst && prim < T.hit.prim))))) {
+                            T.hit.t = t; T.hit.b1 = r.y; T.hit.b2 = r.z; T.hit.prim = prim; T.hit.inst = T.curInst->instanceID;
+                            T.tbest = t; T.any = true;
+                            if (!onCandidate(T.hit)) { alive = false; gbits = 0u; }
+                        }
+                    }
+                }
+                __syncwarp(together);
+            }
+            if (alive && !entered) alive = T.tail(scene);
+            if (!__any_sync(together, alive)) break;
+        }
+    }
+#else
     while (T.step(scene, onCandidate)) {}
 #if defined(__CUDA_ARCH__) && RD_RECONVERGE
     __syncwarp(together);
+#endif
 #endif
     hit = T.hit;
     return T.any;
