@@ -451,6 +451,10 @@ static std::string generate_steal_kernel(const std::vector<RaygenParam>& P)
 // band's counter; the block that completes a band raises the band's flag in host-mapped memory. The host, which is
 // blocked in TraceRays / ReadBuffer anyway, watches the flags and starts each band's copy on the copy stream, so the
 // band's image rows go over PCIe while the rest of the frame is still being traced.
+// Cost of the reporting, measured on C2 (tools/exp_variants.py, "banded" variants): plain raygen 0.467 ms, banded 0.496 ms;
+// without the per-block __threadfence 0.481, without fence and barrier 0.476 (RD_BAND_NOFENCE / RD_BAND_NOSYNC exist for
+// that timing experiment only -- without the fence a band could be copied before its last stores have landed). The fence
+// holds each of the 16 200 blocks' SM slot about 1 us longer.
 static std::string generate_banded_kernel(const std::vector<RaygenParam>& P)
 {
     std::string plist, names;
@@ -460,10 +464,10 @@ static std::string generate_banded_kernel(const std::vector<RaygenParam>& P)
         "namespace rd_lb {\n"
         "extern \"C\" __global__ void rd_raygen_banded(" + plist + "RdBandArgs a)\n{\n"
         "    raygen(" + names + ");\n"
-        "    __syncthreads();\n"
+        "#ifndef RD_BAND_NOSYNC\n    __syncthreads();\n#endif\n"
         "    if (threadIdx.x == 0) {\n"
         "        const unsigned int b = blockIdx.x / a.blocksPerBand;\n"
-        "        __threadfence();\n"
+        "#ifndef RD_BAND_NOFENCE\n        __threadfence();\n#endif\n"
         "        if (atomicAdd(a.done + b, 1u) + 1u == (b + 1u == a.nBands ? a.targetLast : a.target)) {\n"
         "            __threadfence_system();   // every block of the band has passed its fence\n"
         "            *(volatile unsigned int*)(a.flags + b) = a.epoch;   // host-mapped memory\n"
