@@ -3,6 +3,7 @@
 // usage: sample_shim <program.cl> <sbt.json> <out.rgba> [width height]
 // Scene: a floor quad and a box, one instance each (MeshInfo is indexed by instanceIndex), one material per
 // mesh, one directional light; descriptors in the order of samples/shader.cl:176-190.
+#include <cstdlib>
 #include <cstdio>
 #include <string>
 #include <vector>
@@ -78,6 +79,9 @@ int main(int argc, char** argv)
     char *code = nullptr, *sbt = nullptr; size_t codeSize = 0, sbtSize = 0;
     if (RD::read_kernel_file_str(argv[1], &code, &codeSize) || RD::read_kernel_file_str(argv[2], &sbt, &sbtSize)) return 3;
     RD::LoadShaderBindingTable(plt, sbt);   // extension: replaces the offline tools/genSBT.py step
+    // RD_SAMPLE_STREAM=1: the same loop with the B200 extension that copies the frame out band by band while it renders
+    const bool streamed = getenv("RD_SAMPLE_STREAM") != nullptr;
+    if (streamed && rd_set_option(plt->impl, "stream_image", 1)) return 5;
     RD::ShaderModule module = RD::CreateShaderModule(plt, code, (unsigned)codeSize, (char*)"raygen");
     RD::Pipeline pipeline = RD::CreatePipeline({2, layout, {module}, {}});
     RD::BindPipeline(plt, pipeline);
@@ -85,6 +89,7 @@ int main(int argc, char** argv)
 
     // progressive loop of samples/sample1.cpp:466-490: two calls of two samples each
     std::vector<unsigned char> image(width * height * RD_CHANNEL);
+    if (streamed) RD::StreamBufferToHost(plt, rdImage, image.data(), RD_CHANNEL, 8);
     for (int call = 0; call < 2; ++call) {
         RD::WriteBuffer(plt, rdRTProp, sizeof(RTProp), &RTProp);
         RD::TraceRays(plt, 0, 0, 0, width, height);

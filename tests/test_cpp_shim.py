@@ -47,6 +47,12 @@ def test_cpp_sample_matches_python_mirror(pkg, plt, tmp_path):
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert r.returncode == 0, r.stdout
     img_cpp = np.fromfile(out, np.uint8).reshape(h, w, 4)
+    # the same program with the streamed read-back (RD::StreamBufferToHost) delivers the same bytes
+    out2 = str(tmp_path / "shim_streamed.rgba")
+    r = subprocess.run([exe, os.path.join(PROG, "primary.cl"), os.path.join(PROG, "primary_sbt.json"), out2, str(w), str(h)],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=dict(os.environ, RD_SAMPLE_STREAM="1"))
+    assert r.returncode == 0, r.stdout
+    assert np.array_equal(np.fromfile(out2, np.uint8).reshape(h, w, 4), img_cpp)
     # the same scene through the Python mirror
     lo, hi, t = -0.3, 0.3, 0.6
     bv = np.array([[lo, 0, lo], [lo, t, lo], [hi, t, lo], [hi, 0, lo], [lo, 0, hi], [hi, 0, hi], [hi, t, hi], [lo, t, hi],
