@@ -167,6 +167,10 @@ RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, f
 #ifndef RD_DEQUANT_I2F
 #define RD_DEQUANT_I2F 1
 #endif
+#ifndef RD_NODE_UNROLL_H
+#define RD_NODE_UNROLL_H 2   // ablation: 1 keeps the loop over the two node halves of rd_node_test rolled (4 % less code in kernels that
+#define RD_NODE_UNROLL_J 4   // inline several traversals). Measured on C3 path.cl, 4 spp: wavefront 1726 -> 1652, inline 805 -> 697 Mrays/s
+#endif
 #ifndef RD_INNER_FROM_IMASK
 #define RD_INNER_FROM_IMASK 1   // inner-child byte mask of rd_node_test spread from the imask nibble (2 IMAD on the FMA pipe) instead of
                                 // being derived from the meta bytes (4 ALU instructions): C2 4450 -> 4490 Mrays/s, 10 M unchanged, same image
@@ -225,7 +229,11 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 #endif
     rd_u32 hitmask = 0;
 #if defined(__CUDA_ARCH__)
+#if RD_NODE_UNROLL_H > 1
 #pragma unroll
+#else
+#pragma unroll 1
+#endif
 #endif
     for (int h = 0; h < 2; ++h) {
         const rd_u32 meta4 = h ? n1.w : n1.z;
@@ -253,7 +261,11 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
         const rd_u32 ny = f.iy < 0.0f ? qhy : qly, fy = f.iy < 0.0f ? qly : qhy;
         const rd_u32 nz = f.iz < 0.0f ? qhz : qlz, fz = f.iz < 0.0f ? qlz : qhz;
 #if defined(__CUDA_ARCH__)
+#if RD_NODE_UNROLL_J > 1
 #pragma unroll
+#else
+#pragma unroll 1
+#endif
 #endif
         for (int j = 0; j < 4; ++j) {
             const int sh = 8 * j;
