@@ -173,8 +173,9 @@ static double rd_now_us()
     timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts);
     return ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3;
 }
-double rd_band_t0 = 0.0;
+static double rd_band_t0 = 0.0;
 static double rd_band_seen[64];
+void rd_stream_bands_mark_launch() { static const bool trace = getenv("RD_BAND_TRACE") != 0; if (trace) rd_band_t0 = rd_now_us(); }
 
 int rd_stream_bands_drain(rd_platform* p)
 {

@@ -82,6 +82,7 @@ void rd_set_error(const char* fmt, ...);
 // finish = drain + wait for the copies, after which the image buffer is free again
 int rd_stream_bands_drain(rd_platform* p);
 int rd_stream_bands_finish(rd_platform* p);
+void rd_stream_bands_mark_launch();   // developer knob RD_BAND_TRACE: host time of the frame's launch
 #define RD_CUDA(call)                                                                       \
     do {                                                                                    \
         cudaError_t _e = (call);                                                            \

@@ -819,7 +819,7 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
         const unsigned info[8] = {0u, (unsigned)total, tileW, 0u, 0u, 0u, 0u, 0u};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         argv.push_back(&a);
-        { extern double rd_band_t0; timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); rd_band_t0 = ts.tv_sec * 1e6 + ts.tv_nsec * 1e-3; }
+        rd_stream_bands_mark_launch();
         RD_CU(cuLaunchKernel(m->bandedRaygen, full, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
         const size_t rowBytes = (size_t)4u * width * p->mirrorItemBytes;   // one row of tiles = 4 image rows
