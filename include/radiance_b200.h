@@ -48,6 +48,12 @@ int rd_platform_destroy(rd_platform* p);
 /* stream used for all work of this platform (cudaStream_t as void*), for external event timing */
 void* rd_platform_stream(rd_platform* p);
 int rd_platform_sync(rd_platform* p);
+/* Device status flags: out[0] = traversal-stack overflow, out[1] = traceRay nested deeper than option max_trace_depth.
+ * Every call that synchronises the platform stream (rd_trace_rays, rd_platform_sync, rd_buffer_read, rd_steal_owned,
+ * rd_trace_counters, rd_ray_count) reports a raised flag as RD_E_OVERFLOW / RD_E_STATE and clears it, so work issued
+ * through the asynchronous entry points cannot return incomplete results silently; this call reads them without
+ * synchronising (clear != 0 resets them). The reference prints and returns a miss (radiance/shader/radiance.cl:66-74). */
+int rd_status(rd_platform* p, uint32_t out[2], int clear);
 
 /* RD::CreateBuffer, radiance/src/radiance.cpp:133-140 */
 int rd_buffer_create(rd_platform* p, size_t size, rd_handle* out);

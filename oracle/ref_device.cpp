@@ -198,6 +198,48 @@ void ref_generate_ray(const void* cam48, const unsigned int* rand3, size_t index
     for (int k = 0; k < 3; ++k) { o3[k] = o[k]; d3[k] = d[k]; }
 }
 
+// Known answers of the reference's library functions (radiance/shader/pbr.cl, math.cl) as samples/shader.cl sees them.
+// fn: 0 BRDF(L,V,N,metallic,roughness,albedo)            in 14 -> out 3      pbr.cl:147-170
+//     1 refract(V,H,eta)                                 in 7  -> out 3      pbr.cl:176-186
+//     2 G_pbrt(wo,wi,N,roughness)                        in 10 -> out 1      pbr.cl:75-96
+//     3 sampleMicrofacetBRDF_transm(V,N,base,m,r,tr,ior,random) in 16 -> out 6 (direction, nextFactor)  pbr.cl:289-385
+//     4 microfacetBRDF(L,V,N,albedo,m,r,tr,ior)          in 16 -> out 3      pbr.cl:268-287
+//     5 GetNormalSpace(normal)                           in 3  -> out 16     math.cl:269-298
+//     6 sampleMicrofacetBRDF(V,N,base,m,r,random)        in 14 -> out 6      pbr.cl:199-266
+// Returns the output stride (floats per item).
+int ref_library_kat(int fn, const float* in, size_t n, float* out)
+{
+    using namespace ref_shader1;
+    static const int inS[7] = {14, 7, 10, 16, 16, 3, 14}, outS[7] = {3, 3, 1, 6, 3, 16, 6};
+    if (fn < 0 || fn > 6) return 0;
+    for (size_t i = 0; i < n; ++i) {
+        const float* a = in + i * inS[fn];
+        float* o = out + i * outS[fn];
+        rd_float3 r, f(0.0f, 0.0f, 0.0f);
+        switch (fn) {
+        case 0: r = BRDF(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), rd_float3(a[6], a[7], a[8]), a[9], a[10],
+                         rd_float3(a[11], a[12], a[13]));
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; break;
+        case 1: r = refract(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), a[6]);
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; break;
+        case 2: o[0] = G_pbrt(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), rd_float3(a[6], a[7], a[8]), a[9]); break;
+        case 3: r = sampleMicrofacetBRDF_transm(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), rd_float3(a[6], a[7], a[8]),
+                                                a[9], a[10], a[11], a[12], rd_float3(a[13], a[14], a[15]), &f);
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = f.x; o[4] = f.y; o[5] = f.z; break;
+        case 4: r = microfacetBRDF(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), rd_float3(a[6], a[7], a[8]),
+                                   rd_float3(a[9], a[10], a[11]), a[12], a[13], a[14], a[15]);
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; break;
+        case 5: { mat4x4 m; for (int k = 0; k < 16; ++k) m[k] = 0.0f;
+                  GetNormalSpace(rd_float3(a[0], a[1], a[2]), &m);
+                  for (int k = 0; k < 16; ++k) o[k] = m[k]; break; }
+        case 6: r = sampleMicrofacetBRDF(rd_float3(a[0], a[1], a[2]), rd_float3(a[3], a[4], a[5]), rd_float3(a[6], a[7], a[8]),
+                                         a[9], a[10], rd_float3(a[11], a[12], a[13]), &f);
+                o[0] = r.x; o[1] = r.y; o[2] = r.z; o[3] = f.x; o[4] = f.y; o[5] = f.z; break;
+        }
+    }
+    return outS[fn];
+}
+
 #define RD_RAYGEN_ARGS(NS) \
     (NS::RayTraceProperties*)args[0], (float*)args[1], (uchar*)args[2], (NS::PhysicalCamera*)args[3], \
     (NS::SceneProperties*)args[4], (NS::MeshInfo*)args[5], (float*)args[6], (uint*)args[7], (float*)args[8], \

@@ -29,6 +29,15 @@ def available():
     return os.path.exists(_SO)
 
 
+def sample_sources():
+    """(samples/shader.cl, samples/sbt.json) of the reference, unmodified, as oracle/Makefile copied them into
+    the git-ignored _ref/samples/ (config C1: the reference's own user program runs on the GPU); None if absent."""
+    cl, sbt = os.path.join(_HERE, "_ref", "samples", "shader.cl"), os.path.join(_HERE, "_ref", "samples", "sbt.json")
+    if not (os.path.exists(cl) and os.path.exists(sbt)):
+        return None
+    return open(cl).read(), open(sbt).read()
+
+
 _lib = None
 
 
@@ -54,6 +63,8 @@ def lib():
         L.ref_intersect_triangle.argtypes = [C.c_void_p] * 4
         L.ref_generate_ray.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p]
         L.ref_raygen_shader1.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]
+        L.ref_library_kat.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_void_p]
+        L.ref_library_kat.restype = C.c_int
         L.ref_raygen.argtypes = [C.c_int, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int]
         assert C.sizeof(RefInstance) == 80
         _lib = L
@@ -138,6 +149,20 @@ def generate_ray(cam48, rand3, index):
     o, d = np.zeros(3, np.float32), np.zeros(3, np.float32)
     lib().ref_generate_ray(cam.ctypes.data, r.ctypes.data, int(index), o.ctypes.data, d.ctypes.data)
     return o, d
+
+
+LIBRARY_KAT = {"BRDF": (0, 14, 3), "refract": (1, 7, 3), "G_pbrt": (2, 10, 1), "sampleMicrofacetBRDF_transm": (3, 16, 6),
+               "microfacetBRDF": (4, 16, 3), "GetNormalSpace": (5, 3, 16), "sampleMicrofacetBRDF": (6, 14, 6)}
+
+
+def library_kat(name, inputs):
+    """The reference's pbr.cl / math.cl function `name` on rows of flat float inputs (argument order of the
+    function, vectors expanded); returns rows of outputs (oracle/ref_device.cpp ref_library_kat)."""
+    fn, ins, outs = LIBRARY_KAT[name]
+    a = _f32(inputs).reshape(-1, ins)
+    out = np.zeros((a.shape[0], outs), np.float32)
+    assert lib().ref_library_kat(fn, a.ctypes.data, a.shape[0], out.ctypes.data) == outs
+    return out
 
 
 def raygen_shader1(args, global_size, first=0, count=None, nthreads=None):

@@ -38,6 +38,9 @@ __global__ void rd_k_centroid_bounds(const RdF4* lo, const RdF4* hi, rd_u32 n, u
     for (rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const RdF4 l = lo[i], h = hi[i];
         const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
+        // a NaN / Inf coordinate (or a box whose centre overflows) is refused by the host: bounds[6] = count of such primitives
+        if (!(fabsf(c[0]) < 3.0e38f && fabsf(c[1]) < 3.0e38f && fabsf(c[2]) < 3.0e38f &&
+              fabsf(h.x - l.x) < 3.0e38f && fabsf(h.y - l.y) < 3.0e38f && fabsf(h.z - l.z) < 3.0e38f)) atomicAdd(&bounds[6], 1u);
 #pragma unroll
         for (int a = 0; a < 3; ++a) { mn[a] = fminf(mn[a], c[a]); mx[a] = fmaxf(mx[a], c[a]); }
     }
@@ -120,13 +123,16 @@ __global__ void rd_k_ploc_nearest(RdPlocSide A, rd_u32 m, int radius, rd_u32* ne
     const RdF4 l = A.lo[i], h = A.hi[i];
     const int j0 = (int)i - radius < 0 ? 0 : (int)i - radius;
     const int j1 = (int)i + radius >= (int)m ? (int)m - 1 : (int)i + radius;
-    float best = 3.0e38f; rd_u32 bj = i;
+    float best = __int_as_float(0x7f800000); rd_u32 bj = i;
     for (int j = j0; j <= j1; ++j) {
         if (j == (int)i) continue;
         const RdF4 a = A.lo[j], b = A.hi[j];
         const float ex = fmaxf(h.x, b.x) - fminf(l.x, a.x), ey = fmaxf(h.y, b.y) - fminf(l.y, a.y),
                     ez = fmaxf(h.z, b.z) - fminf(l.z, a.z);
-        const float area = ex * ey + ey * ez + ez * ex;
+        float area = ex * ey + ey * ez + ez * ex;
+        // NaN / Inf / overflowing areas (a non-finite vertex) stay comparable, so the pair with the smallest (area, i, j)
+        // is always mutual and every round merges at least once -- the clustering terminates on any input
+        area = area < 3.0e38f ? area : 3.0e38f;
         // the same pair must score the same from both ends and ties must resolve the same way for a merge to be
         // mutual: area is symmetric, ties go to the lower index
         if (area < best) { best = area; bj = (rd_u32)j; }
@@ -181,13 +187,14 @@ __global__ void __launch_bounds__(1024) rd_k_ploc_small(RdBinTree T, RdPlocSide 
             const RdF4 l = A.lo[i], h = A.hi[i];
             const int j0 = (int)i - radius < 0 ? 0 : (int)i - radius;
             const int j1 = (int)i + radius >= (int)m ? (int)m - 1 : (int)i + radius;
-            float best = 3.0e38f; rd_u32 bj = i;
+            float best = __int_as_float(0x7f800000); rd_u32 bj = i;
             for (int j = j0; j <= j1; ++j) {
                 if (j == (int)i) continue;
                 const RdF4 a = A.lo[j], b = A.hi[j];
                 const float ex = fmaxf(h.x, b.x) - fminf(l.x, a.x), ey = fmaxf(h.y, b.y) - fminf(l.y, a.y),
                             ez = fmaxf(h.z, b.z) - fminf(l.z, a.z);
-                const float area = ex * ey + ey * ez + ez * ex;
+                float area = ex * ey + ey * ez + ez * ex;
+                area = area < 3.0e38f ? area : 3.0e38f;   // NaN / Inf / overflow: still comparable, so a round always has a mutual pair
                 if (area < best) { best = area; bj = (rd_u32)j; }
             }
             nearest[i] = bj;
@@ -291,12 +298,16 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     RD_CUDA(tmp.alloc(&dbounds, 8));
     RD_CUDA(tmp.alloc(&keysA, n)); RD_CUDA(tmp.alloc(&keysB, n));
     RD_CUDA(tmp.alloc(&valsA, n)); RD_CUDA(tmp.alloc(&valsB, n));
-    const unsigned init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    const unsigned init[8] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u, 0u, 0u};   // [6] = non-finite primitive boxes
     RD_CUDA(cudaMemcpyAsync(dbounds, init, sizeof(init), cudaMemcpyHostToDevice, st));
     unsigned rb = rd_grid(n); if (rb > (unsigned)p->smCount * 8) rb = p->smCount * 8;
     rd_k_centroid_bounds<<<rb, RD_BT, 0, st>>>(dlo, dhi, n, dbounds);
     rd_k_morton<<<rd_grid(n), RD_BT, 0, st>>>(dlo, dhi, n, dbounds, keysA, valsA);
     p->launches += 2;
+    unsigned nonFinite = 0;   // device -> pageable host: returns once the value has arrived
+    RD_CUDA(cudaMemcpyAsync(&nonFinite, dbounds + 6, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    RD_CUDA(cudaStreamSynchronize(st));
+    if (nonFinite) { rd_set_error("BuildAccelStruct: %u primitive(s) with NaN / Inf coordinates", nonFinite); return RD_E_ARG; }
     RdSortScratch sortScratch;
     const size_t tableCount = 256u * (size_t)rd_sort_blocks(n);
     RD_CUDA(tmp.alloc(&sortScratch.hist, 8 * 256)); RD_CUDA(tmp.alloc(&sortScratch.table, tableCount));
@@ -496,7 +507,7 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
     if (n) RD_CUDA(cudaMemcpyAsync(o->dinst, inst.data(), (size_t)n * sizeof(RdInstance), cudaMemcpyHostToDevice, st));
     RdScene S; memset(&S, 0, sizeof(S));
     S.nodes = r.nodes; S.leafInstances = r.leafPrim; S.instances = (const RdInstance*)o->dinst;
-    S.instanceCount = n; S.nodeCount = r.nodeCount; S.status = p->dstatus;
+    S.instanceCount = n; S.nodeCount = r.nodeCount; S.status = p->dstatus; S.rayCounter = (rd_u64*)p->dRayCounter;
     RD_CUDA(cudaMalloc(&o->dptr, sizeof(RdScene)));
     RD_CUDA(cudaMemcpyAsync(o->dptr, &S, sizeof(S), cudaMemcpyHostToDevice, st));
     RD_CUDA(cudaStreamSynchronize(st));

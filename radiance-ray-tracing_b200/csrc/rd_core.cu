@@ -51,8 +51,15 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
         cudaMemPool_t pool; unsigned long long keep = ~0ull;
         if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
     }
-    RD_CUDA(cudaMalloc(&p->dstatus, 64));
-    RD_CUDA(cudaMemset(p->dstatus, 0, 64));
+    {
+        void* hs = 0; void* ds = 0;
+        RD_CUDA(cudaHostAlloc(&hs, 64, cudaHostAllocMapped));
+        memset(hs, 0, 64);
+        RD_CUDA(cudaHostGetDevicePointer(&ds, hs, 0));
+        p->hstatus = (volatile uint32_t*)hs; p->dstatus = (uint32_t*)ds;
+    }
+    RD_CUDA(cudaMalloc(&p->dRayCounter, 64));
+    RD_CUDA(cudaMemset(p->dRayCounter, 0, 64));
     RD_CUDA(cudaMalloc(&p->dcounters, 64));
     RD_CUDA(cudaMemset(p->dcounters, 0, 64));
     RD_CUDA(cudaDeviceGetAttribute(&p->smCount, cudaDevAttrMultiProcessorCount, device));
@@ -69,7 +76,8 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     cudaStreamSynchronize(p->stream);
     rd_wf_release(p);
     { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
-    cudaFree(p->dstatus);
+    cudaFreeHost((void*)p->hstatus);
+    cudaFree(p->dRayCounter);
     cudaFree(p->dcounters);
     if (p->copyStream) { cudaStreamSynchronize(p->copyStream); cudaStreamDestroy(p->copyStream); }
     if (p->bandDone) cudaFree(p->bandDone);
@@ -81,11 +89,33 @@ extern "C" int rd_platform_destroy(rd_platform* p)
 
 extern "C" void* rd_platform_stream(rd_platform* p) { return p ? (void*)p->stream : 0; }
 
+// Device status flags (traversal-stack overflow, traceRay nested deeper than option max_trace_depth). They live in
+// host-mapped memory, so looking at them costs nothing; every entry point that has just synchronised the platform
+// stream calls this, reports the condition once and clears it -- work launched through the asynchronous entry points
+// (rd_trace_rays_async / _range / _interleaved / _steal, rd_trace_ray_list) cannot come back incomplete with RD_OK.
+int rd_check_status(rd_platform* p, const char* where)
+{
+    const uint32_t s0 = p->hstatus[0], s1 = p->hstatus[1];
+    if (!(s0 | s1)) return RD_OK;
+    p->hstatus[0] = 0u; p->hstatus[1] = 0u;
+    if (s0) { rd_set_error("%s: traversal stack overflow on the device (results incomplete)", where); return RD_E_OVERFLOW; }
+    rd_set_error("%s: traceRay nested deeper than option max_trace_depth (%ld)", where, p->optMaxDepth);
+    return RD_E_STATE;
+}
+
+extern "C" int rd_status(rd_platform* p, uint32_t out[2], int clear)
+{
+    if (!p || !out) { rd_set_error("rd_status: null argument"); return RD_E_ARG; }
+    out[0] = p->hstatus[0]; out[1] = p->hstatus[1];
+    if (clear) { p->hstatus[0] = 0u; p->hstatus[1] = 0u; }
+    return RD_OK;
+}
+
 extern "C" int rd_platform_sync(rd_platform* p)
 {
     if (!p) { rd_set_error("null platform"); return RD_E_ARG; }
     RD_CUDA(cudaStreamSynchronize(p->stream));
-    return RD_OK;
+    return rd_check_status(p, "rd_platform_sync");
 }
 
 static RdHandleObj* new_handle(RdHandleKind kind)
@@ -266,12 +296,12 @@ extern "C" int rd_buffer_read(rd_platform* p, rd_handle h, size_t size, void* da
         // copies of the bands as they complete; behind the last ray only the small last band is left to move
         rc = rd_stream_bands_finish(p);
         p->mirrorFresh = 0;
-        return rc;
+        return rc ? rc : rd_check_status(p, "rd_buffer_read");
     }
     if (p->copyPending) { rc = rd_stream_bands_finish(p); if (rc) return rc; p->mirrorFresh = 0; }
     RD_CUDA(cudaMemcpyAsync(data, (const char*)o->dptr + offset, size, cudaMemcpyDeviceToHost, p->stream));
     RD_CUDA(cudaStreamSynchronize(p->stream));
-    return RD_OK;
+    return rd_check_status(p, "rd_buffer_read");
 }
 
 // Streamed read-back. The reference's render loop is TraceRays (blocking) followed by ReadBuffer of the whole image

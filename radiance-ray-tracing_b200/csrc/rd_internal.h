@@ -53,10 +53,15 @@ struct RdWfBuffers {
     unsigned capacity, payloadStride;
 };
 
+int rd_check_status(struct rd_platform* p, const char* where);   // rd_core.cu
+
 struct rd_platform {
     int device;
     cudaStream_t stream;
-    uint32_t* dstatus;        // [0] stack overflow flag, [1] traceRay nesting exceeded, [2..3] 64-bit traceRay counter (option count_rays)
+    volatile uint32_t* hstatus;   // host-mapped: [0] stack overflow flag, [1] traceRay nesting exceeded -- the device only ever writes them
+                              // when something went wrong, the host reads them for free at every call that synchronises (rd_check_status)
+    uint32_t* dstatus;        // the device address of hstatus (RdScene::status)
+    unsigned long long* dRayCounter;   // 64-bit traceRay counter (option count_rays), device memory
     unsigned long long* dcounters;   // trace counters [nodes, tris, rays] + work counter at [4]
     std::vector<uint64_t> boundArgs;
     std::vector<int> boundKinds;

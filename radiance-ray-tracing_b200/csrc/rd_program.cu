@@ -939,7 +939,7 @@ extern "C" int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, 
     RD_CUDA(cudaMemcpy(count, p->stealOwned, sizeof(unsigned), cudaMemcpyDeviceToHost));
     const unsigned n = *count < capacity ? *count : capacity;
     if (ids && n) RD_CUDA(cudaMemcpy(ids, p->stealOwned + 1, (size_t)n * sizeof(unsigned), cudaMemcpyDeviceToHost));
-    return RD_OK;
+    return rd_check_status(p, "rd_steal_owned");
 }
 
 extern "C" int rd_ray_count(rd_platform* p, uint64_t* out, int reset)
@@ -948,10 +948,10 @@ extern "C" int rd_ray_count(rd_platform* p, uint64_t* out, int reset)
     RD_CUDA(cudaSetDevice(p->device));
     RD_CUDA(cudaStreamSynchronize(p->stream));
     unsigned long long v = 0;
-    RD_CUDA(cudaMemcpy(&v, p->dstatus + 2, 8, cudaMemcpyDeviceToHost));
-    if (reset) RD_CUDA(cudaMemset(p->dstatus + 2, 0, 8));
+    RD_CUDA(cudaMemcpy(&v, p->dRayCounter, 8, cudaMemcpyDeviceToHost));
+    if (reset) RD_CUDA(cudaMemset(p->dRayCounter, 0, 8));
     *out = v;
-    return RD_OK;
+    return rd_check_status(p, "rd_ray_count");
 }
 
 // Multi-GPU static partition without load imbalance: the frame's 8x4-tile rows are dealt to the ranks in bands
@@ -991,13 +991,5 @@ extern "C" int rd_trace_rays(rd_platform* p, unsigned raygenGroupIndex, unsigned
     if (rc) return rc;
     if (p->copyPending) { rc = rd_stream_bands_drain(p); if (rc) return rc; }   // start the band copies while waiting
     RD_CUDA(cudaStreamSynchronize(p->stream));   // blocking like clFinish (radiance.cpp:261)
-    uint32_t status[2] = {0, 0};
-    RD_CUDA(cudaMemcpy(status, p->dstatus, 8, cudaMemcpyDeviceToHost));
-    if (status[0] || status[1]) {
-        cudaMemset(p->dstatus, 0, 8);
-        if (status[0]) { rd_set_error("rd_trace_rays: traversal stack overflow on the device (results incomplete)"); return RD_E_OVERFLOW; }
-        rd_set_error("rd_trace_rays: traceRay nested deeper than option max_trace_depth (%ld)", p->optMaxDepth);
-        return RD_E_STATE;
-    }
-    return RD_OK;
+    return rd_check_status(p, "rd_trace_rays");
 }

@@ -156,7 +156,7 @@ extern "C" int rd_trace_counters(rd_platform* p, uint64_t out[3])
     RD_CUDA(cudaMemcpyAsync(h, p->dcounters, sizeof(h), cudaMemcpyDeviceToHost, p->stream));
     RD_CUDA(cudaStreamSynchronize(p->stream));
     out[0] = h[0]; out[1] = h[1]; out[2] = h[2];
-    return RD_OK;
+    return rd_check_status(p, "rd_trace_counters");
 }
 
 // ---- primary rays ---------------------------------------------------------------------------

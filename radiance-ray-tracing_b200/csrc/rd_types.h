@@ -65,8 +65,8 @@ struct RD_ALIGN(16) RdScene {
     const rd_u32* leafInstances;  // instance indices in top-level leaf order
     const RdInstance* instances;  // caller order: instanceID == array index
     rd_u32 instanceCount, nodeCount, flags, pad;
-    rd_u32* status;               // [0] = traversal-stack overflow counter (must stay 0)
-    rd_u64 pad2;
+    rd_u32* status;               // host-mapped flags: [0] traversal-stack overflow, [1] traceRay nested too deep (must stay 0)
+    rd_u64* rayCounter;           // traceRay invocations (option count_rays), device memory
 };
 
 // Ray / hit records of the wavefront queues (structure of arrays, 16-byte vector loads):

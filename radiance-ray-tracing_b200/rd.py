@@ -28,7 +28,7 @@ ABI_SYMBOLS = [
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
-    "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host",
+    "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
 ]
 
 
@@ -76,6 +76,7 @@ def lib():
             "rd_trace_ray_list": [vp, vp, vp, vp, vp, vp, sz, u], "rd_trace_counters": [vp, C.POINTER(C.c_uint64)],
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
             "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
+            "rd_status": [vp, C.POINTER(C.c_uint32), C.c_int],
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
@@ -119,6 +120,12 @@ class Platform:
 
     def sync(self):
         _check(lib().rd_platform_sync(self.handle))
+
+    def status(self, clear=False):
+        """(stack overflow, traceRay nesting exceeded) device flags, without synchronising."""
+        out = (C.c_uint32 * 2)()
+        _check(lib().rd_status(self.handle, out, int(bool(clear))))
+        return int(out[0]), int(out[1])
 
     def launch_count(self):
         return int(lib().rd_launch_count(self.handle))

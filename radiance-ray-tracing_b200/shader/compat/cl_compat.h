@@ -384,7 +384,7 @@ RD_F rd_uint4 convert_uint4(const rd_float4& a) { return rd_uint4((uint)a.x, (ui
 extern "C" { __constant__ unsigned int rd_launch_info[8]; }
 // Wavefront stages (csrc/rd_wavefront.h) run a path on whatever thread its queue entry lands on; the
 // stage stores the path's work-item id here before calling user code and sets rd_launch_info[3].
-__shared__ unsigned int rd_wf_gid[256];
+__shared__ unsigned int rd_wf_gid[1024];   // one slot per thread of the largest block option "block" accepts
 RD_F size_t get_global_id(uint dim)
 {
     if (dim != 0) return 0;

@@ -107,7 +107,7 @@ RD_F void traceRay(
     const RdScene* scene = (const RdScene*)topLevel;
 #ifdef RD_COUNT_RAYS
     // metric pass only (option "count_rays"): every traceRay invocation is one ray of the Mrays/s figure
-    atomicAdd((unsigned long long*)(scene->status + 2), 1ull);
+    atomicAdd((unsigned long long*)scene->rayCounter, 1ull);
 #endif
     RdUserAnyHit cb;
     cb.scene = scene; cb.o = origin; cb.d = direction; cb.sbtRecordOffset = sbtRecordOffset;

@@ -29,3 +29,42 @@ def ref():
 @pytest.fixture(scope="session")
 def plt(pkg):
     return pkg.rd.Platform.GetPlatform(0)
+
+
+class _ParityLog:
+    """Achieved parity numbers (mismatch fractions, max relative t error, RMSE) per configuration; written to
+    gpurun_out/parity_r2.json at the end of the session and copied under profiles/ by hand."""
+
+    def __init__(self):
+        self.rows = {}
+
+    def record(self, config, **numbers):
+        row = self.rows.setdefault(config, {})
+        for k, v in numbers.items():
+            row[k] = float(v) if hasattr(v, "__float__") and not isinstance(v, (bool, int, str)) else v
+
+    def dump(self):
+        import json
+        if not self.rows:
+            return
+        out = os.path.join(ROOT, "gpurun_out")
+        try:
+            os.makedirs(out, exist_ok=True)
+            path = os.path.join(out, "parity_r2.json")
+            old = {}
+            if os.path.exists(path):
+                try:
+                    old = json.load(open(path))
+                except Exception:
+                    old = {}
+            old.update(self.rows)
+            json.dump(old, open(path, "w"), indent=1, sort_keys=True)
+        except OSError:
+            pass
+
+
+@pytest.fixture(scope="session")
+def parity_log():
+    log = _ParityLog()
+    yield log
+    log.dump()

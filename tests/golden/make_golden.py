@@ -81,4 +81,54 @@ ref.raygen("primary", [np.array(scenes.rtprop(0, 2, 1, 0)).reshape(1), scratch, 
                        np.array(b.scene).reshape(1), b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData,
                        b.materials, None, 0, tl.blob], w * h)
 np.savez_compressed(os.path.join(out, "primary_cornell_96x72.npz"), image=image.reshape(h, w, 4), scratch=scratch.reshape(h, w, 4))
+
+# 6. generateRay (samples/shader.cl:111-173): pinhole and thin lens, a tilted camera, work-items all over the frame
+cams = [scenes.camera(800, 600, (0.013, 1.037, 3.4), (0.0, 0.0, 0.0), 0.030, 0.036, 2.0, 0.0),
+        scenes.camera(800, 600, (0.0, 0.6, 0.9), (-0.6, 0.3, 0.1), 0.030, 0.036, 3.1, 1.4),
+        scenes.camera(1920, 1080, (1.0, 2.0, -3.0), (0.2, -2.4, 0.05), 0.050, 0.036, 5.0, 2.8)]
+gr_cam, gr_in, gr_o, gr_d = [], [], [], []
+for ci, c in enumerate(cams):
+    wpx, hpx = int(c["widthPixel"]), int(c["heightPixel"])
+    for k in range(256):
+        index = int(rng.integers(0, wpx * hpx))
+        frame, total = int(rng.integers(0, 64)), int(rng.integers(0, 64))
+        o3, d3 = ref.generate_ray(np.array(c).reshape(1), np.array([frame, total, index], np.uint32), index)
+        gr_cam.append(ci), gr_in.append((frame, total, index)), gr_o.append(o3), gr_d.append(d3)
+np.savez(os.path.join(out, "generate_ray.npz"), cameras=np.array(cams), camera_index=np.array(gr_cam, np.uint32),
+         input=np.array(gr_in, np.uint32), origin=np.array(gr_o), direction=np.array(gr_d))
+
+# 7. pbr.cl / math.cl library functions as samples/shader.cl calls them (oracle/ref_device.cpp ref_library_kat)
+def unit(n):
+    v = rng.normal(size=(n, 3))
+    return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+
+def same_side(nrm, n):
+    v = unit(n)
+    flip = (v * nrm).sum(axis=1) < 0.05
+    v[flip] = (v[flip] + 2.0 * nrm[flip] * np.abs((v[flip] * nrm[flip]).sum(axis=1, keepdims=True)) + 0.3 * nrm[flip]).astype(np.float32)
+    return (v / np.linalg.norm(v, axis=1, keepdims=True)).astype(np.float32)
+
+nk = 512
+N = unit(nk); V = same_side(N, nk); L = same_side(N, nk)
+alb = rng.uniform(0.05, 0.95, size=(nk, 3)).astype(np.float32)
+met = rng.choice([0.0, 0.25, 0.9, 1.0], size=(nk, 1)).astype(np.float32)
+rough = rng.uniform(0.02, 1.0, size=(nk, 1)).astype(np.float32)
+trans = rng.choice([0.0, 0.5, 0.9], size=(nk, 1)).astype(np.float32)
+ior = rng.uniform(1.05, 1.9, size=(nk, 1)).astype(np.float32)
+rnd = rng.uniform(0.0, 1.0, size=(nk, 3)).astype(np.float32)
+eta = rng.choice([1.0 / 1.45, 1.45, 1.0 / 1.1, 1.9], size=(nk, 1)).astype(np.float32)
+kat_inputs = {
+    "BRDF": np.hstack([L, V, N, met, rough, alb]),
+    "refract": np.hstack([V, N, eta]),
+    "G_pbrt": np.hstack([V, L, N, rough]),
+    "sampleMicrofacetBRDF_transm": np.hstack([V, N, alb, met, rough, trans, ior, rnd]),
+    "microfacetBRDF": np.hstack([L, V, N, alb, met, rough, trans, ior]),
+    "GetNormalSpace": np.vstack([N, [[1, 0, 0], [-1, 0, 0], [0, 1, 0], [0, 0, 1]]]).astype(np.float32),
+    "sampleMicrofacetBRDF": np.hstack([V, N, alb, met, rough, rnd]),
+}
+kat = {}
+for name, a in kat_inputs.items():
+    kat[name + "_in"] = np.ascontiguousarray(a, np.float32)
+    kat[name + "_out"] = ref.library_kat(name, a)
+np.savez_compressed(os.path.join(out, "library_kat.npz"), **kat)
 print("golden vectors written to", out)

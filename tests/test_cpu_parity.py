@@ -176,3 +176,51 @@ def test_compile_errors_and_bad_sbt_are_reported(pkg):
         rd.CompileCheck('#include "radiance.cl"\n__kernel void raygen() {}\n', '[{"raygen": 3}]')
     with pytest.raises(rd.RadianceError, match="no sbt.json"):
         rd.CompileCheck('#include "radiance.cl"\n__kernel void raygen() {}\n', None)
+
+
+def test_library_kat_golden_is_the_reference(pkg):
+    """tests/golden/library_kat.npz and generate_ray.npz reproduce from the reference's own functions (oracle/_ref)."""
+    import __graft_entry__ as entry
+    ref = entry.load_oracle()
+    if not ref.available():
+        pytest.skip("oracle/_ref not built")
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "library_kat.npz"))
+    for name in ref.LIBRARY_KAT:
+        out = ref.library_kat(name, g[name + "_in"])
+        assert np.array_equal(out.view(np.uint32), g[name + "_out"].view(np.uint32)), name
+    gr = np.load(os.path.join(os.path.dirname(__file__), "golden", "generate_ray.npz"))
+    for k in range(0, len(gr["input"]), 17):
+        cam = gr["cameras"][gr["camera_index"][k]]
+        o, d = ref.generate_ray(np.array(cam).reshape(1), gr["input"][k], int(gr["input"][k][2]))
+        assert np.array_equal(o, gr["origin"][k]) and np.array_equal(d, gr["direction"][k])
+
+
+def test_restated_library_matches_reference_golden_on_host():
+    """shader/math.cl, shader/pbr.cl and the traversal's triangle test, compiled for the host (tests/kat), on the
+    golden vectors of the reference: integer / triangle results bit-exact, transcendental chains within 1e-6."""
+    so = os.path.join(os.path.dirname(__file__), "kat", "libkat_host.so")
+    if not os.path.exists(so):
+        pytest.skip("tests/kat/libkat_host.so not built")
+    L = C.CDLL(so)
+
+    def kat(fn, a, stride):
+        a = np.ascontiguousarray(a)
+        hdr = np.array([fn, a.shape[0], a.shape[1], stride], np.uint32)
+        out = np.zeros((a.shape[0], stride), np.float32)
+        L.kat_run(C.c_void_p(hdr.ctypes.data), C.c_void_p(a.ctypes.data), C.c_void_p(out.ctypes.data))
+        return out
+    gold = os.path.join(os.path.dirname(__file__), "golden")
+    p = np.load(os.path.join(gold, "pcg3d.npz"))
+    assert np.array_equal(kat(0, p["input"].astype(np.uint32).view(np.float32), 3).view(np.uint32), p["output"].view(np.uint32))
+    t = np.load(os.path.join(gold, "triangle.npz"))
+    o = kat(2, np.hstack([t["origin"], t["direction"], t["triangle"]]).astype(np.float32), 5)
+    hit = t["hit"].astype(bool)
+    assert np.array_equal(o[:, 0] == 1, hit)
+    assert np.array_equal(o[hit][:, 1].view(np.uint32), t["result"][hit][:, 0].view(np.uint32))
+    assert np.array_equal(o[hit][:, 2:5].view(np.uint32), t["result"][hit][:, 4:7].view(np.uint32))
+    g = np.load(os.path.join(gold, "library_kat.npz"))
+    for name, fn in {"BRDF": 10, "refract": 11, "G_pbrt": 12, "sampleMicrofacetBRDF_transm": 13, "microfacetBRDF": 14,
+                     "GetNormalSpace": 15, "sampleMicrofacetBRDF": 16}.items():
+        exp = g[name + "_out"]
+        out = kat(fn, g[name + "_in"], exp.shape[1])
+        assert (np.abs(out - exp) / (1.0 + np.abs(exp))).max() <= 1e-6, name
