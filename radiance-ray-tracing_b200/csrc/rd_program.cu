@@ -763,6 +763,17 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     return RD_OK;
 }
 
+// Threads per block for kernel f: option "block", lowered to what the kernel's register count allows (a 128-register
+// path-tracing raygen cannot run 1024 threads per block; the work-item -> thread mapping does not depend on the block size).
+static unsigned rd_block_for(rd_platform* p, CUfunction f)
+{
+    unsigned block = (unsigned)p->optBlock;
+    int maxThreads = 0;
+    if (cuFuncGetAttribute(&maxThreads, CU_FUNC_ATTRIBUTE_MAX_THREADS_PER_BLOCK, f) == CUDA_SUCCESS && maxThreads >= 32 &&
+        block > (unsigned)maxThreads) block = (unsigned)maxThreads & ~31u;
+    return block;
+}
+
 // Launches work-items [first, first + count) of the width*height NDRange (count == 0: all of them).
 // With the 8x4 tile mapping on, consecutive work-items of a warp cover one 8x4 pixel tile, so a
 // contiguous range is a contiguous run of screen tiles (the unit of the multi-GPU partition).
@@ -789,7 +800,7 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
     RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
     std::vector<void*> argv(p->boundArgs.size());
     for (size_t i = 0; i < argv.size(); ++i) argv[i] = &p->boundArgs[i];
-    const unsigned block = (unsigned)p->optBlock;
+    const unsigned block = rd_block_for(p, m->raygen);
     const unsigned tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     const unsigned full = (unsigned)(count / block), tail = (unsigned)(count % block);
     // a frame that is going to be read back into a registered host mirror: bands of tile rows, copied out as they finish
@@ -918,7 +929,7 @@ extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned heig
     std::vector<void*> argv(p->boundArgs.size() + 1);
     for (size_t i = 0; i < p->boundArgs.size(); ++i) argv[i] = &p->boundArgs[i];
     argv[p->boundArgs.size()] = &a;
-    const unsigned block = (unsigned)p->optBlock;
+    const unsigned block = rd_block_for(p, m->stealRaygen);
     const unsigned warpsPerBlock = block / 32u;
     unsigned blocks = (unsigned)p->smCount * 8u;
     if (blocks > (numChunks + warpsPerBlock - 1) / warpsPerBlock) blocks = (numChunks + warpsPerBlock - 1) / warpsPerBlock;

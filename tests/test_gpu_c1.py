@@ -108,7 +108,7 @@ def test_c1_shader_cl_as_shipped_matches_reference(pkg, plt, ref, c1_sources, pa
         exp, exp_scratch = reference_frame(ref, scenes, b, rt)
         compare(img, scratch, exp, exp_scratch, bar, parity_log, "C1_shader_cl_%dspp" % batch)
         # the scene really exercises every branch: lit and shadowed surfaces, the sky, refraction
-        assert len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 5000
+        assert len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 2000
 
 
 def test_c1_generated_dispatchers_equal_handwritten(pkg, plt, ref, c1_sources):
@@ -127,13 +127,13 @@ def test_c1_thin_lens_matches_reference(pkg, plt, ref, c1_sources, parity_log):
     lens point, focal plane)."""
     scenes = pkg.scenes
     src, sbt = c1_sources
-    b = c1_bundle(scenes, fstop=1.4)
+    b = c1_bundle(scenes, fstop=0.05)   # lens radius 0.3: a strong blur away from the focal plane
     rt = scenes.rtprop(0, 4, 8, 0)
     img, scratch, _ = gpu_frame(pkg, plt, b, rt, src, sbt)
     exp, exp_scratch = reference_frame(ref, scenes, b, rt)
     compare(img, scratch, exp, exp_scratch, C1_RMSE_U8, parity_log, "C1_shader_cl_thin_lens_4spp")
     sharp, _ = reference_frame(ref, scenes, c1_bundle(scenes), rt)
-    assert np.abs(exp[..., :3].astype(int) - sharp[..., :3].astype(int)).mean() > 0.5   # the lens really blurs
+    assert np.abs(exp[..., :3].astype(int) - sharp[..., :3].astype(int)).mean() > 2.0   # the lens really blurs
 
 
 def test_c1_debug_view_and_progressive_accumulation(pkg, plt, ref, c1_sources, parity_log):
