@@ -285,7 +285,10 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     memset(out, 0, sizeof(*out));
     if (n == 0) {
         // empty structure: one node without children
-        RdNode8 e; memset(&e, 0, sizeof(e)); e.w[0].w = 1u | (1u << 8) | (1u << 16);
+        RdNode8 e; memset(&e, 0, sizeof(e));
+#if !RD_NODE_F32
+        e.w[0].w = 1u | (1u << 8) | (1u << 16);
+#endif
         RD_CUDA(cudaMalloc(&out->nodes, sizeof(RdNode8)));
         RD_CUDA(cudaMemcpyAsync(out->nodes, &e, sizeof(e), cudaMemcpyHostToDevice, st));
         RD_CUDA(cudaMalloc(&out->leafPrim, 16));
@@ -486,6 +489,9 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
         memcpy(I.inv, inv, 48);
         I.sbtOffset = instances[i].SBTOffset; I.instanceID = i; I.customID = instances[i].customInstanceID; I.flags = b->triCount;   // flags = triangle records of the BLAS (rd_tlas_save)
         I.nodes = b->nodes; I.tris = b->tris;
+        I.maxAbs = 0.0f; I.pad[0] = I.pad[1] = I.pad[2] = 0u;
+        for (int k = 0; k < 3; ++k) I.maxAbs = fmaxf(I.maxAbs, fmaxf(fabsf(b->lo[k]), fabsf(b->hi[k])));
+        if (!(I.maxAbs < 3.0e38f)) I.maxAbs = 0.0f;   // empty structure: inverted root box
         RdF4 bl, bh; bl.x = b->lo[0]; bl.y = b->lo[1]; bl.z = b->lo[2]; bl.w = 0; bh.x = b->hi[0]; bh.y = b->hi[1]; bh.z = b->hi[2]; bh.w = 0;
         rd_instance_world_box(I.fwd, bl, bh, &lo[i], &hi[i]);
     }
@@ -508,6 +514,9 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
     RdScene S; memset(&S, 0, sizeof(S));
     S.nodes = r.nodes; S.leafInstances = r.leafPrim; S.instances = (const RdInstance*)o->dinst;
     S.instanceCount = n; S.nodeCount = r.nodeCount; S.status = p->dstatus; S.rayCounter = (rd_u64*)p->dRayCounter;
+    S.maxAbs = 0.0f;
+    for (int k = 0; k < 3; ++k) S.maxAbs = fmaxf(S.maxAbs, fmaxf(fabsf(r.lo[k]), fabsf(r.hi[k])));
+    if (!(S.maxAbs < 3.0e38f) || !n) S.maxAbs = 0.0f;
     RD_CUDA(cudaMalloc(&o->dptr, sizeof(RdScene)));
     RD_CUDA(cudaMemcpyAsync(o->dptr, &S, sizeof(S), cudaMemcpyHostToDevice, st));
     RD_CUDA(cudaStreamSynchronize(st));

@@ -315,6 +315,60 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
         }
         slotOf[bk] = bs; childAt[bs] = ch[bk];
     }
+#if RD_NODE_F32
+    rd_u32 imask = 0, nInner = 0, nLeafPrims = 0;
+    for (int s = 0; s < 8; ++s) {
+        if (childAt[s] == RD_INVALID) continue;
+        const rd_u32 c = childAt[s];
+        if (!(c & RD_BIN_LEAF) && rd_bin_count(T, c) > RD_LEAF_MAX) { imask |= 1u << s; nInner++; }
+        else nLeafPrims += rd_bin_count(T, c);
+    }
+    const rd_u32 childBase = nInner ? RD_ATOMIC_ADD_U32(&O.counters[0], nInner) : 0u;
+    const rd_u32 primBase = nLeafPrims ? RD_ATOMIC_ADD_U32(&O.counters[1], nLeafPrims) : 0u;
+    const rd_u32 nextBase = nInner ? RD_ATOMIC_ADD_U32(&O.counters[2], nInner) : 0u;
+    RdNode8 node;
+    for (int k = 0; k < 16; ++k) { node.w[k].x = 0u; node.w[k].y = 0u; node.w[k].z = 0u; node.w[k].w = 0u; }
+    float* planes = (float*)&node;    // float index = byte offset / 4
+    rd_u32 leafNib = 0, innerNib = 0, leafOff = 0, innerRank = 0;
+    for (int s = 0; s < 8; ++s) {
+        float bl[3] = {3.0e38f, 3.0e38f, 3.0e38f}, bh[3] = {-3.0e38f, -3.0e38f, -3.0e38f};   // empty slot: inverted box
+        if (childAt[s] != RD_INVALID) {
+            const rd_u32 c = childAt[s];
+            const rd_u32 slotBox = rd_bin_slot(T, c);
+            const RdF4 l = T.lo[slotBox], h = T.hi[slotBox];
+            // The boxes are the exact bounds of the triangles; the triangle test has rounding of its own (a ray can hit a
+            // triangle numerically a few ulps outside its exact extent), so every child box grows by 4 ulps of its
+            // coordinates. A parent's extreme coordinate is >= its children's, so padded children stay inside padded parents.
+            const float pad = 4.76837158e-7f;
+            bl[0] = l.x - pad * fabsf(l.x); bl[1] = l.y - pad * fabsf(l.y); bl[2] = l.z - pad * fabsf(l.z);
+            bh[0] = h.x + pad * fabsf(h.x); bh[1] = h.y + pad * fabsf(h.y); bh[2] = h.z + pad * fabsf(h.z);
+            if (imask & (1u << s)) {
+                innerNib |= 1u << (4 * s);
+                RdCollapseItem nx; nx.wide = childBase + innerRank; nx.bin = c;
+                O.next[nextBase + innerRank] = nx;
+                innerRank++;
+            } else {
+                const rd_u32 cnt = rd_bin_count(T, c);
+                leafNib |= ((1u << cnt) - 1u) << (4 * s);
+                // the <= RD_LEAF_MAX primitives of the subtree, left to right
+                rd_u32 walk[RD_LEAF_MAX + 1]; int wp = 0; rd_u32 j = 0;
+                walk[wp++] = c;
+                while (wp > 0) {
+                    const rd_u32 r = walk[--wp];
+                    if (r & RD_BIN_LEAF) { O.leafPrim[primBase + leafOff + j] = T.prim[r & ~RD_BIN_LEAF]; ++j; }
+                    else { walk[wp++] = T.right[r]; walk[wp++] = T.left[r]; }
+                }
+                leafOff += cnt;
+            }
+        }
+        planes[RD_NODE_OFF_LOX / 4 + s] = bl[0]; planes[RD_NODE_OFF_LOY / 4 + s] = bl[1]; planes[RD_NODE_OFF_LOZ / 4 + s] = bl[2];
+        planes[RD_NODE_OFF_HIX / 4 + s] = bh[0]; planes[RD_NODE_OFF_HIY / 4 + s] = bh[1]; planes[RD_NODE_OFF_HIZ / 4 + s] = bh[2];
+    }
+    node.w[0].x = childBase; node.w[0].y = primBase; node.w[0].z = leafNib; node.w[0].w = imask;
+    node.w[1].x = innerNib;
+    node.w[8].x = RD_F2U(nlo.x); node.w[8].y = RD_F2U(nlo.y); node.w[8].z = RD_F2U(nlo.z);
+    node.w[9].x = RD_F2U(nhi.x); node.w[9].y = RD_F2U(nhi.y); node.w[9].z = RD_F2U(nhi.z);
+#else
     // quantisation grid
     const rd_u32 ex = rd_grid_exponent(nhi.x - nlo.x), ey = rd_grid_exponent(nhi.y - nlo.y),
                  ez = rd_grid_exponent(nhi.z - nlo.z);
@@ -374,6 +428,7 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
     node.w[3].x = RD_PACK4(q[2], 0); node.w[3].y = RD_PACK4(q[2], 4); node.w[3].z = RD_PACK4(q[3], 0); node.w[3].w = RD_PACK4(q[3], 4);
     node.w[4].x = RD_PACK4(q[4], 0); node.w[4].y = RD_PACK4(q[4], 4); node.w[4].z = RD_PACK4(q[5], 0); node.w[4].w = RD_PACK4(q[5], 4);
 #undef RD_PACK4
+#endif
     O.nodes[item.wide] = node;
 }
 

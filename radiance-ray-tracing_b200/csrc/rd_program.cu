@@ -563,6 +563,7 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
                                      "-lineinfo", "-w", "--ptxas-options=-v"};
     opts.push_back(fmad ? "--fmad=true" : "--fmad=false");
     if (countRays) opts.push_back("-DRD_COUNT_RAYS=1");
+    opts.push_back(RD_NODE_F32 ? "-DRD_NODE_F32=1" : "-DRD_NODE_F32=0");   // user programs walk the node form this library builds
     // developer knob for ablations: extra NVRTC flags (e.g. "-DRD_FLUSH_DIV=2 -DRD_DEQUANT_I2F=0")
     std::vector<std::string> extra;
     if (const char* env = getenv("RD_NVRTC_FLAGS")) {

@@ -172,15 +172,23 @@ __global__ void rd_k_wf_ray_keys(const RdScene* __restrict__ scene, const RdWfSt
     const unsigned n = wf.counts[wf.cur];
     const unsigned j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
+    const float4 a = __ldg(&((const float4*)wf.rayA[wf.cur])[j]), b = __ldg(&((const float4*)wf.rayB[wf.cur])[j]);
+#if RD_NODE_F32
+    // scene box = the root node's own box (w[8], w[9]); cell coordinate in [0,8) per axis
+    const float4 blo = __ldg((const float4*)&scene->nodes[0].w[8]), bhi = __ldg((const float4*)&scene->nodes[0].w[9]);
+    const float wx = fmaxf(bhi.x - blo.x, 1e-30f), wy = fmaxf(bhi.y - blo.y, 1e-30f), wz = fmaxf(bhi.z - blo.z, 1e-30f);
+    const float fx = (a.x - blo.x) / wx * 8.0f, fy = (a.y - blo.y) / wy * 8.0f, fz = (a.z - blo.z) / wz * 8.0f;
+    const float ex = wx, ey = wy, ez = wz;   // extents decide which axis keeps one bit
+#else
     // scene box from the root node of the top-level structure: origin p, 256 grid steps of 2^(e-127) per axis
     const uint4 n0 = __ldg((const uint4*)&scene->nodes[0].w[0]);
     const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
     const unsigned ex = n0.w & 0xffu, ey = (n0.w >> 8) & 0xffu, ez = (n0.w >> 16) & 0xffu;
-    const float4 a = __ldg(&((const float4*)wf.rayA[wf.cur])[j]), b = __ldg(&((const float4*)wf.rayB[wf.cur])[j]);
     // cell coordinate in [0,8) per axis
     const float fx = (a.x - px) * __uint_as_float((254u - ex) << 23) * (1.0f / 32.0f);
     const float fy = (a.y - py) * __uint_as_float((254u - ey) << 23) * (1.0f / 32.0f);
     const float fz = (a.z - pz) * __uint_as_float((254u - ez) << 23) * (1.0f / 32.0f);
+#endif
     unsigned cx = (unsigned)fminf(fmaxf(fx, 0.0f), 7.0f), cy = (unsigned)fminf(fmaxf(fy, 0.0f), 7.0f), cz = (unsigned)fminf(fmaxf(fz, 0.0f), 7.0f);
     // the axis with the smallest extent keeps one bit
     unsigned c0, c1, c2;   // c0, c1: 3 bits each; c2: 1 bit

@@ -25,7 +25,10 @@ static void emu_build(const std::vector<RdF4>& plo, const std::vector<RdF4>& phi
     const rd_u32 n = (rd_u32)plo.size();
     out.nodes.clear(); out.leafPrim.clear(); out.levels = 0;
     if (n == 0) {
-        RdNode8 e; memset(&e, 0, sizeof(e)); e.w[0].w = 1u | (1u << 8) | (1u << 16);
+        RdNode8 e; memset(&e, 0, sizeof(e));
+#if !RD_NODE_F32
+        e.w[0].w = 1u | (1u << 8) | (1u << 16);
+#endif
         out.nodes.push_back(e);
         rootLo->x = rootLo->y = rootLo->z = 0; rootHi->x = rootHi->y = rootHi->z = 0;
         return;
@@ -108,6 +111,8 @@ void* emu_tlas_build(const EmuInstanceIn* in, unsigned n)
         if (!rd_inverse4x4(I.fwd, inv)) memset(inv, 0, sizeof(inv));
         memcpy(I.inv, inv, 48);
         I.sbtOffset = in[i].sbt; I.instanceID = i; I.customID = in[i].custom; I.flags = 0;
+        I.maxAbs = fmaxf(fmaxf(fmaxf(fabsf(b->lo.x), fabsf(b->hi.x)), fmaxf(fabsf(b->lo.y), fabsf(b->hi.y))), fmaxf(fabsf(b->lo.z), fabsf(b->hi.z)));
+        if (!(I.maxAbs < 3.0e38f)) I.maxAbs = 0.0f;
         I.nodes = b->nodes.data(); I.tris = b->tris.data();
         rd_instance_world_box(I.fwd, b->lo, b->hi, &plo[i], &phi[i]);
     }
@@ -117,6 +122,8 @@ void* emu_tlas_build(const EmuInstanceIn* in, unsigned n)
     memset(&t->scene, 0, sizeof(RdScene)); memset(t->status, 0, sizeof(t->status));
     t->scene.nodes = t->nodes.data(); t->scene.leafInstances = t->leafInst.data(); t->scene.instances = t->inst.data();
     t->scene.instanceCount = n; t->scene.nodeCount = (rd_u32)t->nodes.size(); t->scene.status = t->status;
+    t->scene.maxAbs = fmaxf(fmaxf(fmaxf(fabsf(rl.x), fabsf(rh.x)), fmaxf(fabsf(rl.y), fabsf(rh.y))), fmaxf(fabsf(rl.z), fabsf(rh.z)));
+    if (!(t->scene.maxAbs < 3.0e38f) || !n) t->scene.maxAbs = 0.0f;
     return t;
 }
 void emu_tlas_free(void* h) { delete (EmuTlas*)h; }

@@ -64,5 +64,6 @@ for v in VARIANTS:
         base = img
     diff = int((img != base).any(axis=-1).sum())
     t = float(np.median(ms[3:]))
-    print("%-50s %s  %.4f ms  %.0f Mrays/s  min %.4f  regs %s  px_diff %d" % (
-        json.dumps(v), "", t, W * H / t / 1e3, min(ms[3:]), module.info(), diff), flush=True)
+    import zlib
+    print("%-50s %s  %.4f ms  %.0f Mrays/s  min %.4f  regs %s  px_diff %d  crc %08x" % (
+        json.dumps(v), "", t, W * H / t / 1e3, min(ms[3:]), module.info(), diff, zlib.crc32(img.tobytes())), flush=True)
