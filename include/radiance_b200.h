@@ -164,6 +164,37 @@ int rd_steal_counter_import(rd_platform* p, const unsigned char handle[64]);
 int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned height, unsigned frame, unsigned chunkItems);
 int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, unsigned* count);
 
+/* The multi-GPU frame collective (csrc/rd_comm.cu). The reference renders one blocking frame on one device and reads it
+ * back (radiance/src/radiance.cpp:242-267, :186-199; one cl_context on one device, clcontext.cpp:12-40); here the frame is
+ * partitioned over the GPUs of one box (one process or host thread per GPU, scene replicated) and the finished framebuffer
+ * is gathered on rank 0 over NVLink with NCCL -- the only exchange of a frame. A host in the reference's idiom
+ * (samples/sample1.cpp:466-490) calls, per frame and on every rank:
+ *     rd_trace_rays_interleaved(p, w, h, rank, world, bandTileRows);   rd_frame_gather(p, image, w, h, 4, bandTileRows);
+ * and rank 0 then reads the frame with rd_buffer_read. NCCL is loaded on first use (libnccl.so.2).
+ *   rd_comm_unique_id   rank 0 creates the 128-byte NCCL id and hands it to the other ranks (any transport)
+ *   rd_comm_init        every rank: joins the communicator (collective call); rd_comm_adopt uses an ncclComm_t the host owns
+ *   rd_frame_gather     static interleaved partition: each peer packs its bands, ONE send per peer, rank 0 unpacks
+ *   rd_frame_gather_ranges  contiguous work-item ranges per rank (rd_trace_rays_range), sent in place
+ *   rd_trace_rays_units + rd_frame_gather_units   DYNAMIC partition: the frame is cut into `units` (<= 64) equal runs of
+ *                       8x4-tile rows, every rank takes the next unit from the job-wide counter of rd_steal_counter_export /
+ *                       _import (system-scope atomic over NVLink) and renders it in whatever mode is on -- wavefront
+ *                       included; `frame` = 0, 1, 2, ... selects the counter slot as in rd_trace_rays_steal; ownedMask
+ *                       returns the units this rank rendered and is what rd_frame_gather_units exchanges. */
+int rd_comm_unique_id(unsigned char id[128]);
+int rd_comm_init(rd_platform* p, int rank, int world, const unsigned char id[128]);
+int rd_comm_adopt(rd_platform* p, void* ncclComm, int rank, int world);
+int rd_comm_destroy(rd_platform* p);
+int rd_frame_gather(rd_platform* p, rd_handle image, unsigned width, unsigned height, unsigned itemBytes, unsigned bandTileRows);
+int rd_frame_gather_ranges(rd_platform* p, rd_handle image, unsigned itemBytes, const unsigned long long* first,
+                           const unsigned long long* count);
+int rd_trace_rays_units(rd_platform* p, unsigned width, unsigned height, unsigned units, unsigned frame,
+                        unsigned long long* ownedMask);
+int rd_frame_gather_units(rd_platform* p, rd_handle image, unsigned width, unsigned height, unsigned itemBytes,
+                          unsigned units, unsigned long long ownedMask);
+/* Stage timeline of the last wavefront-mode call (option "wf_timeline" = 1): ms[i] = device time of stage i, codes[i] =
+ * 1 generate, 2 trace, 3 sort, 4 shade, 5 accumulate, 6 resolve, 7 ray re-sort. Synchronises the platform stream. */
+int rd_wf_timeline(rd_platform* p, float* ms, int* codes, unsigned capacity, unsigned* count);
+
 /* Explicit ray list through the traversal kernel (wavefront building block; used for hit-ID parity
  * against the reference's traceRay, radiance/shader/radiance.cl:254-275).
  *   rayA[i] = {o.xyz, tmin}, rayB[i] = {d.xyz, tmax}; hitA[i] = {t, b1, b2, primID bits}, hitB[i] = instanceID.

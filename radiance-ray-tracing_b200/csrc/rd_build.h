@@ -383,10 +383,9 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
     const rd_u32 childBase = nInner ? RD_ATOMIC_ADD_U32(&O.counters[0], nInner) : 0u;
     const rd_u32 primBase = nLeafPrims ? RD_ATOMIC_ADD_U32(&O.counters[1], nLeafPrims) : 0u;
     const rd_u32 nextBase = nInner ? RD_ATOMIC_ADD_U32(&O.counters[2], nInner) : 0u;
-    rd_u8 meta[8], q[6][8];
-    rd_u32 leafOff = 0, innerRank = 0;
+    rd_u8 q[6][8];
+    rd_u32 leafOff = 0, innerRank = 0, leafNib = 0, innerNib = 0;
     for (int s = 0; s < 8; ++s) {
-        meta[s] = 0;
         for (int a = 0; a < 6; ++a) q[a][s] = 0;
         if (childAt[s] == RD_INVALID) { q[0][s] = q[1][s] = q[2][s] = 255; continue; }   // inverted box
         const rd_u32 c = childAt[s];
@@ -400,13 +399,13 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
         v = ceilf((h.y - nlo.y) * isy); q[4][s] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
         v = ceilf((h.z - nlo.z) * isz); q[5][s] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
         if (imask & (1u << s)) {
-            meta[s] = (rd_u8)(0x20u | (24u + (rd_u32)s));
+            innerNib |= 1u << (4 * s);
             RdCollapseItem nx; nx.wide = childBase + innerRank; nx.bin = c;
             O.next[nextBase + innerRank] = nx;
             innerRank++;
         } else {
             const rd_u32 cnt = rd_bin_count(T, c);
-            meta[s] = (rd_u8)((((1u << cnt) - 1u) << 5) | leafOff);
+            leafNib |= ((1u << cnt) - 1u) << (4 * s);
             // the <= RD_LEAF_MAX primitives of the subtree, left to right
             rd_u32 walk[RD_LEAF_MAX + 1]; int wp = 0; rd_u32 j = 0;
             walk[wp++] = c;
@@ -423,7 +422,7 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
     node.w[0].w = ex | (ey << 8) | (ez << 16) | (imask << 24);
     node.w[1].x = childBase; node.w[1].y = primBase;
 #define RD_PACK4(a, o) ((rd_u32)(a)[o] | ((rd_u32)(a)[o + 1] << 8) | ((rd_u32)(a)[o + 2] << 16) | ((rd_u32)(a)[o + 3] << 24))
-    node.w[1].z = RD_PACK4(meta, 0); node.w[1].w = RD_PACK4(meta, 4);
+    node.w[1].z = leafNib; node.w[1].w = innerNib;
     node.w[2].x = RD_PACK4(q[0], 0); node.w[2].y = RD_PACK4(q[0], 4); node.w[2].z = RD_PACK4(q[1], 0); node.w[2].w = RD_PACK4(q[1], 4);
     node.w[3].x = RD_PACK4(q[2], 0); node.w[3].y = RD_PACK4(q[2], 4); node.w[3].z = RD_PACK4(q[3], 0); node.w[3].w = RD_PACK4(q[3], 4);
     node.w[4].x = RD_PACK4(q[4], 0); node.w[4].y = RD_PACK4(q[4], 4); node.w[4].z = RD_PACK4(q[5], 0); node.w[4].w = RD_PACK4(q[5], 4);

@@ -45,6 +45,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->bandFlags = 0; p->bandFlagsDev = 0; p->bandCount = p->bandRows = p->bandTileRows = 0; p->bandCopied = 0; p->bandRowBytes = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
+    p->comm = 0; p->unitSlots = 0; p->unitSlotsDev = 0; p->unitEvent = 0; p->optWfTimeline = 0; p->tlUsed = 0;
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     {   // build scratch is stream-ordered (RdTmp in rd_build.cu): keep freed blocks in the pool instead of returning them to the OS
@@ -74,6 +75,9 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     if (!p) return RD_OK;
     cudaSetDevice(p->device);
     cudaStreamSynchronize(p->stream);
+    rd_comm_destroy(p);
+    for (cudaEvent_t e : p->tlEvents) cudaEventDestroy(e);
+    if (p->unitSlots) { cudaFreeHost((void*)p->unitSlots); cudaEventDestroy(p->unitEvent); }
     rd_wf_release(p);
     { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
     cudaFreeHost((void*)p->hstatus);
@@ -392,6 +396,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     else if (!strcmp(key, "wf_sort")) p->optWfSort = value;
     else if (!strcmp(key, "wf_dynamic")) p->optWfDynamic = value;
     else if (!strcmp(key, "wf_ray_sort")) p->optWfRaySort = value;
+    else if (!strcmp(key, "wf_timeline")) p->optWfTimeline = value;
     else if (!strcmp(key, "trim_pool")) {   // give the build scratch and the wavefront queues back to the driver (value ignored)
         cudaSetDevice(p->device);
         cudaStreamSynchronize(p->stream);

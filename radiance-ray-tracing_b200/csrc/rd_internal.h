@@ -78,6 +78,9 @@ struct rd_platform {
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
+    void* comm;                                  // RdComm* (rd_comm.cu): the NCCL communicator of the multi-GPU frame gather
+    volatile unsigned* unitSlots; unsigned* unitSlotsDev; cudaEvent_t unitEvent;   // rd_trace_rays_units: unit numbers land in host-mapped memory
+    long optWfTimeline; std::vector<cudaEvent_t> tlEvents; std::vector<int> tlCodes; size_t tlUsed;   // rd_wf_timeline
     uint64_t launches;
     int smCount;
 };

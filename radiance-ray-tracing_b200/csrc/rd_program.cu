@@ -692,8 +692,39 @@ extern "C" int rd_descriptors_bind(rd_platform* p, const rd_handle* handles, uns
 // ---- wavefront sequencer ------------------------------------------------------------------------
 // RD::TraceRays in wavefront mode: the sample loop and the bounce loop of samples/shader.cl:196-281 as
 // stage launches (rd_wavefront.h). The only host read is RTProp (16 bytes) before the first stage.
+// Stage timeline (option "wf_timeline"): one event in front of every stage launch of the last wavefront call; read with
+// rd_wf_timeline after the frame. Codes: 1 generate, 2 trace, 3 sort, 4 shade, 5 accumulate, 6 resolve, 7 ray re-sort.
+static int rd_tl_mark(rd_platform* p, int code)
+{
+    if (!p->optWfTimeline) return RD_OK;
+    if (p->tlUsed == p->tlEvents.size()) {
+        cudaEvent_t e; RD_CUDA(cudaEventCreate(&e));
+        p->tlEvents.push_back(e); p->tlCodes.push_back(0);
+    }
+    p->tlCodes[p->tlUsed] = code;
+    RD_CUDA(cudaEventRecord(p->tlEvents[p->tlUsed], p->stream));
+    p->tlUsed += 1;
+    return RD_OK;
+}
+
+extern "C" int rd_wf_timeline(rd_platform* p, float* ms, int* codes, unsigned capacity, unsigned* count)
+{
+    if (!p || !count) { rd_set_error("rd_wf_timeline: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    const unsigned n = p->tlUsed > 0 ? (unsigned)p->tlUsed - 1u : 0u;   // the last mark closes the last stage
+    *count = n;
+    for (unsigned i = 0; i < n && i < capacity; ++i) {
+        float t = 0.0f;
+        RD_CUDA(cudaEventElapsedTime(&t, p->tlEvents[i], p->tlEvents[i + 1]));
+        if (ms) ms[i] = t;
+        if (codes) codes[i] = p->tlCodes[i];
+    }
+    return RD_OK;
+}
+
 static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned height, unsigned long long first,
-                                   unsigned long long count)
+                                   unsigned long long count, const unsigned* rtKnown = 0, bool resetTimeline = true)
 {
     rd_module* m = p->boundModule;
     if (!m->wfGenerate) {
@@ -703,8 +734,12 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     if (p->boundArgs.size() < 3) { rd_set_error("rd_trace_rays: wavefront mode needs RTProp, imageScratch, image as descriptors 0..2"); return RD_E_STATE; }
     const unsigned total = width * height;
     unsigned rt[4] = {0, 0, 0, 0};   // RayTraceProperties: totalSamples, batchSize, depth, debug (core.h:103-109)
-    RD_CUDA(cudaMemcpyAsync(rt, (const void*)p->boundArgs[0], 16, cudaMemcpyDeviceToHost, p->stream));
-    RD_CUDA(cudaStreamSynchronize(p->stream));
+    if (rtKnown) memcpy(rt, rtKnown, 16);   // the caller read it already (one read per frame when the frame is rendered in units)
+    else {
+        RD_CUDA(cudaMemcpyAsync(rt, (const void*)p->boundArgs[0], 16, cudaMemcpyDeviceToHost, p->stream));
+        RD_CUDA(cudaStreamSynchronize(p->stream));
+    }
+    if (resetTimeline) p->tlUsed = 0;
     const unsigned stride = (m->wfPayloadSize + 15u) & ~15u;
     // samples in flight per pass: as many as option wf_paths allows (HBM: ~200 B per path)
     unsigned long long inFlight = (unsigned long long)p->optWfPaths / count;
@@ -744,23 +779,29 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
         const unsigned samples = rt[1] - k < (unsigned)inFlight ? rt[1] - k : (unsigned)inFlight;
         const unsigned live = samples * (unsigned)count, pathBlocks = (live + 127u) / 128u;
         rc = rd_wf_advance(p, 0u, rt[0] + k, samples); if (rc) return rc;
+        rd_tl_mark(p, 1);
         RD_CU(cuLaunchKernel(m->wfGenerate, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
         for (unsigned d = 0; d < rt[2]; ++d) {
-            if (d > 0 && p->optWfRaySort) { rc = rd_wf_reorder_rays(p, scene, live); if (rc) return rc; }
+            if (d > 0 && p->optWfRaySort) { rd_tl_mark(p, 7); rc = rd_wf_reorder_rays(p, scene, live); if (rc) return rc; }
+            rd_tl_mark(p, 2);
             // primary rays are coherent (static batches); bounce rays are not (dynamic fetch), option wf_dynamic: 0 never, 1 bounces, 2 always
             rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) return rc;
-            if (S.sortOn) { rc = rd_wf_sort(p, live); if (rc) return rc; }
+            if (S.sortOn) { rd_tl_mark(p, 3); rc = rd_wf_sort(p, live); if (rc) return rc; }
+            rd_tl_mark(p, 4);
             RD_CU(cuLaunchKernel(m->wfShade, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
             p->launches += 1;
             rc = rd_wf_advance(p, 2u, 0u); if (rc) return rc;
             if (rt[3]) break;
         }
+        rd_tl_mark(p, 5);
         RD_CU(cuLaunchKernel(m->wfAccumulate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
     }
+    rd_tl_mark(p, 6);
     RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
     p->launches += 1;
+    rd_tl_mark(p, 0);
     return RD_OK;
 }
 
@@ -840,7 +881,7 @@ extern "C" int rd_trace_rays_range(rd_platform* p, unsigned width, unsigned heig
         return RD_OK;
     }
     if (full) {
-        const unsigned info[8] = {(unsigned)first, (unsigned)total, tileW, 0u, p->ilWorld, p->ilRank, p->ilBandRows, 0u};
+        const unsigned info[8] = {(unsigned)first, (unsigned)total, tileW, 0u, p->ilWorld, p->ilRank, p->ilBandRows, (unsigned)p->smCount};
         RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
         RD_CU(cuLaunchKernel(m->raygen, full, 1, 1, block, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
         p->launches += 1;
@@ -988,6 +1029,65 @@ extern "C" int rd_trace_rays_interleaved(rd_platform* p, unsigned width, unsigne
     const int rc = rd_trace_rays_range(p, width, height, 0, (unsigned long long)owned * 4u * width);
     p->ilWorld = 0; p->ilRank = 0; p->ilBandRows = 0;
     return rc;
+}
+
+// ---- multi-GPU dynamic partition by work units ----------------------------------------------------------------
+// The frame is cut into `units` equal runs of 8x4-tile rows; every rank of the job takes the next unit from the job-wide
+// counter (the same IPC-shared counter array as chunk stealing: system-scope atomic over NVLink, one per unit) and renders
+// it with the bound pipeline in whatever mode is on -- including wavefront mode, whose stage launches the host sequences.
+// The NEXT unit is requested before the current one is enqueued, so the round trip (one tiny kernel + an event wait)
+// hides behind the rendering of the current unit. ownedMask: bit u = this rank rendered unit u (rd_frame_gather_units).
+__global__ void rd_k_take_unit(unsigned* counter, volatile unsigned* slot) { *slot = atomicAdd_system(counter, 1u); }
+
+extern "C" int rd_trace_rays_units(rd_platform* p, unsigned width, unsigned height, unsigned units, unsigned frame,
+                                   unsigned long long* ownedMask)
+{
+    if (!p || !p->boundModule || !ownedMask) { rd_set_error("rd_trace_rays_units: no pipeline bound / null argument"); return RD_E_STATE; }
+    if (!units || units > 64u || (width % 8u) || (height % 4u) || !p->optTile) {
+        rd_set_error("rd_trace_rays_units: needs 1..64 units, width %% 8 == 0, height %% 4 == 0, option tile"); return RD_E_ARG;
+    }
+    RD_CUDA(cudaSetDevice(p->device));
+    if (!p->stealCounters) { unsigned char tmp[64]; int rc = rd_steal_counter_export(p, tmp); if (rc) return rc; }
+    if (!p->unitSlots) {
+        void* h = 0; void* d = 0;
+        RD_CUDA(cudaHostAlloc(&h, 2 * sizeof(unsigned), cudaHostAllocMapped));
+        RD_CUDA(cudaHostGetDevicePointer(&d, h, 0));
+        p->unitSlots = (volatile unsigned*)h; p->unitSlotsDev = (unsigned*)d;
+        RD_CUDA(cudaEventCreateWithFlags(&p->unitEvent, cudaEventDisableTiming));
+    }
+    if (!p->stealImported)   // the owner clears the slot that comes into use half a ring from now
+        RD_CUDA(cudaMemsetAsync(p->stealCounters + ((frame + p->stealSlots / 2) % p->stealSlots), 0, sizeof(unsigned), p->stream));
+    unsigned* counter = p->stealCounters + (frame % p->stealSlots);
+    unsigned rt[4] = {0, 0, 0, 0};
+    if (p->optWavefront) {
+        if (p->boundArgs.size() < 3) { rd_set_error("rd_trace_rays_units: wavefront mode needs RTProp, imageScratch, image as descriptors 0..2"); return RD_E_STATE; }
+        RD_CUDA(cudaMemcpyAsync(rt, (const void*)p->boundArgs[0], 16, cudaMemcpyDeviceToHost, p->stream));
+    }
+    const unsigned tileRows = height / 4u;
+    *ownedMask = 0;
+    p->tlUsed = 0;
+    int which = 0;
+    rd_k_take_unit<<<1, 1, 0, p->stream>>>(counter, p->unitSlotsDev + which);
+    p->launches += 1;
+    RD_CUDA(cudaEventRecord(p->unitEvent, p->stream));
+    RD_CUDA(cudaEventSynchronize(p->unitEvent));
+    unsigned cur = p->unitSlots[which];
+    while (cur < units) {
+        which ^= 1;
+        rd_k_take_unit<<<1, 1, 0, p->stream>>>(counter, p->unitSlotsDev + which);   // ahead of the current unit's work in stream order
+        p->launches += 1;
+        RD_CUDA(cudaEventRecord(p->unitEvent, p->stream));
+        const unsigned r0 = (unsigned)((unsigned long long)tileRows * cur / units), r1 = (unsigned)((unsigned long long)tileRows * (cur + 1u) / units);
+        if (r1 > r0) {
+            const unsigned long long first = (unsigned long long)r0 * 4u * width, count = (unsigned long long)(r1 - r0) * 4u * width;
+            int rc = p->optWavefront ? rd_trace_rays_wavefront(p, width, height, first, count, rt, false) : rd_trace_rays_range(p, width, height, first, count);
+            if (rc) return rc;
+        }
+        *ownedMask |= 1ull << cur;
+        RD_CUDA(cudaEventSynchronize(p->unitEvent));   // the next unit's number arrived while this one was being enqueued / rendered
+        cur = p->unitSlots[which];
+    }
+    return RD_OK;
 }
 
 extern "C" int rd_trace_rays_async(rd_platform* p, unsigned width, unsigned height)

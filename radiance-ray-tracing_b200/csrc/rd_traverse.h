@@ -229,21 +229,14 @@ RD_HD rd_u32 rd_node_test(const RdNode8* n, const RdRayFrame& f, float tmin, flo
     return acc;
 }
 
-// hit nibbles of the inner slots -> priority bits 24..31 (bit 24 + p set <=> the child in slot p ^ octinv was hit)
-RD_HD rd_u32 rd_inner_priorities(rd_u32 hitInner, const RdRayFrame& f)
-{
-    const rd_u32 E = hitInner & 0x0f0f0f0fu, O = (hitInner >> 4) & 0x0f0f0f0fu;   // byte k = slot 2k / slot 2k + 1, value 0 or 1
-    const rd_u32 Ep = RD_PRMT(E, O, f.selE), Op = RD_PRMT(E, O, f.selE ^ 0x4444u); // byte k = priority 2k / 2k + 1
-    // byte k (bit 8k) -> bit 24 + 2k (+1): every partial product lands on its own bit, the ones below bit 24 are masked off
-    return ((Ep * 0x01041040u) | (Op * 0x02082080u)) & 0xff000000u;
-}
 #else
 // ---------------------------------------------------------------------------------------------------------------
 // 8-bit quantised nodes (round-1 form, kept for the A/B measurement).
 struct RdRayFrame {   // per-space ray constants for the quantised box test
     float ox, oy, oz, dx, dy, dz;
     float ix, iy, iz;   // 1/d with |d| clamped away from zero
-    rd_u32 octinv4;     // (7 - octant) replicated to 4 bytes; octant bit2=x<0, bit1=y<0, bit0=z<0
+    rd_u32 octinv;      // 7 - octant; octant bit2=x<0, bit1=y<0, bit0=z<0
+    rd_u32 selE;        // PRMT selector that sorts the even-priority hit bytes (see rd_inner_priorities)
 };
 
 RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, float dy, float dz, float)
@@ -251,16 +244,16 @@ RD_HD void rd_frame_set(RdRayFrame& f, float ox, float oy, float oz, float dx, f
     f.ox = ox; f.oy = oy; f.oz = oz; f.dx = dx; f.dy = dy; f.dz = dz;
     f.ix = rd_safe_rcp(dx); f.iy = rd_safe_rcp(dy); f.iz = rd_safe_rcp(dz);
     rd_u32 oct = (f.ix < 0.0f ? 4u : 0u) | (f.iy < 0.0f ? 2u : 0u) | (f.iz < 0.0f ? 1u : 0u);
-    f.octinv4 = (7u - oct) * 0x01010101u;
+    f.octinv = 7u - oct;
+    f.selE = (0x3210u ^ ((f.octinv >> 1) * 0x1111u)) | ((f.octinv & 1u) ? 0x4444u : 0u);
 }
-#define RD_OCTINV(f) ((f).octinv4 & 0xffu)
+#define RD_OCTINV(f) ((f).octinv)
 
-// Tests the 8 quantised child boxes of one node against the ray interval [tmin, tbest].
-// Returns the hit mask: bits 24..31 = inner children keyed by visiting priority (highest first),
-// bits 0..23 = leaf records (one bit per primitive record relative to primBase).
+// Tests the 8 quantised child boxes of one node against the ray interval [tmin, tbest]. Returns the hit slots as
+// nibbles: 0xf << 4s for every slot s whose box the ray enters.
 // Plane distance of quantised coordinate c on one axis: t = (p + c*s - o) / d = c*a + b with a = s/d, b = (p - o)/d;
 // the conversion of the byte runs on the XU pipe (I2F.U8), floor / ceil quantisation keeps the test conservative.
-RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const RdU4& n3, const RdU4& n4,
+RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n2, const RdU4& n3, const RdU4& n4,
                           const RdRayFrame& f, float tmin, float tbest)
 {
     const float sx = RD_U2F((n0.w & 0xffu) << 23), sy = RD_U2F(((n0.w >> 8) & 0xffu) << 23),
@@ -268,26 +261,11 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
     const float Ax = sx * f.ix, Ay = sy * f.iy, Az = sz * f.iz;
     const float bx = (RD_U2F(n0.x) - f.ox) * f.ix, by = (RD_U2F(n0.y) - f.oy) * f.iy, bz = (RD_U2F(n0.z) - f.oz) * f.iz;
 #define RD_PLANE(q, j, P, pb) RD_FMA((float)(((q) >> (8 * (j))) & 0xffu), P, pb)
-    rd_u32 hitmask = 0;
+    rd_u32 acc = 0;
 #if defined(__CUDA_ARCH__)
 #pragma unroll
 #endif
     for (int h = 0; h < 2; ++h) {
-        const rd_u32 meta4 = h ? n1.w : n1.z;
-        // 0xff in the bytes of the inner children, spread from the node's imask nibble (bit j = slot j is inner) by two
-        // integer multiply-adds (FMA pipe) instead of being derived from the meta bytes on the ALU pipe
-        const rd_u32 innerMask4 = ((((n0.w >> (24 + 4 * h)) & 0xfu) * 0x00204081u) & 0x01010101u) * 0xffu;
-        const rd_u32 bitIndex4 = (meta4 ^ (f.octinv4 & innerMask4)) & 0x1f1f1f1fu;
-#if defined(__CUDA_ARCH__)
-        // the shift below takes its amount modulo 32, so the index bytes need no masking here
-        rd_u32 childBits4 = (meta4 >> 5) & 0x07070707u, shift4 = meta4 ^ (f.octinv4 & innerMask4);
-        // keep the two 4-wide words as computed: left alone, ptxas re-derives them per child under the hit predicate
-        // (8 ALU instructions per child instead of 4)
-        asm volatile("" : "+r"(childBits4), "+r"(shift4));
-        (void)bitIndex4;
-#else
-        const rd_u32 childBits4 = (meta4 >> 5) & 0x07070707u;
-#endif
         const rd_u32 qlx = h ? n2.y : n2.x, qly = h ? n2.w : n2.z, qlz = h ? n3.y : n3.x;
         const rd_u32 qhx = h ? n3.w : n3.z, qhy = h ? n4.y : n4.x, qhz = h ? n4.w : n4.z;
         const rd_u32 nx = f.ix < 0.0f ? qhx : qlx, fx = f.ix < 0.0f ? qlx : qhx;
@@ -297,20 +275,24 @@ RD_HD rd_u32 rd_node_test(const RdU4& n0, const RdU4& n1, const RdU4& n2, const 
 #pragma unroll
 #endif
         for (int j = 0; j < 4; ++j) {
-            const int sh = 8 * j;
             const float tn = RD_FMAX(RD_FMAX(RD_PLANE(nx, j, Ax, bx), RD_PLANE(ny, j, Ay, by)), RD_FMAX(RD_PLANE(nz, j, Az, bz), tmin));
             const float tf = RD_FMIN(RD_FMIN(RD_PLANE(fx, j, Ax, bx), RD_PLANE(fy, j, Ay, by)), RD_FMIN(RD_PLANE(fz, j, Az, bz), tbest));
-#if defined(__CUDA_ARCH__)
-            if (tn <= tf) hitmask |= __byte_perm(childBits4, 0u, 0x4440u | (unsigned)j) << ((shift4 >> sh) & 31u);
-#else
-            if (tn <= tf) hitmask |= ((childBits4 >> sh) & 0xffu) << ((bitIndex4 >> sh) & 0xffu);
-#endif
+            if (tn <= tf) acc |= 0xfu << (4 * (4 * h + j));
         }
     }
 #undef RD_PLANE
-    return hitmask;
+    return acc;
 }
 #endif  // RD_NODE_F32
+
+// hit nibbles of the inner slots -> priority bits 24..31 (bit 24 + p set <=> the child in slot p ^ octinv was hit)
+RD_HD rd_u32 rd_inner_priorities(rd_u32 hitInner, const RdRayFrame& f)
+{
+    const rd_u32 E = hitInner & 0x0f0f0f0fu, O = (hitInner >> 4) & 0x0f0f0f0fu;   // byte k = slot 2k / slot 2k + 1, value 0 or 1
+    const rd_u32 Ep = RD_PRMT(E, O, f.selE), Op = RD_PRMT(E, O, f.selE ^ 0x4444u); // byte k = priority 2k / 2k + 1
+    // byte k (bit 8k) -> bit 24 + 2k (+1): every partial product lands on its own bit, the ones below bit 24 are masked off
+    return ((Ep * 0x01041040u) | (Op * 0x02082080u)) & 0xff000000u;
+}
 
 // Traversal state of one ray over the two-level structure. begin() arms it, step() runs one
 // iteration and returns false when the ray is finished. Kept as a struct so that a persistent kernel
@@ -384,6 +366,16 @@ struct RdTraversal {
             const rd_u32 acc = rd_node_test(n, f, tmin, tbest);
             ng.x = n0.x; ng.y = rd_inner_priorities(acc & n1.x, f) | n0.w;
             const rd_u32 leafBits = acc & n0.z;
+            const rd_u32 nodePrimBase = n0.y, nodeLeafNib = n0.z;
+#else
+            RdU4 n0, n1, n2, n3, n4;   // n1 = { childBase, primBase, leafNib, innerNib }
+            RD_LOAD_U4(n0, &n->w[0]); RD_LOAD_U4(n1, &n->w[1]); RD_LOAD_U4(n2, &n->w[2]);
+            RD_LOAD_U4(n3, &n->w[3]); RD_LOAD_U4(n4, &n->w[4]);
+            const rd_u32 acc = rd_node_test(n0, n2, n3, n4, f, tmin, tbest);
+            ng.x = n1.x; ng.y = rd_inner_priorities(acc & n1.w, f) | (n0.w >> 24);
+            const rd_u32 leafBits = acc & n1.z;
+            const rd_u32 nodePrimBase = n1.y, nodeLeafNib = n1.z;
+#endif
             if (leafBits) {
                 if (blasSp < 0) {
                     // top level: few nodes, few records -- densify the record bits so a parked group fits a stack entry
@@ -391,25 +383,16 @@ struct RdTraversal {
                     while (lb) {
                         const rd_u32 low = lb & (0u - lb);
                         lb ^= low;
-                        dense |= 1u << RD_POPC(n0.z & (low - 1u));
+                        dense |= 1u << RD_POPC(nodeLeafNib & (low - 1u));
                     }
-                    tg.x = n0.y; tg.y = dense;
+                    tg.x = nodePrimBase; tg.y = dense;
                 } else {
-                    pend[0].x = n0.y; pend[0].y = leafBits; pend[1].x = n0.z; np = 1;
+                    // np indexes the slot on purpose: with a constant address ptxas forwards the stored values in registers and
+                    // threads lanes straight from the node test into the triangle loop -- the warp then stops walking the
+                    // phases together (measured -12 % on C2, -19 % at 10 M triangles, profiles/README_r2.md)
+                    pend[2 * np].x = nodePrimBase; pend[2 * np].y = leafBits; pend[2 * np + 1].x = nodeLeafNib; ++np;
                 }
             }
-#else
-            RdU4 n0, n1, n2, n3, n4;
-            RD_LOAD_U4(n0, &n->w[0]); RD_LOAD_U4(n1, &n->w[1]); RD_LOAD_U4(n2, &n->w[2]);
-            RD_LOAD_U4(n3, &n->w[3]); RD_LOAD_U4(n4, &n->w[4]);
-            const rd_u32 hm = rd_node_test(n0, n1, n2, n3, n4, f, tmin, tbest);
-            ng.x = n1.x; ng.y = (hm & 0xff000000u) | (n0.w >> 24);
-            const rd_u32 leafBits = hm & 0x00ffffffu;
-            if (leafBits) {
-                if (blasSp < 0) { tg.x = n1.y; tg.y = leafBits; }
-                else { pend[0].x = n1.y; pend[0].y = leafBits; np = 1; }
-            }
-#endif
         } else if (ng.y) {
             tg = ng; ng.x = 0; ng.y = 0;   // a parked top-level instance group came off the stack
         }
@@ -435,22 +418,13 @@ struct RdTraversal {
             }
         } else if (np > 0) {
             // ---- 2. triangle phase
-            np = 0;
-            const rd_u32 gbase = pend[0].x;
-            rd_u32 gbits = pend[0].y;
-#if RD_NODE_F32
-            const rd_u32 gnib = pend[1].x;
-#endif
-            while (gbits) {
-#if RD_NODE_F32
-                const rd_u32 low = gbits & (0u - gbits);
-                gbits ^= low;
-                const RdTri* tr = tris + (gbase + (rd_u32)RD_POPC(gnib & (low - 1u)));
-#else
-                const rd_u32 k = (rd_u32)RD_FFS(gbits) - 1u;
-                gbits &= gbits - 1u;
-                const RdTri* tr = tris + (gbase + k);
-#endif
+            RdStackEntry g; g.x = 0; g.y = 0;
+            rd_u32 gnib = 0;
+            while (np > 0 || g.y) {
+                if (!g.y) { --np; g = pend[2 * np]; gnib = pend[2 * np + 1].x; }
+                const rd_u32 low = g.y & (0u - g.y);
+                g.y ^= low;
+                const RdTri* tr = tris + (g.x + (rd_u32)RD_POPC(gnib & (low - 1u)));
                 RdF4 a, b, c;
                 RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
                 onCandidate.countTri();

@@ -65,10 +65,10 @@ struct RD_ALIGN(16) RdNode8 { RdU4 w[16]; };
 //  w[0] = { p.x, p.y, p.z (float bits),  ex | ey<<8 | ez<<16 | imask<<24 }
 //         p = lower corner of the node box, e* = biased float exponents of the grid step per axis,
 //         imask bit s set <=> slot s holds an inner child
-//  w[1] = { childBase, primBase, meta[0..3], meta[4..7] }
+//  w[1] = { childBase, primBase, leafNib, innerNib }
 //         inner child in slot s lives at node index childBase + popc(imask & ((1<<s)-1))
-//         meta byte: 0 = empty; inner = 0b001_11sss; leaf = unary(count 1..3)<<5 | first record
-//         offset (0..21) relative to primBase
+//         leafNib nibble s = unary primitive count of a leaf slot (0b0001 / 0b0011 / 0b0111), bit b set <=> primitive
+//         record primBase + popc(leafNib & ((1<<b)-1)); innerNib = 0x1 in the nibble of every inner slot
 //  w[2] = { qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7] }
 //  w[3] = { qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7] }
 //  w[4] = { qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7] }

@@ -29,6 +29,8 @@ ABI_SYMBOLS = [
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
     "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
+    "rd_comm_unique_id", "rd_comm_init", "rd_comm_adopt", "rd_comm_destroy", "rd_frame_gather", "rd_frame_gather_ranges",
+    "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline",
 ]
 
 
@@ -77,6 +79,12 @@ def lib():
             "rd_generate_primary_rays": [vp, vp, u, u, u, u, vp, vp], "rd_set_option": [vp, C.c_char_p, C.c_long],
             "rd_ray_count": [vp, C.POINTER(C.c_uint64), C.c_int],
             "rd_status": [vp, C.POINTER(C.c_uint32), C.c_int],
+            "rd_comm_unique_id": [vp], "rd_comm_init": [vp, C.c_int, C.c_int, vp], "rd_comm_adopt": [vp, vp, C.c_int, C.c_int],
+            "rd_comm_destroy": [vp], "rd_frame_gather": [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint],
+            "rd_frame_gather_ranges": [vp, vp, C.c_uint, vp, vp],
+            "rd_trace_rays_units": [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_uint64)],
+            "rd_frame_gather_units": [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint64],
+            "rd_wf_timeline": [vp, vp, vp, C.c_uint, C.POINTER(C.c_uint)],
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
@@ -228,6 +236,54 @@ def StealOwned(plt, capacity=1 << 20):
     ids, n = np.zeros(capacity, np.uint32), C.c_uint(0)
     _check(lib().rd_steal_owned(plt.handle, ids.ctypes.data, capacity, C.byref(n)))
     return ids[:min(capacity, n.value)].copy()
+
+
+def CommUniqueId():
+    """128-byte NCCL id created on rank 0; hand it to the other ranks (any transport)."""
+    buf = (C.c_ubyte * 128)()
+    _check(lib().rd_comm_unique_id(buf))
+    return np.frombuffer(bytes(buf), np.uint8).copy()
+
+
+def CommInit(plt, rank, world, unique_id):
+    uid = np.ascontiguousarray(unique_id, np.uint8)
+    assert uid.size == 128
+    _check(lib().rd_comm_init(plt.handle, int(rank), int(world), uid.ctypes.data))
+
+
+def CommDestroy(plt):
+    _check(lib().rd_comm_destroy(plt.handle))
+
+
+def FrameGather(plt, image, width, height, item_bytes=4, band_tile_rows=1):
+    """After TraceRaysInterleaved on every rank: the bands of all ranks land in rank 0's buffer (async)."""
+    _check(lib().rd_frame_gather(plt.handle, image.handle, width, height, item_bytes, band_tile_rows))
+
+
+def FrameGatherRanges(plt, image, item_bytes, first, count):
+    f, c = np.ascontiguousarray(first, np.uint64), np.ascontiguousarray(count, np.uint64)
+    _check(lib().rd_frame_gather_ranges(plt.handle, image.handle, item_bytes, f.ctypes.data, c.ctypes.data))
+
+
+def TraceRaysUnits(plt, width, height, units, frame):
+    """Dynamic partition: renders the work units this rank wins; returns their bit mask."""
+    mask = C.c_uint64(0)
+    _check(lib().rd_trace_rays_units(plt.handle, width, height, units, frame, C.byref(mask)))
+    return int(mask.value)
+
+
+def FrameGatherUnits(plt, image, width, height, item_bytes, units, owned_mask):
+    _check(lib().rd_frame_gather_units(plt.handle, image.handle, width, height, item_bytes, units, C.c_uint64(owned_mask)))
+
+
+WF_STAGE_NAMES = {1: "generate", 2: "trace", 3: "sort", 4: "shade", 5: "accumulate", 6: "resolve", 7: "ray_sort"}
+
+
+def WavefrontTimeline(plt, capacity=4096):
+    """[(stage name, ms)] of the last wavefront-mode call made under option wf_timeline."""
+    ms, codes, n = np.zeros(capacity, np.float32), np.zeros(capacity, np.int32), C.c_uint(0)
+    _check(lib().rd_wf_timeline(plt.handle, ms.ctypes.data, codes.ctypes.data, capacity, C.byref(n)))
+    return [(WF_STAGE_NAMES.get(int(codes[i]), "?"), float(ms[i])) for i in range(min(n.value, capacity))]
 
 
 def TopAccelStructToFile(plt, accelStruct, path):

@@ -389,7 +389,19 @@ RD_F size_t get_global_id(uint dim)
 {
     if (dim != 0) return 0;
     if (rd_launch_info[3]) return rd_wf_gid[threadIdx.x];
-    unsigned int t = rd_launch_info[0] + blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned int blk = blockIdx.x;
+#ifdef RD_SM_LOCAL
+    // ablation: blocks that are resident on one SM together (block b, b + S, b + 2S, ... of a wave of S * RD_SM_LOCAL blocks,
+    // S = rd_launch_info[7] SMs) render neighbouring tiles, so the warps of an SM share the nodes in its L1
+    {
+        const unsigned int S = rd_launch_info[7], G = S * RD_SM_LOCAL;
+        if (S && blk < (gridDim.x / G) * G) {
+            const unsigned int g = blk / G, r = blk - g * G;
+            blk = g * G + (r % S) * RD_SM_LOCAL + r / S;
+        }
+    }
+#endif
+    unsigned int t = rd_launch_info[0] + blk * blockDim.x + threadIdx.x;
     unsigned int w = rd_launch_info[2];
     if (w) {
         // t enumerates 8x4 pixel tiles row by row; lanes of a warp cover one tile.
