@@ -1,14 +1,21 @@
 #!/usr/bin/env python
-"""bench.py -- BASELINE.json metric on BASELINE config C2 (configs[1]): primary-ray closest-hit,
-1920x1080, 1 spp, procedural 1 002 528-triangle height-field, user program programs/primary.cl
-through RD::TraceRays. One "step" = one TraceRays frame (W*H primary rays).
+"""bench.py -- BASELINE.json metric. Headline = BASELINE config C2 (configs[1]): primary-ray closest-hit, 1920x1080, 1 spp,
+procedural 1 002 528-triangle height-field, user program programs/primary.cl through RD::TraceRays. One "step" = one
+TraceRays frame (W*H primary rays).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
 
-N > 1 is launched by torchrun (one rank per GPU): the scene is replicated, the frame is split into
-contiguous runs of 8x4 screen tiles (one run per rank), and the RGBA8 framebuffer is gathered on
-rank 0 with NCCL (the only collective). Scaling is "strong" (the frame is fixed).
-Prints ONE JSON line on rank 0. See DESIGN.md "Measurement" for every field's definition.
+The same JSON line carries, under "extra", every other BASELINE configuration at its own size (each a few frames):
+  P10M  north_star's target: primary closest-hit on the 10 M-triangle height-field (own roofline + issue-slot accounting)
+  C1    the reference's own samples/shader.cl + sbt.json (800x600, 16 spp, depth 8) when oracle/_ref/samples is present
+  C3    4-bounce path tracing, 10 M triangles, 16 spp: inline / wavefront sorted / wavefront unsorted
+  C4    64 hit groups, 4096 instances: hit-group sort on vs off
+  C5    4K 64 spp on the 50 M-triangle replicated scene (the single-GPU leg of the multi-GPU configuration)
+N > 1 is launched by torchrun (one rank per GPU): the scene is replicated, the frame is dealt to the ranks in
+interleaved bands of 8x4-tile rows (rd_trace_rays_interleaved) or taken dynamically in work units from a job-wide
+counter (rd_trace_rays_units), and the finished framebuffer bands are gathered on rank 0 with NCCL through the C ABI
+(rd_frame_gather / rd_frame_gather_units) -- the only collective. Scaling is "strong" (the frame is fixed); extras at
+N > 1: C3 and C5 frame ms. Prints ONE JSON line on rank 0. See DESIGN.md "Measurement" for every field's definition.
 """
 import argparse
 import json
@@ -26,10 +33,20 @@ import __graft_entry__ as entry  # noqa: E402
 
 WIDTH, HEIGHT, GRID_N = 1920, 1080, 708
 WORKLOAD = "C2: primary-ray closest-hit, 1920x1080, 1 spp, height-field n=708 (1002528 triangles), programs/primary.cl"
+L2_NOTE = "256 MiB flush between timed frames"
 NODE_BYTES, TRI_BYTES, RAY_BYTES, HIT_BYTES = 80, 48, 32, 16
-# dram__bytes_read.sum + dram__bytes_write.sum of one raygen launch of this workload, from the ncu --set full capture
-# summarised in profiles/ncu_r1c_primary.txt (93.44 MB + 29.40 MB); re-measured whenever the kernel changes
-NCU_DRAM_BYTES_PER_LAUNCH = 124.57e6   # profiles/ncu_r1g_primary.txt: dram read 93.56 MB + write 31.01 MB
+# 148 SMs x 4 schedulers x 1.965 GHz: warp instructions the B200 can issue per second (one per scheduler per cycle)
+ISSUE_PEAK = 148 * 4 * 1.965e9
+
+
+def ncu_reference(key):
+    """Per-launch DRAM bytes and warp instructions of the dominant kernel from the committed ncu --set full captures
+    (profiles/ncu_traffic.json names the capture file and the commit it was taken at); None when absent."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
 
 
 def measured_peaks():
@@ -135,7 +152,8 @@ def reference_arm(args, rank, world):
     return json.dumps({"impl": "reference", "metric": "Mrays/s (primary closest-hit, 1080p)", "value": v, "unit": "Mrays/s",
                       "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
                       "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                      "config": {"workload": WORKLOAD, "sample": sample},
+                      "config": {"workload": WORKLOAD, "l2": L2_NOTE, "rays_per_step": WIDTH * HEIGHT, "partition": "single GPU"},
+                      "details": {"sample": sample, "note": "CPU arm: each step renders the sample rows of the frame; value = rays of the sample / time"},
                       "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "reference", "sample": sample},
                       "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
@@ -221,16 +239,102 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
     return out
 
 
-def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bundle, w, h, spp, depth, frames=3):
-    """Path tracing across all ranks with dynamic chunk stealing: frame ms (max over ranks, device events, gather
-    included) and Mrays/s with the rays of one frame counted on rank 0 by a count_rays build."""
+def primary_config(torch, pkg, plt, stream, flush, name, grid_n, key):
+    """Primary closest-hit on a height-field of grid_n x grid_n quads at 1080p (P10M: north_star's target configuration):
+    Mrays/s, the traversal's own node / triangle fetch counts, the HBM roofline and the issue-slot accounting."""
+    rd, scenes = pkg.rd, pkg.scenes
+    bundle = scenes.heightfield_scene(grid_n, WIDTH, HEIGHT)
+    t0 = time.perf_counter()
+    tlas, blas = scenes.build_scene(plt, bundle)
+    plt.sync()
+    build_ms = (time.perf_counter() - t0) * 1e3
+    ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, 1, 1, 0))
+    pipe, module = scenes.make_pipeline(plt, "primary")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    ms = time_frames(torch, plt, rd, stream, flush, WIDTH, HEIGHT, reps=9)
+    n = WIDTH * HEIGHT
+    ra, rb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 16)
+    ha, hb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 4)
+    rd.GeneratePrimaryRays(plt, ds.rdCam, 0, 0, WIDTH, HEIGHT, ra, rb)
+    rd.TraceRayList(plt, tlas, ra, rb, ha, hb, n, rd.TRACE_COUNTERS)
+    plt.sync()
+    c = rd.TraceCounters(plt)
+    for hnd in (ra, rb, ha, hb):
+        hnd.free()
+    nodes_per_ray, tris_per_ray = c["nodes"] / c["rays"], c["tris"] / c["rays"]
+    bytes_per_ray = nodes_per_ray * NODE_BYTES + tris_per_ray * TRI_BYTES + RAY_BYTES + HIT_BYTES
+    peak, peak_kind = measured_peaks()
+    achieved = n * bytes_per_ray / (ms * 1e-3) / 1e9
+    ncu = ncu_reference(key) or {}
+    out = {"workload": name, "triangles": bundle.triangle_count(), "value": n / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms,
+           "build_ms_incl_upload": build_ms, "bvh": blas[0].stats(), "raygen": module.info(),
+           "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                        "traffic": ncu.get("dram_bytes_per_launch"), "traffic_source": ncu.get("source"),
+                        "algorithmic_bytes_per_launch": n * bytes_per_ray, "peak_kind": peak_kind,
+                        "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)", "kernel_ms": ms,
+                        "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray, "tris_per_ray": tris_per_ray}}
+    if ncu.get("warp_inst_per_launch"):
+        wi = ncu["warp_inst_per_launch"] / n
+        out["issue"] = {"warp_inst_per_ray": wi, "source": ncu.get("source"), "issue_peak_warp_inst_per_s": ISSUE_PEAK,
+                        "ceiling_mrays_at_full_issue": ISSUE_PEAK / wi / 1e6, "frac_of_issue_ceiling": (n / ms / 1e3) / (ISSUE_PEAK / wi / 1e6)}
+    for hnd in [tlas] + list(blas):
+        hnd.free()
+    return out
+
+
+def c1_config(torch, pkg, plt, stream, flush):
+    """BASELINE configs[0] on the GPU: the reference's own samples/shader.cl + sbt.json (copied unmodified into the git-ignored
+    oracle/_ref/samples/ by oracle/Makefile -- plugin INPUT, read here as a user would read their shader file), SURVEY 8(d)
+    C1 scene, 800x600, 16 spp, depth 8."""
+    rd, scenes = pkg.rd, pkg.scenes
+    cl = os.path.join(ROOT, "oracle", "_ref", "samples", "shader.cl")
+    sbt = os.path.join(ROOT, "oracle", "_ref", "samples", "sbt.json")
+    if not (os.path.exists(cl) and os.path.exists(sbt)):
+        return {"unavailable": "oracle/_ref/samples/shader.cl not present on this box"}
+    src, sbt_text = open(cl).read(), open(sbt).read()
+    w, h, spp, depth = 800, 600, 16, 8
+    b = scenes.cornell_like()
+    b.camera["x"], b.camera["y"] = 0.013, 1.037
+    tlas, blas = scenes.build_scene(plt, b)
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, spp, depth, 0))
+    plt.set_option("count_rays", 1)
+    try:
+        pipe, _ = scenes.make_pipeline(plt, source=src, sbt=sbt_text)
+    finally:
+        plt.set_option("count_rays", 0)
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    plt.ray_count()
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    rays = plt.ray_count()
+    pipe, module = scenes.make_pipeline(plt, source=src, sbt=sbt_text)
+    rd.BindPipeline(plt, pipe)
+    ms = time_frames(torch, plt, rd, stream, flush, w, h, reps=5)
+    for hnd in [tlas] + list(blas):
+        hnd.free()
+    return {"workload": "C1: samples/shader.cl + samples/sbt.json as shipped, Cornell-like scene (%d triangles), 800x600, 16 spp, depth 8" % b.triangle_count(),
+            "rays_per_frame": rays, "value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "raygen": module.info(),
+            "parity": "tests/test_gpu_c1.py compares this frame with the reference runtime (profiles/parity_r2.json)"}
+
+
+def comm_setup(torch, dist, rd, plt, rank, world):
+    """One NCCL communicator inside the library per rank (rd_comm_init): rank 0 creates the id, torch.distributed only
+    carries its 128 bytes; the dynamic partition's counter handle travels the same way."""
+    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        uid.copy_(torch.from_numpy(rd.CommUniqueId()))
+    dist.broadcast(uid, src=0)
+    rd.CommInit(plt, rank, world, uid.cpu().numpy())
+
+
+def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bundle, w, h, spp, depth, frames=3, units_per_rank=4):
+    """Path tracing across all ranks, wavefront mode: frame ms (max over ranks, device events, gather included) of the
+    static interleaved band partition (rd_trace_rays_interleaved + rd_frame_gather) and of the dynamic work-unit
+    partition (rd_trace_rays_units + rd_frame_gather_units); Mrays/s with the rays of one frame counted on rank 0."""
     rd, scenes, mg = pkg.rd, pkg.scenes, pkg.multigpu
     tlas, blas = scenes.build_scene(plt, bundle)
     ds = scenes.DeviceScene(plt, bundle, tlas, w, h, scenes.rtprop(0, spp, depth, 0))
-    n = w * h
-    image_t = torch.zeros(n * 4, dtype=torch.uint8, device="cuda")
-    ds.rdImage = rd.WrapBuffer(plt, image_t.data_ptr(), n * 4, owner=image_t)
-    ds.descriptors[2] = ds.rdImage
     rays = 0
     if rank == 0:
         plt.set_option("count_rays", 1)
@@ -243,23 +347,24 @@ def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bund
         plt.ray_count()
         rd.TraceRays(plt, 0, 0, 0, w, h)
         rays = plt.ray_count()
-    plt.set_option("stealing", 1)
     mg.exchange_steal_handle(rd, plt, rank, world, dist, "cuda")
     pipe, _ = scenes.make_pipeline(plt, "path")
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
+    units = min(64, world * units_per_rank)
+    frame_no = [1000]
 
     def timed(render):
         ms = []
         for f in range(frames + 1):
             torch.cuda.synchronize()
             dist.barrier()
+            ds.set_rtprop(0, spp, depth)
+            plt.sync()
             with torch.cuda.stream(stream):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record(stream)
-                image_t.zero_()
-                render(f)
-                mg.combine_sum(image_t, world, dist)
+                render()
                 e1.record(stream)
             torch.cuda.synchronize()
             t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
@@ -267,27 +372,54 @@ def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bund
             ms.append(float(t[0]))
         return float(np.median(ms[1:]))
 
-    steal_ms = timed(lambda f: rd.TraceRaysSteal(plt, w, h, 600 + f, 32))
-    owned = torch.tensor([len(rd.StealOwned(plt))], device="cuda")
-    allc = [torch.zeros_like(owned) for _ in range(world)]
-    dist.all_gather(allc, owned)
-    # wavefront stages on the interleaved band partition
+    def static_frame():
+        rd.TraceRaysInterleaved(plt, w, h, rank, world, 1)
+        rd.FrameGather(plt, ds.rdImage, w, h, 4, 1)
+
+    owned = [0]
+
+    def dynamic_frame():
+        frame_no[0] += 1
+        owned[0] = rd.TraceRaysUnits(plt, w, h, units, frame_no[0])
+        rd.FrameGatherUnits(plt, ds.rdImage, w, h, 4, units, owned[0])
+
     plt.set_option("wavefront", 1)
     try:
-        def wave(f):
-            ds.set_rtprop(0, spp, depth)
-            rd.TraceRaysInterleaved(plt, w, h, rank, world, 1)
-        wave_ms = timed(wave)
+        static_ms = timed(static_frame)
+        img_static = ds.read_image() if rank == 0 else None
+        dynamic_ms = timed(dynamic_frame)
+        img_dynamic = ds.read_image() if rank == 0 else None
+        # per-rank stage timeline of one static frame (what the frame's time is made of on every rank)
+        plt.set_option("wf_timeline", 1)
+        ds.set_rtprop(0, spp, depth)
+        plt.sync()
+        rd.TraceRaysInterleaved(plt, w, h, rank, world, 1)
+        tl = rd.WavefrontTimeline(plt)
+        plt.set_option("wf_timeline", 0)
     finally:
         plt.set_option("wavefront", 0)
+        plt.set_option("wf_timeline", 0)
+    stage = {}
+    for nme, t in tl:
+        stage[nme] = stage.get(nme, 0.0) + t
+    mine = torch.tensor([stage.get(k, 0.0) for k in ("generate", "trace", "sort", "shade", "accumulate", "resolve")] +
+                        [float(bin(owned[0]).count("1"))], dtype=torch.float64, device="cuda")
+    allt = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allt, mine)
     for hnd in [tlas] + list(blas):
         hnd.free()
-    best = min(steal_ms, wave_ms)
+    if rank != 0:
+        return None
+    same = bool(np.abs(img_static[..., :3].astype(np.int32) - img_dynamic[..., :3].astype(np.int32)).max() <= 1)
+    best = min(static_ms, dynamic_ms)
     return {"workload": name, "triangles": bundle.triangle_count(), "spp": spp, "depth": depth, "rays_per_frame": rays,
             "frame_ms": best, "value": rays / best / 1e3 if rays else None, "unit": "Mrays/s",
-            "inline_stealing": {"frame_ms": steal_ms, "partition": "dynamic chunk stealing + NCCL sum-reduce",
-                                "chunks_per_rank": [int(c) for c in allc]},
-            "wavefront_interleaved": {"frame_ms": wave_ms, "partition": "interleaved tile-row bands + NCCL sum-reduce"}}
+            "wavefront_interleaved": {"frame_ms": static_ms, "partition": "interleaved tile-row bands + rd_frame_gather (one packed NCCL send per peer)"},
+            "wavefront_units": {"frame_ms": dynamic_ms, "units": units, "units_per_rank_last_frame": [int(t[6]) for t in allt],
+                                "partition": "dynamic work units from the job-wide counter + rd_frame_gather_units",
+                                "frame_equals_static": same},
+            "stage_ms_per_rank_static": {k: [round(float(t[i]), 3) for t in allt]
+                                         for i, k in enumerate(("generate", "trace", "sort", "shade", "accumulate", "resolve"))}}
 
 
 def main():
@@ -297,15 +429,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--partition", default="interleave", choices=["interleave", "steal", "static"],
-                    help="N>1: interleaved tile-row bands + sum-reduce (default), dynamic chunk stealing + sum-reduce, "
-                         "or contiguous tile rows + send/recv gather")
+    ap.add_argument("--partition", default="interleave", choices=["interleave", "units", "static"],
+                    help="N>1 headline: interleaved tile-row bands + rd_frame_gather (default), dynamic work units + "
+                         "rd_frame_gather_units, or contiguous tile rows + rd_frame_gather_ranges")
     ap.add_argument("--band", type=int, default=1, help="tile rows per band of the interleaved partition")
-    ap.add_argument("--chunk", type=int, default=32, help="work-items per stolen chunk (multiple of 32)")
-    ap.add_argument("--extra", default="c3", choices=["c3", "all"], help="extra configs measured at N=1: C3, or C3 and C4")
+    ap.add_argument("--units-per-rank", type=int, default=4, help="work units per rank of the dynamic partition")
+    ap.add_argument("--extra", default="all", help="comma list of extra configs (P10M,C1,C3,C4,C5), 'all' or 'none'")
     ap.add_argument("--readback-bands", type=int, default=24,
                     help="N=1 end-to-end leg: bands of the streamed read-back (rd_buffer_stream_to_host); 0 = plain ReadBuffer")
-    ap.add_argument("--no-extra", action="store_true", help="skip the C3 / C4 wavefront measurements (N=1 only)")
+    ap.add_argument("--no-extra", action="store_true", help="same as --extra none")
     args = ap.parse_args()
     claim_stdout()
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
@@ -315,6 +447,8 @@ def main():
         if line:
             emit(line)
         return
+    want = set() if (args.no_extra or args.extra == "none") else (
+        {"P10M", "C1", "C3", "C4", "C5"} if args.extra == "all" else {x.strip().upper() for x in args.extra.split(",")})
 
     import torch
     import torch.distributed as dist
@@ -326,11 +460,10 @@ def main():
     pkg = entry.load_package()
     rd, scenes, mg = pkg.rd, pkg.scenes, pkg.multigpu
     plt = rd.Platform.GetPlatform(local)
-    steal = world > 1 and args.partition == "steal"
-    interleave = world > 1 and args.partition == "interleave"
-    if steal:
-        plt.set_option("stealing", 1)
     stream = torch.cuda.ExternalStream(plt.stream(), device=local)
+    if world > 1:
+        comm_setup(torch, dist, rd, plt, rank, world)
+        mg.exchange_steal_handle(rd, plt, rank, world, dist, "cuda")
 
     bundle = scenes.heightfield_scene(GRID_N, WIDTH, HEIGHT)
     t0 = time.perf_counter()
@@ -344,42 +477,38 @@ def main():
     plt.sync()
     build_warm_ms = (time.perf_counter() - t0) * 1e3
     ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, 1, 1, 0))
-    # the RGBA8 framebuffer lives in a torch tensor so NCCL can gather it in place (zero copy)
     n = WIDTH * HEIGHT
-    image_t = torch.zeros(n * 4, dtype=torch.uint8, device="cuda")
-    ds.rdImage = rd.WrapBuffer(plt, image_t.data_ptr(), n * 4, owner=image_t)
-    ds.descriptors[2] = ds.rdImage
     streamed = world == 1 and args.readback_bands > 0
     if streamed:   # the module also gets the band-reporting raygen; it only runs once a host mirror is registered (e2e leg)
         plt.set_option("stream_image", 1)
     pipe, module = scenes.make_pipeline(plt, "primary")
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
-    first, count, row0, rows = mg.tile_row_range(rank, world, WIDTH, HEIGHT)
-    if steal:
-        mg.exchange_steal_handle(rd, plt, rank, world, dist, "cuda")
-        first, count = 0, n
+    firsts = [mg.tile_row_range(r, world, WIDTH, HEIGHT)[0] for r in range(world)]
+    counts = [mg.tile_row_range(r, world, WIDTH, HEIGHT)[1] for r in range(world)]
+    units = min(64, world * args.units_per_rank)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
     frame_no = [0]
 
     def render_and_gather():
         """One frame of this rank's share + the frame's only collective; returns the event between them."""
         e1 = torch.cuda.Event(enable_timing=True)
-        if steal:
-            image_t.zero_()
-            rd.TraceRaysSteal(plt, WIDTH, HEIGHT, frame_no[0], args.chunk)
-            frame_no[0] += 1
+        if world == 1:
+            rd.TraceRaysAsync(plt, WIDTH, HEIGHT)
             e1.record(stream)
-            mg.combine_sum(image_t, world, dist)
-        elif interleave:
-            image_t.zero_()
+        elif args.partition == "interleave":
             rd.TraceRaysInterleaved(plt, WIDTH, HEIGHT, rank, world, args.band)
             e1.record(stream)
-            mg.combine_sum(image_t, world, dist)
-        else:
-            rd.TraceRaysRange(plt, WIDTH, HEIGHT, first, count)
+            rd.FrameGather(plt, ds.rdImage, WIDTH, HEIGHT, 4, args.band)
+        elif args.partition == "units":
+            frame_no[0] += 1
+            owned = rd.TraceRaysUnits(plt, WIDTH, HEIGHT, units, frame_no[0])
             e1.record(stream)
-            mg.gather_rows(image_t, rank, world, WIDTH, HEIGHT, dist)
+            rd.FrameGatherUnits(plt, ds.rdImage, WIDTH, HEIGHT, 4, units, owned)
+        else:
+            rd.TraceRaysRange(plt, WIDTH, HEIGHT, firsts[rank], counts[rank])
+            e1.record(stream)
+            rd.FrameGatherRanges(plt, ds.rdImage, 4, firsts, counts)
         return e1
 
     def step(timed):
@@ -416,31 +545,52 @@ def main():
     frame_ms, kern_ms = float(t[0]), float(t[1])
 
     # ---- end to end through the public API with HOST buffers (sample1.cpp render loop :466-490):
-    # WriteBuffer(RTProp) from pinned memory, TraceRays (blocking), ReadBuffer(image) into pinned memory
+    # WriteBuffer(RTProp) from pinned memory, TraceRays (blocking), ReadBuffer(image) into pinned memory.
+    # Cache state: the device-timed loop above flushes L2 before every frame; this loop does not (a host program renders frame
+    # after frame), so e2e frames see whatever of the 56 MB scene the previous frame left in the 126 MB L2 -- labelled below.
     host_rt = torch.zeros(4, dtype=torch.int32).pin_memory()
-    host_img = torch.zeros(count * 4, dtype=torch.uint8).pin_memory()
     host_rt[1], host_rt[2] = 1, 1
+    host_full = torch.zeros(n * 4, dtype=torch.uint8).pin_memory()
 
-    def e2e_step():
+    def e2e_step(cold=False):
         rd.WriteBuffer(plt, ds.rdRTProp, 16, host_rt.data_ptr())
         with torch.cuda.stream(stream):
+            if cold:
+                flush.fill_(rank + 1)
             render_and_gather()
         if rank == 0:
-            rd.ReadBuffer(plt, ds.rdImage, n * 4 if world > 1 else count * 4, host_full.data_ptr(), 0)
+            rd.ReadBuffer(plt, ds.rdImage, n * 4, host_full.data_ptr(), 0)
         else:
             plt.sync()
-    host_full = torch.zeros(n * 4, dtype=torch.uint8).pin_memory()
+
+    def e2e_loop(cold):
+        for _ in range(3):
+            e2e_step(cold)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step(cold)
+        barrier()
+        ms = (time.perf_counter() - t0) * 1e3 / args.steps
+        tt = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt[0])
+
     if streamed:
         # same two API calls per frame; the bands of the frame travel to host_full while the later bands render
         rd.StreamBufferToHost(plt, ds.rdImage, host_full.data_ptr(), 4, args.readback_bands)
-    for _ in range(3):
-        e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(args.steps):
-        e2e_step()
-    barrier()
-    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    e2e_ms = e2e_loop(False)
+    # the same loop with the 256 MiB flush in front of every frame, minus the flush's own time: the cold-cache figure
+    with torch.cuda.stream(stream):
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        f0.record(stream)
+        for _ in range(5):
+            flush.fill_(7)
+        f1.record(stream)
+    torch.cuda.synchronize()
+    flush_ms = f0.elapsed_time(f1) / 5
+    e2e_cold_ms = e2e_loop(True) - flush_ms
     if streamed:
         rd.StreamBufferToHost(plt, None, None)
         with torch.cuda.stream(stream):   # the streamed frame must be the frame the plain path delivers
@@ -449,21 +599,21 @@ def main():
         rd.ReadBuffer(plt, ds.rdImage, n * 4, check.data_ptr(), 0)
         if not torch.equal(check, host_full):
             raise SystemExit("bench: streamed read-back delivered a different frame than TraceRays + ReadBuffer")
-    t = torch.tensor([e2e_ms], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t[0])
+    if plt.status() != (0, 0):
+        raise SystemExit("bench: device status flags raised %r" % (plt.status(),))
 
     multi = {}
-    if world > 1 and not args.no_extra:
+    if world > 1 and want:
         # frame ms of the path-traced configs across the ranks (the "frame ms at 1/2/4/8 B200" half of the metric)
         try:
-            multi["C3"] = multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world,
-                "C3: path.cl, 1080p 16 spp depth 5, blob-field n=2237", scenes.blob_field_scene(2237, WIDTH, HEIGHT), WIDTH, HEIGHT, 16, 5)
-            if args.extra == "all":
+            if "C3" in want:
+                multi["C3"] = multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world,
+                    "C3: path.cl, 1080p 16 spp depth 5, blob-field n=2237", scenes.blob_field_scene(2237, WIDTH, HEIGHT), WIDTH, HEIGHT, 16, 5,
+                    units_per_rank=args.units_per_rank)
+            if "C5" in want:
                 multi["C5"] = multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world,
                     "C5: path.cl, 3840x2160 64 spp depth 5, 5 instances of the n=2237 height-field (50 M triangles)",
-                    scenes.replicated_scene(2237, 5, 3840, 2160), 3840, 2160, 64, 5, frames=2)
+                    scenes.replicated_scene(2237, 5, 3840, 2160), 3840, 2160, 64, 5, frames=2, units_per_rank=args.units_per_rank)
         except Exception as e:
             multi["error"] = repr(e)[:300]
     if rank == 0:
@@ -477,53 +627,72 @@ def main():
         nodes_per_ray, tris_per_ray = c["nodes"] / c["rays"], c["tris"] / c["rays"]
         bytes_per_ray = nodes_per_ray * NODE_BYTES + tris_per_ray * TRI_BYTES + RAY_BYTES + HIT_BYTES
         peak, peak_kind = measured_peaks()
-        rays_per_launch = n // world if (steal or interleave) else count
+        rays_per_launch = n // world if world > 1 and args.partition != "static" else counts[0]
         achieved = rays_per_launch * bytes_per_ray / (kern_ms * 1e-3) / 1e9
+        ncu = (ncu_reference("C2") or {}) if world == 1 else {}
+        partition = ("single GPU" if world == 1 else
+                     "interleaved bands of %d 8x4-tile row(s), round robin over ranks + rd_frame_gather (one packed NCCL send per peer to rank 0)" % args.band
+                     if args.partition == "interleave" else
+                     "dynamic work units (%d, job-wide counter over CUDA IPC / NVLink) + rd_frame_gather_units" % units if args.partition == "units"
+                     else "contiguous 8x4-tile rows per GPU + rd_frame_gather_ranges (NCCL send/recv in place)")
         out = {
             "metric": "Mrays/s (primary closest-hit, 1080p)", "value": n / (frame_ms * 1e-3) / 1e6, "unit": "Mrays/s",
             "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": frame_ms,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "l2": "256 MiB flush between timed frames", "rays_per_step": n,
-                       "partition": ("single GPU" if world == 1 else
-                                     "interleaved bands of %d 8x4-tile row(s), round robin over ranks + NCCL sum-reduce to rank 0" % args.band if interleave else
-                                     "dynamic stealing of 8x4-tile chunks (IPC counter, system-scope atomics) + NCCL sum-reduce to rank 0" if steal
-                                     else "contiguous 8x4-tile rows per GPU, NCCL send/recv gather to rank 0"),
-                       "build_ms_incl_upload": build_ms, "build_ms_incl_upload_warm": build_warm_ms,
-                       "bvh": blas[0].stats(), "raygen": module.info()},
+            "config": {"workload": WORKLOAD, "l2": L2_NOTE, "rays_per_step": n, "partition": partition},
+            "details": {"build_ms_incl_upload": build_ms, "build_ms_incl_upload_warm": build_warm_ms, "bvh": blas[0].stats(),
+                        "raygen": module.info(), "node_bytes": NODE_BYTES},
             "clocks": clocks, "gpu_launches": launches,
             "e2e": {"value": n / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": 16,
-                    "d2h_bytes_per_step": n * 4 if world > 1 else count * 4, "ms_per_step": e2e_ms,
+                    "d2h_bytes_per_step": n * 4, "ms_per_step": e2e_ms,
+                    "cache_state": "frames back to back, no L2 flush (the render loop of samples/sample1.cpp:466-490)",
+                    "cold": {"value": n / (e2e_cold_ms * 1e-3) / 1e6, "ms_per_step": e2e_cold_ms,
+                             "cache_state": "256 MiB L2 flush before every frame, the flush's own %.3f ms subtracted" % flush_ms},
                     "readback": ("streamed in %d bands while the frame renders (rd_buffer_stream_to_host)" % args.readback_bands)
-                    if streamed else "ReadBuffer after the frame"},
+                    if streamed else "ReadBuffer after the frame (rank 0, after the gather)"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": NCU_DRAM_BYTES_PER_LAUNCH if world == 1 else None, "traffic_unit": "bytes per launch (ncu dram read + write)",
-                         "algorithmic_bytes_per_launch": rays_per_launch * bytes_per_ray, "peak_kind": peak_kind, "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",
+                         "traffic": ncu.get("dram_bytes_per_launch"), "traffic_source": ncu.get("source"),
+                         "traffic_unit": "bytes per launch (ncu dram read + write)",
+                         "algorithmic_bytes_per_launch": rays_per_launch * bytes_per_ray, "peak_kind": peak_kind,
+                         "kernel": "raygen (NVRTC, programs/primary.cl + inlined traversal)",
                          "kernel_ms": kern_ms, "bytes_per_ray": bytes_per_ray, "nodes_per_ray": nodes_per_ray,
                          "tris_per_ray": tris_per_ray},
         }
+        if ncu.get("warp_inst_per_launch"):
+            wi = ncu["warp_inst_per_launch"] / n
+            out["issue"] = {"warp_inst_per_ray": wi, "source": ncu.get("source"), "issue_peak_warp_inst_per_s": ISSUE_PEAK,
+                            "ceiling_mrays_at_full_issue": ISSUE_PEAK / wi / 1e6,
+                            "frac_of_issue_ceiling": (n / (kern_ms * 1e-3) / 1e6) / (ISSUE_PEAK / wi / 1e6)}
         if multi:
-            out["extra"] = multi
-        if world == 1 and not args.no_extra:
-            # the path-tracing half of the metric ("primary + 4-bounce path"): BASELINE configs[2] (and configs[3]
-            # with --extra all), wavefront mode against the inline raygen kernel of the same program
-            inflight = 1 << 25   # paths in flight per wavefront pass (all 16 samples of a 1080p frame); 1 = one sample per pass
-            modes = (("inline", 0, 1, inflight), ("wavefront_sorted", 1, 1, inflight), ("wavefront_unsorted", 1, 0, inflight),
-                     ("wavefront_sorted_one_sample_per_pass", 1, 1, 1))
+            out["extra"] = {k: v for k, v in multi.items() if v is not None}
+        if world == 1 and want:
+            for h in [tlas] + list(blas):   # the extras build their own scenes
+                h.free()
+            inflight = 1 << 25   # paths in flight per wavefront pass (all 16 samples of a 1080p frame)
+            modes = (("inline", 0, 1, inflight), ("wavefront_sorted", 1, 1, inflight), ("wavefront_unsorted", 1, 0, inflight))
             out["extra"] = {}
-            try:
-                out["extra"]["C3"] = extra_config(torch, pkg, plt, stream, flush,
+            todo = [
+                ("P10M", lambda: primary_config(torch, pkg, plt, stream, flush,
+                    "P10M: primary-ray closest-hit, 1920x1080, 1 spp, height-field n=2237 (10008338 triangles), programs/primary.cl", 2237, "P10M")),
+                ("C1", lambda: c1_config(torch, pkg, plt, stream, flush)),
+                ("C3", lambda: extra_config(torch, pkg, plt, stream, flush,
                     "C3: 4-bounce path tracing (depth 5) with any-hit shadow rays, 1080p 16 spp, blob-field n=2237, programs/path.cl",
-                    scenes.blob_field_scene(2237, WIDTH, HEIGHT), "path", 16, 5, modes)
-                if args.extra == "all":
-                    # single-GPU leg of BASELINE configs[4] (4K, 64 spp, 50 M triangles): the denominator of its 2/4/8-GPU frame ms
-                    out["extra"]["C5"] = extra_config(torch, pkg, plt, stream, flush,
-                        "C5: path.cl, 3840x2160 64 spp depth 5, 5 instances of the n=2237 height-field (50 M triangles)",
-                        scenes.replicated_scene(2237, 5, 3840, 2160), "path", 64, 5, (("wavefront_sorted", 1, 1, inflight),), 3840, 2160)
-                    out["extra"]["C4"] = extra_config(torch, pkg, plt, stream, flush,
-                        "C4: 64 SBT hit groups, 4096 instances, n=2240 height-field, 1080p 16 spp depth 5, programs/groups.cl",
-                        scenes.groups_scene(2240, 64, 64, WIDTH, HEIGHT), "groups", 16, 5, modes)
-            except Exception as e:   # the headline line must survive a failure here
-                out["extra"]["error"] = repr(e)[:300]
+                    scenes.blob_field_scene(2237, WIDTH, HEIGHT), "path", 16, 5, modes)),
+                ("C4", lambda: extra_config(torch, pkg, plt, stream, flush,
+                    "C4: 64 SBT hit groups, 4096 instances, n=2240 height-field, 1080p 16 spp depth 5, programs/groups.cl",
+                    scenes.groups_scene(2240, 64, 64, WIDTH, HEIGHT), "groups", 16, 5, modes[1:])),
+                # single-GPU leg of BASELINE configs[4] (4K, 64 spp, 50 M triangles): the denominator of its 2/4/8-GPU frame ms
+                ("C5", lambda: extra_config(torch, pkg, plt, stream, flush,
+                    "C5: path.cl, 3840x2160 64 spp depth 5, 5 instances of the n=2237 height-field (50 M triangles)",
+                    scenes.replicated_scene(2237, 5, 3840, 2160), "path", 64, 5, (("wavefront_sorted", 1, 1, inflight),), 3840, 2160)),
+            ]
+            for key, fn in todo:
+                if key not in want:
+                    continue
+                try:
+                    out["extra"][key] = fn()
+                except Exception as e:   # the headline line must survive a failure here
+                    out["extra"][key] = {"error": repr(e)[:300]}
         if world == 1 and not args.no_cpu_baseline:
             ref = entry.load_oracle()
             if ref.available():
@@ -533,6 +702,7 @@ def main():
                                        "sample": "oracle/_ref not built on this box"}
         emit(json.dumps(out))
     if world > 1:
+        rd.CommDestroy(plt)
         dist.destroy_process_group()
 
 

@@ -280,3 +280,28 @@ extern "C" int rd_frame_gather_units(rd_platform* p, rd_handle image, unsigned w
     if (seen != (units == 64u ? ~0ull : ((1ull << units) - 1ull))) { rd_set_error("rd_frame_gather_units: units missing from the frame (mask %llx)", seen); return RD_E_STATE; }
     return RD_OK;
 }
+
+// Test hook for the single-GPU suite: packs the bands rank `rank` of `world` owns out of `src` and scatters them into
+// `dst` -- what rank `rank` and rank 0 do on either side of the NCCL transfer of rd_frame_gather.
+extern "C" int rd_debug_band_roundtrip(rd_platform* p, rd_handle src, rd_handle dst, unsigned width, unsigned height, unsigned itemBytes,
+                                       unsigned bandTileRows, unsigned rank, unsigned world)
+{
+    RdHandleObj *s = rd_obj(src), *d = rd_obj(dst);
+    const size_t bytes = (size_t)width * height * itemBytes;
+    if (!p || !s || !d || !itemBytes || !bandTileRows || !world || rank >= world || (width % 8u) || (height % 4u) || s->size < bytes ||
+        d->size < bytes || (((size_t)4 * width * itemBytes) & 15u)) { rd_set_error("rd_debug_band_roundtrip: bad argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    RdBandPlan P; P.tileRows = height / 4u; P.bandRows = bandTileRows; P.world = world; P.rowBytes = 4u * width * itemBytes;
+    const unsigned rows = (unsigned)rd_owned_tile_rows(P, rank);
+    if (!rows) return RD_OK;
+    unsigned char* stage = 0;
+    RD_CUDA(cudaMalloc(&stage, (size_t)rows * P.rowBytes));
+    const unsigned blocks = (unsigned)p->smCount * 4u;
+    rd_k_band_copy<<<blocks, 256, 0, p->stream>>>((unsigned char*)s->dptr, stage, P, rank, rows, 1);
+    rd_k_band_copy<<<blocks, 256, 0, p->stream>>>((unsigned char*)d->dptr, stage, P, rank, rows, 0);
+    p->launches += 2;
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    RD_CUDA(cudaGetLastError());
+    cudaFree(stage);
+    return RD_OK;
+}

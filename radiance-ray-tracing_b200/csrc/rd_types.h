@@ -4,8 +4,8 @@
 // Replaces the reference's single-blob binary BVH (radiance/src/core.h:34-101,
 // radiance/shader/data.cl:4-99): 48-byte binary nodes + indexed 16-byte faces + 16-byte vertices
 // addressed by 32-bit byte offsets become
-//   * RdNode8   256 B 8-wide node, child boxes as floats (RD_NODE_F32; the 80-byte 8-bit quantised form is kept
-//                     behind RD_NODE_F32=0 for the A/B measurement)
+//   * RdNode8   80 B  8-wide node, child boxes quantised to 8 bits on a per-node power-of-two grid (a 256-byte form with
+//                     plain float boxes is kept behind RD_NODE_F32=1 for the A/B measurement)
 //   * RdTri     48 B  pre-gathered triangle (3 x float4, primID in v0.w), stored in leaf order
 //   * RdInstance 160 B world->object 3x4 (precomputed once, the reference inverts a 4x4 per ray per
 //                     instance visit: radiance/shader/radiance.cl:166-167), object->world 4x4, ids,
@@ -36,7 +36,11 @@ struct RD_ALIGN(16) RdU4 { rd_u32 x, y, z, w; };
 struct RD_ALIGN(16) RdF4 { float x, y, z, w; };
 
 #ifndef RD_NODE_F32
-#define RD_NODE_F32 1   // 1: 256-byte nodes with plain float child boxes (default); 0: 80-byte nodes, boxes quantised to 8 bits
+#define RD_NODE_F32 0   // 0: 80-byte nodes, child boxes quantised to 8 bits (default); 1: 256-byte nodes with plain float child boxes.
+                        // A/B on the B200 (profiles/README_r2.md): float boxes save the 48 conversions of a node test and cull
+                        // exactly, but move 3.2x the bytes -- C2 (1 M triangles, L2-resident) 4644 vs 4540 Mrays/s at 72 registers,
+                        // 10 M triangles 2812 vs 3000: the walk over a structure larger than L2 is bound by load latency as much
+                        // as by instruction issue, so the small node stays the default
 #endif
 
 #if RD_NODE_F32

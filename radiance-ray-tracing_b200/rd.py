@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
     "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
     "rd_comm_unique_id", "rd_comm_init", "rd_comm_adopt", "rd_comm_destroy", "rd_frame_gather", "rd_frame_gather_ranges",
-    "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline",
+    "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline", "rd_debug_band_roundtrip",
 ]
 
 
@@ -85,6 +85,7 @@ def lib():
             "rd_trace_rays_units": [vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.POINTER(C.c_uint64)],
             "rd_frame_gather_units": [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint64],
             "rd_wf_timeline": [vp, vp, vp, C.c_uint, C.POINTER(C.c_uint)],
+            "rd_debug_band_roundtrip": [vp, vp, vp] + [C.c_uint] * 6,
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],

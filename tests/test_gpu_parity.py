@@ -751,3 +751,81 @@ def test_async_entry_points_report_device_status(pkg, plt, monkeypatch):
     rd.BindDescriptorSet(plt, ds.descriptors)
     rd.TraceRays(plt, 0, 0, 0, 160, 96)
     plt.sync()
+
+
+def test_frame_gather_pack_unpack_and_work_units(pkg, plt):
+    """The C-ABI multi-GPU pieces that need no second GPU: (1) the pack / unpack kernels of rd_frame_gather move exactly the
+    bands of each rank (all ranks together rebuild the frame, RGBA8 and float scratch); (2) rd_trace_rays_units with a
+    private counter renders every unit once, inline and in wavefront mode, bit-identical to the plain frame; (3) a
+    one-rank communicator gathers trivially; (4) the wavefront stage timeline covers the frame."""
+    import ctypes as C
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 320, 240
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 2, 3, 0))
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    plain, plain_scr = ds.read_image(), ds.read_scratch()
+    for item, src in ((4, ds.rdImage), (16, ds.rdImageScratch)):
+        dst = rd.CreateBuffer(plt, w * h * item)
+        for world, band in ((2, 1), (8, 1), (3, 2), (4, 7)):
+            rd.WriteBuffer(plt, dst, w * h * item, np.zeros(w * h * item, np.uint8))
+            for r in range(world):
+                rd._check(rd.lib().rd_debug_band_roundtrip(plt.handle, src.handle, dst.handle, w, h, item, band, r, world))
+                if r == 0 and world > 1:
+                    part = np.zeros(w * h * item, np.uint8)
+                    rd.ReadBuffer(plt, dst, part.nbytes, part)
+                    rows = part.reshape(h, -1)
+                    mine = np.zeros(h, bool)
+                    for y0, ny in pkg.multigpu.interleaved_rows(0, world, h, band):
+                        mine[y0:y0 + ny] = True
+                    assert (rows[~mine] == 0).all()
+            out = np.zeros(w * h * item, np.uint8)
+            rd.ReadBuffer(plt, dst, out.nbytes, out)
+            ref_bytes = (plain if item == 4 else plain_scr).reshape(-1).view(np.uint8)
+            assert np.array_equal(out, ref_bytes), (item, world, band)
+        dst.free()
+    # dynamic work units (one rank takes them all)
+    for wf in (0, 1):
+        plt.set_option("wavefront", wf)
+        try:
+            for units, frame in ((1, 0), (7, 1), (60, 2), (64, 3)):
+                rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
+                ds.set_rtprop(0, 2, 3)
+                mask = rd.TraceRaysUnits(plt, w, h, units, frame)
+                assert mask == (1 << units) - 1
+                plt.sync()
+                img = ds.read_image()
+                if wf == 0:
+                    assert np.array_equal(img, plain), units
+                else:
+                    d = img[..., :3].astype(np.float64) - plain[..., :3].astype(np.float64)
+                    assert np.sqrt((d * d).mean()) <= 0.5, units
+        finally:
+            plt.set_option("wavefront", 0)
+    # stage timeline
+    plt.set_option("wavefront", 1)
+    plt.set_option("wf_timeline", 1)
+    try:
+        ds.set_rtprop(0, 2, 3)
+        rd.TraceRays(plt, 0, 0, 0, w, h)
+        tl = rd.WavefrontTimeline(plt)
+    finally:
+        plt.set_option("wavefront", 0)
+        plt.set_option("wf_timeline", 0)
+    names = [n for n, _ in tl]
+    assert names[0] == "generate" and names[-1] == "resolve" and names.count("shade") == 3 and names.count("trace") == 3
+    assert all(ms >= 0.0 for _, ms in tl) and sum(ms for _, ms in tl) > 0.0
+    # a communicator of one rank: gather is a no-op that succeeds (NCCL present on the GPU box)
+    uid = rd.CommUniqueId()
+    rd.CommInit(plt, 0, 1, uid)
+    try:
+        rd.FrameGather(plt, ds.rdImage, w, h, 4, 1)
+        rd.FrameGatherUnits(plt, ds.rdImage, w, h, 4, 8, 0xff)
+        with pytest.raises(rd.RadianceError):
+            rd.CommInit(plt, 0, 1, uid)
+    finally:
+        rd.CommDestroy(plt)
