@@ -792,7 +792,7 @@ def test_frame_gather_pack_unpack_and_work_units(pkg, plt):
     for wf in (0, 1):
         plt.set_option("wavefront", wf)
         try:
-            for units, frame in ((1, 0), (7, 1), (60, 2), (64, 3)):
+            for units, frame in ((1, 200 + 10 * wf), (7, 201 + 10 * wf), (60, 202 + 10 * wf), (64, 203 + 10 * wf)):   # counter slots no other test used
                 rd.WriteBuffer(plt, ds.rdImage, plain.nbytes, np.zeros_like(plain))
                 ds.set_rtprop(0, 2, 3)
                 mask = rd.TraceRaysUnits(plt, w, h, units, frame)
