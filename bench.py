@@ -318,6 +318,9 @@ def c1_config(torch, pkg, plt, stream, flush):
             "parity": "tests/test_gpu_c1.py compares this frame with the reference runtime (profiles/parity_r2.json)"}
 
 
+_UNIT_FRAME = [1000]
+
+
 def comm_setup(torch, dist, rd, plt, rank, world):
     """One NCCL communicator inside the library per rank (rd_comm_init): rank 0 creates the id, torch.distributed only
     carries its 128 bytes; the dynamic partition's counter handle travels the same way."""
@@ -352,7 +355,7 @@ def multi_gpu_path_config(torch, dist, pkg, plt, stream, rank, world, name, bund
     rd.BindPipeline(plt, pipe)
     rd.BindDescriptorSet(plt, ds.descriptors)
     units = min(64, world * units_per_rank)
-    frame_no = [1000]
+    frame_no = _UNIT_FRAME   # counter slots are consumed in order over the whole job (rd_trace_rays_units)
 
     def timed(render):
         ms = []

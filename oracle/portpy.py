@@ -32,6 +32,7 @@ def lib():
         L.rdo_tlas_build.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_size_t)]
         L.rdo_free.argtypes = [C.c_void_p]
         L.rdo_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int]
+        L.rdo_trace_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.rdo_pcg3d.argtypes = [C.c_void_p, C.c_void_p]
         L.rdo_inverse4x4.argtypes = [C.c_void_p, C.c_void_p]
         L.rdo_intersect_aabb.argtypes = [C.c_void_p] * 4
@@ -76,6 +77,16 @@ def trace(blob, rays, terminate_on_first_hit=False, nthreads=None):
     lib().rdo_trace(blob.ctypes.data, r.ctypes.data, r.shape[0], int(terminate_on_first_hit), out.ctypes.data,
                     nthreads or os.cpu_count() or 1)
     return out
+
+
+def trace_ex(blob, rays, terminate_on_first_hit=False, top_stack=8, nthreads=None):
+    """trace() with a top-level stack of `top_stack` entries (8 = the reference, radiance.cl:38). Returns (hits, overflow):
+    overflow[i] = 1 where the limit made the walk give up and report a miss (the reference does that at 4096 instances)."""
+    r = np.ascontiguousarray(rays, np.float32).reshape(-1, 8)
+    out, ovf = np.zeros(r.shape[0], HIT_DTYPE), np.zeros(r.shape[0], np.uint8)
+    lib().rdo_trace_ex(blob.ctypes.data, r.ctypes.data, r.shape[0], int(terminate_on_first_hit), out.ctypes.data,
+                       nthreads or os.cpu_count() or 1, int(top_stack), ovf.ctypes.data)
+    return out, ovf
 
 
 def pcg3d(v):

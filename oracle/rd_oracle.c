@@ -18,6 +18,7 @@ typedef struct { uint32_t i0, i1, i2, primID; } Face;
 typedef struct { float m[16]; uint32_t sbt, instanceID, customID, blasOffset; } Inst;
 enum { TYPE_INST = 1, TYPE_TRIG = 2, TYPE_TOP_AS = 1, TYPE_BOT_AS = 2 };
 #define TOP_STACK 8    /* radiance.cl:38 */
+#define TOP_STACK_MAX 256
 #define BOT_STACK 100  /* radiance.cl:39 */
 
 /* ---- radiance/shader/math.cl:10-23 ----------------------------------------------------------- */
@@ -116,7 +117,7 @@ int rdo_intersect_triangle(const float o[3], const float d[3], const float v[9],
 }
 
 /* ---- radiance/shader/radiance.cl:41-108 (intersectBot) ------------------------------------------ */
-typedef struct { rdo_hit* hit; float transform[16]; int terminate; int cont; } TraceState;
+typedef struct { rdo_hit* hit; float transform[16]; int terminate; int cont; int topStack; int overflow; } TraceState;
 
 static int intersect_bot(const char* as, const float o[3], const float d[3], float Tmin, float Tmax, TraceState* st)
 {
@@ -170,7 +171,7 @@ static int intersect_top(const char* as, const float o[3], const float d[3], flo
     const Node* nodes = (const Node*)(as + hdr->nodeByteOffset);
     const Inst* insts = (const Inst*)(as + hdr->a);
     int hasIntersected = 0;
-    uint32_t stack[TOP_STACK + 2];
+    uint32_t stack[TOP_STACK_MAX + 2];
     int sp = 0;
     stack[sp++] = 0;
     st->cont = 1;
@@ -180,7 +181,7 @@ static int intersect_top(const char* as, const float o[3], const float d[3], flo
             if (rdo_intersect_aabb(o, d, node->lo, node->hi)) {
                 stack[sp++] = node->u1;
                 stack[sp++] = node->u0;
-                if (sp > TOP_STACK) return 0;
+                if (sp > st->topStack) { st->overflow = 1; return 0; }   /* the reference prints and reports a miss */
             }
         } else if (node->u2 == TYPE_INST) {
             const uint32_t count = node->u0 & 0x7fffffffu;
@@ -202,7 +203,7 @@ static int intersect_top(const char* as, const float o[3], const float d[3], flo
     return hasIntersected;
 }
 
-typedef struct { const char* blob; const float* rays; size_t b, e; int terminate; rdo_hit* out; } Job;
+typedef struct { const char* blob; const float* rays; size_t b, e; int terminate; rdo_hit* out; int topStack; unsigned char* overflow; } Job;
 
 static void* trace_job(void* arg)
 {
@@ -213,17 +214,31 @@ static void* trace_job(void* arg)
         memset(&h, 0, sizeof(h));
         h.t = FLT_MAX;                                          /* radiance.cl:265 */
         TraceState st;
-        st.hit = &h; st.terminate = j->terminate; st.cont = 1;
+        st.hit = &h; st.terminate = j->terminate; st.cont = 1; st.topStack = j->topStack; st.overflow = 0;
         const float o[3] = {r[0], r[1], r[2]}, d[3] = {r[4], r[5], r[6]};
         h.hit = (uint32_t)intersect_top(j->blob, o, d, r[3], r[7], &st);
         if (!h.hit) { const uint32_t calls = h.anyhit_calls; memset(&h, 0, sizeof(h)); h.anyhit_calls = calls; }
         j->out[i] = h;
+        if (j->overflow) j->overflow[i] = (unsigned char)st.overflow;
     }
     return 0;
 }
 
+/* top_stack: entries of the top-level stack. TOP_STACK (8) is the reference (radiance.cl:38), whose walk gives up -- and reports a
+ * miss -- when an instance hierarchy needs more (4096 instances do); a larger value walks the same blob in the same order without
+ * that limit, and overflow[i] (optional) tells which rays the limit would have cut. */
+void rdo_trace_ex(const void* tlas_blob, const float* rays, size_t n, int terminate_on_first_hit, rdo_hit* out, int nthreads,
+                  int top_stack, unsigned char* overflow);
 void rdo_trace(const void* tlas_blob, const float* rays, size_t n, int terminate_on_first_hit, rdo_hit* out, int nthreads)
 {
+    rdo_trace_ex(tlas_blob, rays, n, terminate_on_first_hit, out, nthreads, TOP_STACK, 0);
+}
+
+void rdo_trace_ex(const void* tlas_blob, const float* rays, size_t n, int terminate_on_first_hit, rdo_hit* out, int nthreads,
+                  int top_stack, unsigned char* overflow)
+{
+    if (top_stack < 1) top_stack = 1;
+    if (top_stack > TOP_STACK_MAX) top_stack = TOP_STACK_MAX;
     if (nthreads < 1) nthreads = 1;
     if (nthreads > 256) nthreads = 256;
     if (n < 256) nthreads = 1;
@@ -234,6 +249,7 @@ void rdo_trace(const void* tlas_blob, const float* rays, size_t n, int terminate
     for (int t = 0; t < nthreads; ++t) {
         Job* j = &jobs[t];
         j->blob = (const char*)tlas_blob; j->rays = rays; j->terminate = terminate_on_first_hit; j->out = out;
+        j->topStack = top_stack; j->overflow = overflow;
         j->b = (size_t)t * chunk; j->e = j->b + chunk < n ? j->b + chunk : n;
         if (j->b >= j->e) break;
         if (nthreads == 1) { trace_job(j); return; }

@@ -29,6 +29,9 @@ int rdo_intersect_aabb(const float o[3], const float d[3], const float lo[3], co
 int rdo_intersect_triangle(const float o[3], const float d[3], const float v[9], float out[7]);
 /* radiance/shader/radiance.cl:41-192,254-275 over a top-level blob in the reference's byte layout
  * (radiance/src/core.h:34-101). rays: n x {o.xyz, Tmin, d.xyz, Tmax}. */
+/* as rdo_trace with a top-level stack of top_stack entries (8 = the reference); overflow[i] = 1 where the limit cut ray i */
+void rdo_trace_ex(const void* tlas_blob, const float* rays, size_t n, int terminate_on_first_hit, rdo_hit* out, int nthreads,
+                  int top_stack, unsigned char* overflow);
 void rdo_trace(const void* tlas_blob, const float* rays, size_t n, int terminate_on_first_hit, rdo_hit* out, int nthreads);
 
 /* Blob builders in the reference's layout (radiance/src/radiance.cpp:318-425) over a median-split

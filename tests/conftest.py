@@ -68,3 +68,45 @@ def parity_log():
     log = _ParityLog()
     yield log
     log.dump()
+
+
+# ---- reference structures of the 10 M-triangle configurations (tests/test_gpu_fullsize.py) -------------------------------
+# The reference's host builder is single-threaded and takes minutes at 10 M triangles (radiance/src/bvh.cpp:46-341). When the
+# full-size parity tests are part of the session the builds start in background threads as soon as collection is done, so
+# they overlap with the rest of the GPU suite (ctypes releases the GIL); the tests join them.
+_FULLSIZE = {}
+
+
+def fullsize_builds():
+    """{"height": future -> RefBlas of heightfield(2237), "patches": future -> [RefBlas] of the 4096 C4 patch meshes}."""
+    if _FULLSIZE:
+        return _FULLSIZE
+    from concurrent.futures import ThreadPoolExecutor
+    ref = entry.load_oracle()
+    scenes = entry.load_package().scenes
+    if not ref.available():
+        return _FULLSIZE
+    pool = ThreadPoolExecutor(max_workers=max(2, (os.cpu_count() or 2)))
+
+    def height():
+        v, t = scenes.heightfield(2237, 1)
+        return ref.RefBlas(v, t)
+
+    def patches():
+        b = scenes.groups_scene(2240, 64, 64, 1920, 1080)
+        futs = [pool.submit(ref.RefBlas, v, t) for (v, t) in b.meshes]
+        return b, futs
+    _FULLSIZE["height"] = pool.submit(height)
+    _FULLSIZE["patches"] = pool.submit(patches)
+    _FULLSIZE["pool"] = pool
+    return _FULLSIZE
+
+
+def pytest_collection_finish(session):
+    try:
+        import torch
+        gpu = torch.cuda.is_available()
+    except Exception:
+        gpu = False
+    if gpu and any("test_gpu_fullsize" in item.nodeid for item in session.items):
+        fullsize_builds()
