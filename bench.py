@@ -132,7 +132,7 @@ def reference_arm(args, rank, world):
     cores = os.cpu_count() or 1
     b = scenes.heightfield_scene(GRID_N, WIDTH, HEIGHT)
     t0 = time.time()
-    tl = scenes.build_reference_scene(ref, b)
+    tl = ref.build_scene(b)
     build_s = time.time() - t0
     n = WIDTH * HEIGHT
     scratch, image = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
@@ -163,7 +163,7 @@ def cpu_baseline_leg(pkg, ref, bundle):
     scenes = pkg.scenes
     cores = os.cpu_count() or 1
     t0 = time.time()
-    tl = scenes.build_reference_scene(ref, bundle)
+    tl = ref.build_scene(bundle)
     build_s = time.time() - t0
     n = WIDTH * HEIGHT
     host = [np.array(scenes.rtprop(0, 1, 1, 0)).reshape(1), np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8),

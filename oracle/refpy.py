@@ -117,6 +117,13 @@ class RefTlas:
         return out
 
 
+def build_scene(bundle):
+    """The scene of a SceneBundle (meshes + instance list) through the reference's own host builder:
+    RD::BuildAccelStruct per mesh, then over the instances (samples/sample1.cpp:363-443)."""
+    blas = [RefBlas(v, t) for (v, t) in bundle.meshes]
+    return RefTlas([(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in bundle.instances])
+
+
 def pcg3d(v):
     v = _u32(v).reshape(-1, 3)
     out = np.zeros(v.shape, np.float32)

@@ -279,6 +279,119 @@ struct RdTmp {   // scoped device scratch, stream-ordered: freed blocks go back 
     }
 };
 
+// ---- small inputs (<= RD_PLOC_SMALL_MAX primitives): the whole build without a host round trip ---------------------
+// A scene of many small meshes (C4: 4096 patch meshes of 2450 triangles) pays the general path's fixed costs per mesh:
+// ~35 scratch allocations, a host synchronisation per collapse level, per sort and per clustering step, synchronous
+// cudaMalloc / cudaFree of the results -- 0.77 ms per mesh, 3.1 s for the scene. Here: ONE scratch allocation, eight
+// launches (every multi-round step runs its rounds inside one block), ONE synchronisation to learn the node count.
+__global__ void rd_k_small_init(unsigned* bounds, rd_u32* counters)
+{
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;
+    else if (threadIdx.x < 8) bounds[threadIdx.x] = 0u;
+    if (threadIdx.x == 0) { counters[0] = 1u; counters[1] = 0u; counters[2] = 0u; counters[3] = 0u; }
+}
+
+// the one-block sort leaves its result on side *where; the build wants it in (keysB, valsB)
+__global__ void rd_k_small_settle(const rd_u32* where, const rd_u64* keysA, const rd_u32* valsA, rd_u64* keysB, rd_u32* valsB, rd_u32 n)
+{
+    if (*where != 0u) return;
+    for (rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) { keysB[i] = keysA[i]; valsB[i] = valsA[i]; }
+}
+
+// all levels of the wide-node collapse in one block; summary = { nodes, leaf records, levels, non-finite boxes, root lo.xyz, root hi.xyz }
+__global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollapseOut O, RdCollapseItem* itemsA, RdCollapseItem* itemsB,
+                                                          RdCollapseItem rootItem, const unsigned* bounds, rd_u32* summary)
+{
+    __shared__ rd_u32 sCount;
+    RdCollapseItem* cur = itemsA;
+    if (threadIdx.x == 0) { itemsA[0] = rootItem; sCount = 1u; }
+    O.next = itemsB;
+    __syncthreads();
+    rd_u32 levels = 0;
+    for (;;) {
+        const rd_u32 count = sCount;
+        if (!count || levels > 200u) break;
+        __syncthreads();
+        if (threadIdx.x == 0) O.counters[2] = 0u;
+        __syncthreads();
+        for (rd_u32 i = threadIdx.x; i < count; i += blockDim.x) rd_collapse_item(T, O, cur[i]);
+        __syncthreads();
+        if (threadIdx.x == 0) sCount = O.counters[2];
+        RdCollapseItem* t = cur; cur = O.next; O.next = t;
+        ++levels;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const rd_u32 rootSlot = 0u;   // inner root = slot 0; single leaf = slot n - 1 = 0
+        summary[0] = O.counters[0]; summary[1] = O.counters[1]; summary[2] = levels; summary[3] = bounds[6];
+        summary[4] = RD_F2U(T.lo[rootSlot].x); summary[5] = RD_F2U(T.lo[rootSlot].y); summary[6] = RD_F2U(T.lo[rootSlot].z);
+        summary[7] = RD_F2U(T.hi[rootSlot].x); summary[8] = RD_F2U(T.hi[rootSlot].y); summary[9] = RD_F2U(T.hi[rootSlot].z);
+    }
+}
+
+static int rd_build_wide_bvh_small(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out)
+{
+    cudaStream_t st = p->stream;
+    const rd_u32 ni = n > 1 ? n - 1 : 1;
+    // one scratch block, carved
+    size_t off = 0;
+    auto carve = [&off](size_t bytes) { const size_t at = off; off += (bytes + 255u) & ~(size_t)255u; return at; };
+    const size_t oBounds = carve(8 * 4), oCounters = carve(4 * 4), oSummary = carve(16 * 4), oWhere = carve(4);
+    const size_t oKeysA = carve((size_t)n * 8), oKeysB = carve((size_t)n * 8), oValsA = carve((size_t)n * 4), oValsB = carve((size_t)n * 4);
+    const size_t oLeft = carve((size_t)ni * 4), oRight = carve((size_t)ni * 4), oFirst = carve((size_t)ni * 4), oLast = carve((size_t)ni * 4);
+    const size_t oParent = carve(2 * (size_t)n * 4), oCount = carve((size_t)ni * 4);
+    const size_t oLo = carve(2 * (size_t)n * 16), oHi = carve(2 * (size_t)n * 16), oCost = carve(8 * (size_t)ni * 4), oDec = carve(8 * (size_t)ni);
+    const size_t oARef = carve((size_t)n * 4), oALo = carve((size_t)n * 16), oAHi = carve((size_t)n * 16);
+    const size_t oBRef = carve((size_t)n * 4), oBLo = carve((size_t)n * 16), oBHi = carve((size_t)n * 16), oNearest = carve((size_t)n * 4);
+    const size_t oWide = carve(((size_t)n + 1) * sizeof(RdNode8)), oItemsA = carve(((size_t)n + 1) * sizeof(RdCollapseItem)),
+                 oItemsB = carve(((size_t)n + 1) * sizeof(RdCollapseItem));
+    RdTmp tmp(st);
+    char* base;
+    RD_CUDA(tmp.alloc(&base, off));
+    unsigned* dbounds = (unsigned*)(base + oBounds);
+    rd_u32* counters = (rd_u32*)(base + oCounters); rd_u32* summary = (rd_u32*)(base + oSummary); rd_u32* where = (rd_u32*)(base + oWhere);
+    rd_u64 *keysA = (rd_u64*)(base + oKeysA), *keysB = (rd_u64*)(base + oKeysB);
+    rd_u32 *valsA = (rd_u32*)(base + oValsA), *valsB = (rd_u32*)(base + oValsB);
+    RdBinTree T;
+    T.n = n; T.keys = keysB; T.prim = valsB;
+    T.left = (rd_u32*)(base + oLeft); T.right = (rd_u32*)(base + oRight); T.first = (rd_u32*)(base + oFirst); T.last = (rd_u32*)(base + oLast);
+    T.parent = (rd_u32*)(base + oParent); T.arrive = 0; T.count = (rd_u32*)(base + oCount);
+    T.lo = (RdF4*)(base + oLo); T.hi = (RdF4*)(base + oHi); T.cost = (float*)(base + oCost); T.dec = (rd_u8*)(base + oDec);
+    RdPlocSide A, B;
+    A.ref = (rd_u32*)(base + oARef); A.lo = (RdF4*)(base + oALo); A.hi = (RdF4*)(base + oAHi);
+    B.ref = (rd_u32*)(base + oBRef); B.lo = (RdF4*)(base + oBLo); B.hi = (RdF4*)(base + oBHi);
+    RD_CUDA(cudaMallocAsync(&out->leafPrim, (size_t)n * sizeof(rd_u32), st));
+    int radius = 32;
+    if (const char* e = getenv("RD_PLOC_RADIUS")) { radius = atoi(e); if (radius < 1) radius = 1; }
+    rd_k_small_init<<<1, 32, 0, st>>>(dbounds, counters);
+    rd_k_centroid_bounds<<<rd_grid(n), RD_BT, 0, st>>>(dlo, dhi, n, dbounds);
+    rd_k_morton<<<rd_grid(n), RD_BT, 0, st>>>(dlo, dhi, n, dbounds, keysA, valsA);
+    if (n > 1) {
+        rd_k_sort_small<<<1, 1024, 0, st>>>(keysA, valsA, keysB, valsB, n, 8, where);
+        rd_k_small_settle<<<rd_grid(n), RD_BT, 0, st>>>(where, keysA, valsA, keysB, valsB, n);
+    } else {
+        RD_CUDA(cudaMemcpyAsync(keysB, keysA, 8, cudaMemcpyDeviceToDevice, st));
+        RD_CUDA(cudaMemcpyAsync(valsB, valsA, 4, cudaMemcpyDeviceToDevice, st));
+    }
+    rd_k_leaf_boxes<<<rd_grid(n), RD_BT, 0, st>>>(T, dlo, dhi);
+    if (n > 1) rd_k_ploc_small<<<1, 1024, 0, st>>>(T, A, B, (rd_u32*)(base + oNearest), radius);
+    RdCollapseItem rootItem; rootItem.wide = 0; rootItem.bin = (n == 1) ? (RD_BIN_LEAF | 0u) : 0u;
+    RdCollapseOut O; O.nodes = (RdNode8*)(base + oWide); O.leafPrim = out->leafPrim; O.counters = counters; O.next = 0;
+    rd_k_collapse_small<<<1, 256, 0, st>>>(T, O, (RdCollapseItem*)(base + oItemsA), (RdCollapseItem*)(base + oItemsB), rootItem, dbounds, summary);
+    p->launches += n > 1 ? 8 : 5;
+    rd_u32 hs[10];
+    RD_CUDA(cudaMemcpyAsync(hs, summary, sizeof(hs), cudaMemcpyDeviceToHost, st));
+    RD_CUDA(cudaStreamSynchronize(st));
+    RD_CUDA(cudaGetLastError());
+    if (hs[3]) { cudaFreeAsync(out->leafPrim, st); out->leafPrim = 0; rd_set_error("BuildAccelStruct: %u primitive(s) with NaN / Inf coordinates", hs[3]); return RD_E_ARG; }
+    if (hs[1] != n || hs[2] > 200u) { cudaFreeAsync(out->leafPrim, st); out->leafPrim = 0; rd_set_error("rd_build_wide_bvh: %u leaf records for %u primitives", hs[1], n); return RD_E_CUDA; }
+    out->nodeCount = hs[0]; out->levels = hs[2];
+    RD_CUDA(cudaMallocAsync(&out->nodes, (size_t)out->nodeCount * sizeof(RdNode8), st));
+    RD_CUDA(cudaMemcpyAsync(out->nodes, O.nodes, (size_t)out->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, st));
+    for (int k = 0; k < 3; ++k) { memcpy(&out->lo[k], &hs[4 + k], 4); memcpy(&out->hi[k], &hs[7 + k], 4); }
+    return RD_OK;
+}
+
 int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out)
 {
     cudaStream_t st = p->stream;
@@ -289,13 +402,15 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
 #if !RD_NODE_F32
         e.w[0].w = 1u | (1u << 8) | (1u << 16);
 #endif
-        RD_CUDA(cudaMalloc(&out->nodes, sizeof(RdNode8)));
+        RD_CUDA(cudaMallocAsync(&out->nodes, sizeof(RdNode8), st));
         RD_CUDA(cudaMemcpyAsync(out->nodes, &e, sizeof(e), cudaMemcpyHostToDevice, st));
-        RD_CUDA(cudaMalloc(&out->leafPrim, 16));
+        RD_CUDA(cudaMallocAsync(&out->leafPrim, 16, st));
         RD_CUDA(cudaStreamSynchronize(st));
         out->nodeCount = 1;
         return RD_OK;
     }
+    if (n <= RD_PLOC_SMALL_MAX && n <= RD_SORT_SMALL_MAX && !getenv("RD_BUILD_GREEDY") && !getenv("RD_BUILD_LBVH") && !getenv("RD_BUILD_GENERAL"))
+        return rd_build_wide_bvh_small(p, dlo, dhi, n, out);
     RdTmp tmp(st);
     unsigned* dbounds; rd_u64 *keysA, *keysB; rd_u32 *valsA, *valsB;
     RD_CUDA(tmp.alloc(&dbounds, 8));
@@ -383,7 +498,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     (void)maxNodes;
     RD_CUDA(tmp.alloc(&counters, 4));
     RD_CUDA(tmp.alloc(&itemsA, (size_t)n + 1)); RD_CUDA(tmp.alloc(&itemsB, (size_t)n + 1));
-    RD_CUDA(cudaMalloc(&out->leafPrim, (size_t)n * sizeof(rd_u32)));
+    RD_CUDA(cudaMallocAsync(&out->leafPrim, (size_t)n * sizeof(rd_u32), st));
     const rd_u32 c0[4] = {1u, 0u, 0u, 0u};
     RD_CUDA(cudaMemcpyAsync(counters, c0, sizeof(c0), cudaMemcpyHostToDevice, st));
     RD_CUDA(cudaMemcpyAsync(itemsA, &rootItem, sizeof(rootItem), cudaMemcpyHostToDevice, st));
@@ -403,7 +518,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     }
     out->nodeCount = hc[0]; out->levels = levels;
     if (hc[1] != n) { rd_set_error("rd_build_wide_bvh: %u leaf records for %u primitives", hc[1], n); return RD_E_CUDA; }
-    RD_CUDA(cudaMalloc(&out->nodes, (size_t)out->nodeCount * sizeof(RdNode8)));
+    RD_CUDA(cudaMallocAsync(&out->nodes, (size_t)out->nodeCount * sizeof(RdNode8), st));
     RD_CUDA(cudaMemcpyAsync(out->nodes, wide, (size_t)out->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, st));
     RdF4 rl, rh;
     const rd_u32 rootSlot = (n == 1) ? 0u : 0u;   // inner root = slot 0; single leaf = slot n-1 = 0
@@ -431,11 +546,10 @@ extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigne
     rd_blas* b = new rd_blas();
     b->nodes = r.nodes; b->nodeCount = r.nodeCount; b->triCount = nt; b->levels = r.levels;
     memcpy(b->lo, r.lo, 12); memcpy(b->hi, r.hi, 12);
-    RD_CUDA(cudaMalloc(&b->tris, nt ? (size_t)nt * sizeof(RdTri) : 48));
+    RD_CUDA(cudaMallocAsync(&b->tris, nt ? (size_t)nt * sizeof(RdTri) : 48, st));
     if (nt) { rd_k_gather_tris<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, r.leafPrim, b->tris, nt); p->launches += 1; }
-    RD_CUDA(cudaStreamSynchronize(st));
     RD_CUDA(cudaGetLastError());
-    cudaFree(r.leafPrim);
+    RD_CUDA(cudaFreeAsync(r.leafPrim, st));   // everything that follows on the platform stream is ordered behind the build
     (void)nv;
     *out = b;
     return RD_OK;

@@ -38,7 +38,7 @@ __global__ void __launch_bounds__(128, 7) rd_k_wf_trace(const RdScene* __restric
                 const RdInstance* I = scene->instances + h.inst;
                 row = I->sbtOffset + (unsigned)wf.sbtRecordOffset; mat = I->customID & 3u;
             }
-            wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
+            wf.keys[j] = ((row & 255u) << 2) | mat;   // rows beyond 255 share bins modulo 256: still few groups per bin
         }
     }
 }
@@ -61,7 +61,7 @@ __device__ __forceinline__ void rd_wf_store_hit(const RdScene* scene, const RdWf
         const RdInstance* I = scene->instances + h.inst;
         row = I->sbtOffset + (unsigned)wf.sbtRecordOffset; mat = I->customID & 3u;
     }
-    wf.keys[j] = (row > 255u ? 255u : row) * 4u + mat;
+    wf.keys[j] = ((row & 255u) << 2) | mat;   // rows beyond 255 share bins modulo 256: still few groups per bin
 }
 
 template <int MINB>

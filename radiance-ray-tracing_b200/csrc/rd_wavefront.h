@@ -15,7 +15,7 @@
 #define RD_WAVEFRONT_H
 #include "rd_types.h"
 
-#define RD_WF_KEY_BINS 1024u      // (hit group row, capped at 255) * 4 + (instanceCustomIndex & 3)
+#define RD_WF_KEY_BINS 1024u      // (hit group row mod 256) * 4 + (instanceCustomIndex & 3): a coherence key, not an identity
 
 struct RD_ALIGN(16) RdWfState {
     // per path slot

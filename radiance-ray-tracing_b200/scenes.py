@@ -247,7 +247,7 @@ def groups_scene(n=2240, side=64, groups=64, width=1920, height=1080, seed=1):
     """C4: the n x n height-field cut into side x side spatial patches, one instance per patch,
     SBTOffset = hit group of the patch in a checkerboard (neighbouring patches never share a group),
     customInstanceID = material = group. n=2240, side=64: 4096 instances, 10 035 200 triangles."""
-    assert n % side == 0 and groups <= 64
+    assert n % side == 0
     c = n // side
     v, _ = heightfield(n, seed)
     grid = v.reshape(n + 1, n + 1, 3)
@@ -338,12 +338,6 @@ def build_scene(plt, bundle):
     blas = [rd.BuildAccelStruct(plt, rd.Mesh(v, t)) for (v, t) in bundle.meshes]
     inst = [rd.Instance(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in bundle.instances]
     return rd.BuildAccelStruct(plt, inst), blas
-
-
-def build_reference_scene(ref, bundle):
-    """Same scene through the reference's own host builder (oracle/_ref)."""
-    blas = [ref.RefBlas(v, t) for (v, t) in bundle.meshes]
-    return ref.RefTlas([(m, sbt, custom, blas[mi]) for (mi, m, sbt, custom) in bundle.instances])
 
 
 class DeviceScene:

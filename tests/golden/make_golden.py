@@ -56,7 +56,7 @@ np.savez(os.path.join(out, "triangle.npz"), origin=o, direction=d, triangle=tri,
 
 # 4. traceRay hit records (radiance.cl:254-275) on the two small parity scenes
 def record(name, bundle, rays):
-    tl = scenes.build_reference_scene(ref, bundle)
+    tl = ref.build_scene(bundle)
     closest = tl.trace(rays)
     first = tl.trace(rays, terminate_on_first_hit=True)
     np.savez_compressed(os.path.join(out, name), rays=rays, hit=closest["hit"].astype(np.uint8), t=closest["t"],
@@ -76,7 +76,7 @@ w, h = 96, 72
 cam = np.array(b.camera).reshape(()).copy()
 cam["widthPixel"], cam["heightPixel"] = w, h
 scratch, image = np.zeros(w * h * 4, np.float32), np.zeros(w * h * 4, np.uint8)
-tl = scenes.build_reference_scene(ref, b)
+tl = ref.build_scene(b)
 ref.raygen("primary", [np.array(scenes.rtprop(0, 2, 1, 0)).reshape(1), scratch, image, cam.reshape(1),
                        np.array(b.scene).reshape(1), b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData,
                        b.materials, None, 0, tl.blob], w * h)

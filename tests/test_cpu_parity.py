@@ -78,7 +78,7 @@ def test_oracle_triangle_matches_golden(ref):
 def test_oracle_traceray_matches_golden(ref, pkg):
     scenes = pkg.scenes
     g = np.load(os.path.join(GOLD, "cornell_hits.npz"))
-    out = scenes.build_reference_scene(ref, cornell(scenes)).trace(g["rays"])
+    out = ref.build_scene(cornell(scenes)).trace(g["rays"])
     assert np.array_equal(out["hit"], g["hit"]) and np.array_equal(out["prim"], g["prim"])
     assert np.array_equal(out["t"], g["t"])
 

@@ -61,7 +61,7 @@ def reference_frame(ref, scenes, b, rt, first=0, count=None):
     cam["widthPixel"], cam["heightPixel"] = W, H
     n = W * H
     scratch, image = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
-    tl = scenes.build_reference_scene(ref, b)
+    tl = ref.build_scene(b)
     args = [np.array(rt).reshape(1), scratch, image, cam.reshape(1), np.array(b.scene).reshape(1), b.meshInfoData,
             b.vertexData, b.indexData, b.uvData, b.normalData, b.materials, None, 0, tl.blob]
     ref.raygen("shader", args, n, first, count)
@@ -156,7 +156,7 @@ def test_c1_debug_view_and_progressive_accumulation(pkg, plt, ref, c1_sources, p
     cam["widthPixel"], cam["heightPixel"] = W, H
     n = W * H
     rscratch, rimage = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
-    tl = scenes.build_reference_scene(ref, b)
+    tl = ref.build_scene(b)
     for total in (0, 4):
         args = [np.array(scenes.rtprop(total, 4, 8, 0)).reshape(1), rscratch, rimage, cam.reshape(1), np.array(b.scene).reshape(1),
                 b.meshInfoData, b.vertexData, b.indexData, b.uvData, b.normalData, b.materials, None, 0, tl.blob]

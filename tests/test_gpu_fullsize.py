@@ -87,12 +87,16 @@ def test_c3_full_size_primary_bounce_and_shadow_rays(pkg, plt, ref, builds, pari
     tl = ref.RefTlas([(m, sbt, custom, rb[mi]) for (mi, m, sbt, custom) in b.instances])
     rays = pick(scenes.pinhole_rays(b.camera, jitter=(0.37, 0.61)), NRAYS // 2, 11)
     hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
-    assert compare_hits(hitA, hitB, tl.trace(rays), log=parity_log, name="C3_full_size_primary_rays") > NRAYS // 4
+    # The sphere instances are scaled by 0.05..0.07 and rotated: the reference inverts the instance matrix in float for every
+    # ray (radiance.cl:166-167), this tracer once in double -- the instance-local rays differ in the last bits, and with
+    # them the barycentrics of grazing hits (measured 6e-4). north_star sets bars on IDs and t; the own bar on barycentrics
+    # is 1e-4 on identity instances and 2e-3 here.
+    assert compare_hits(hitA, hitB, tl.trace(rays), log=parity_log, name="C3_full_size_primary_rays", bary_tol=2e-3) > NRAYS // 4
     assert len(np.unique(hitB[hitA["t"] < 3e38])) == 4          # the three sphere instances are in view as well
     bounce, shadow = secondary_rays(b, rays, hitA, hitB, 12)
     bounce, shadow = bounce[: NRAYS // 4], shadow[: NRAYS // 4]
     hA, hB = rd.trace_host_rays(plt, tlas, bounce)
-    assert compare_hits(hA, hB, tl.trace(bounce), log=parity_log, name="C3_full_size_bounce_rays") > 1000
+    assert compare_hits(hA, hB, tl.trace(bounce), log=parity_log, name="C3_full_size_bounce_rays", bary_tol=2e-3) > 1000
     # shadow rays: any-hit termination, only occlusion is defined (radiance.cl:93-101, shader.cl:567-572)
     occ, _ = rd.trace_host_rays(plt, tlas, shadow, rd.TRACE_TERMINATE_ON_FIRST_HIT)
     exp = tl.trace(shadow, terminate_on_first_hit=True)

@@ -15,7 +15,7 @@ def reference_sequence(ref, scenes, b, w, h, steps):
     cam["widthPixel"], cam["heightPixel"] = w, h
     n = w * h
     scratch, image = np.zeros(n * 4, np.float32), np.zeros(n * 4, np.uint8)
-    tl = scenes.build_reference_scene(ref, b)
+    tl = ref.build_scene(b)
     rt = np.array(scenes.rtprop(0, 2, 3, 0)).reshape(1).copy()
     out = []
     for edit in steps:

@@ -66,7 +66,7 @@ def test_port_walks_the_reference_blob_identically(port, pkg, ref):
     """Same topology (the reference's own blob) -> the port must reproduce every field bit for bit."""
     scenes = pkg.scenes
     b = cornell(scenes)
-    tl = scenes.build_reference_scene(ref, b)
+    tl = ref.build_scene(b)
     rays = scenes.pinhole_rays(b.camera, stride=8, jitter=(0.11, 0.93))
     exp = tl.trace(rays)
     out = port.trace(tl.blob, rays)
