@@ -161,6 +161,8 @@ int rd_trace_rays_interleaved(rd_platform* p, unsigned width, unsigned height, u
  * rd_steal_owned: the chunk ids this rank rendered in its last frame. */
 int rd_steal_counter_export(rd_platform* p, unsigned char handle[64]);
 int rd_steal_counter_import(rd_platform* p, const unsigned char handle[64]);
+/* ranks that are host threads of ONE process: share the owner platform's counters through peer access instead of IPC */
+int rd_steal_counter_adopt(rd_platform* p, rd_platform* owner);
 int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned height, unsigned frame, unsigned chunkItems);
 int rd_steal_owned(rd_platform* p, unsigned* ids, unsigned capacity, unsigned* count);
 

@@ -932,6 +932,22 @@ extern "C" int rd_steal_counter_import(rd_platform* p, const unsigned char handl
     return RD_OK;
 }
 
+// Ranks that are host THREADS of one process (one platform per GPU) cannot open their own process's IPC handle; they
+// share the owner's counter array directly: peer access over NVLink, the same system-scope atomics.
+extern "C" int rd_steal_counter_adopt(rd_platform* p, rd_platform* owner)
+{
+    if (!p || !owner || p == owner) { rd_set_error("rd_steal_counter_adopt: bad argument"); return RD_E_ARG; }
+    if (!owner->stealCounters) { rd_set_error("rd_steal_counter_adopt: the owner has not exported its counters (rd_steal_counter_export)"); return RD_E_STATE; }
+    RD_CUDA(cudaSetDevice(p->device));
+    if (p->device != owner->device) {
+        cudaError_t e = cudaDeviceEnablePeerAccess(owner->device, 0);
+        if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        else if (e != cudaSuccess) { rd_set_error("rd_steal_counter_adopt: no peer access from device %d to %d (%s)", p->device, owner->device, cudaGetErrorString(e)); return RD_E_CUDA; }
+    }
+    p->stealCounters = owner->stealCounters; p->stealSlots = owner->stealSlots; p->stealImported = 1;
+    return RD_OK;
+}
+
 // RD::TraceRays with chunk stealing: every rank calls it with the same width, height, frame and chunkItems;
 // each work-item of the NDRange is rendered by exactly one rank. Asynchronous on the platform stream.
 extern "C" int rd_trace_rays_steal(rd_platform* p, unsigned width, unsigned height, unsigned frame, unsigned chunkItems)

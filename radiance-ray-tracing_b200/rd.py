@@ -27,7 +27,7 @@ ABI_SYMBOLS = [
     "rd_pipeline_bind", "rd_descriptors_bind", "rd_trace_rays", "rd_trace_rays_async", "rd_trace_rays_range", "rd_trace_ray_list",
     "rd_trace_counters", "rd_generate_primary_rays", "rd_set_option", "rd_launch_count", "rd_ray_count",
     "rd_tlas_load", "rd_tlas_load_memory", "rd_tlas_save", "rd_tlas_save_memory", "rd_free_host",
-    "rd_steal_counter_export", "rd_steal_counter_import", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
+    "rd_steal_counter_export", "rd_steal_counter_import", "rd_steal_counter_adopt", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
     "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
     "rd_comm_unique_id", "rd_comm_init", "rd_comm_adopt", "rd_comm_destroy", "rd_frame_gather", "rd_frame_gather_ranges",
     "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline", "rd_debug_band_roundtrip",

@@ -160,3 +160,17 @@ def test_cpp_scene_builder_and_render_loop_match_python(pkg, plt, tmp_path):
     assert img_cpp[..., :3].std() > 20
     d = img_cpp[..., :3].astype(np.float64) - img_py[..., :3].astype(np.float64)
     assert np.sqrt((d * d).mean()) <= 0.25 and (np.abs(d).max(axis=-1) > 2).mean() < 1e-3   # normals differ by float rounding only
+
+
+@pytest.mark.gpu
+def test_cpp_multigpu_host_through_the_c_abi():
+    """tests/cpp/sample_multigpu.cpp: one host thread per visible GPU, rd_comm_init + rd_trace_rays_interleaved +
+    rd_frame_gather and the dynamic rd_trace_rays_units + rd_frame_gather_units, all through include/radiance_b200.h.
+    The program itself checks that both gathered frames equal the frame rank 0 renders alone."""
+    import torch
+    exe = build_sample("sample_multigpu")
+    gpus = max(1, torch.cuda.device_count())
+    r = subprocess.run([exe, os.path.join(PROG, "path.cl"), os.path.join(PROG, "path_sbt.json"), str(gpus), "320", "240"],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout
+    assert "static partition identical, dynamic partition identical" in r.stdout
