@@ -329,9 +329,11 @@ __global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollap
     }
 }
 
-static int rd_build_wide_bvh_small(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out)
+// deferredSummary != 0: nothing waits for the device -- the nodes go straight into an allocation of the worst-case size
+// (n + 1) and the summary lands in host-mapped memory, to be read by rd_blas_resolve once the build's event has fired.
+static int rd_build_wide_bvh_small(rd_platform* p, cudaStream_t st, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out,
+                                   rd_u32* deferredSummary = 0)
 {
-    cudaStream_t st = p->stream;
     const rd_u32 ni = n > 1 ? n - 1 : 1;
     // one scratch block, carved
     size_t off = 0;
@@ -343,7 +345,7 @@ static int rd_build_wide_bvh_small(rd_platform* p, const RdF4* dlo, const RdF4* 
     const size_t oLo = carve(2 * (size_t)n * 16), oHi = carve(2 * (size_t)n * 16), oCost = carve(8 * (size_t)ni * 4), oDec = carve(8 * (size_t)ni);
     const size_t oARef = carve((size_t)n * 4), oALo = carve((size_t)n * 16), oAHi = carve((size_t)n * 16);
     const size_t oBRef = carve((size_t)n * 4), oBLo = carve((size_t)n * 16), oBHi = carve((size_t)n * 16), oNearest = carve((size_t)n * 4);
-    const size_t oWide = carve(((size_t)n + 1) * sizeof(RdNode8)), oItemsA = carve(((size_t)n + 1) * sizeof(RdCollapseItem)),
+    const size_t oWide = carve(deferredSummary ? 16 : ((size_t)n + 1) * sizeof(RdNode8)), oItemsA = carve(((size_t)n + 1) * sizeof(RdCollapseItem)),
                  oItemsB = carve(((size_t)n + 1) * sizeof(RdCollapseItem));
     RdTmp tmp(st);
     char* base;
@@ -377,8 +379,13 @@ static int rd_build_wide_bvh_small(rd_platform* p, const RdF4* dlo, const RdF4* 
     if (n > 1) rd_k_ploc_small<<<1, 1024, 0, st>>>(T, A, B, (rd_u32*)(base + oNearest), radius);
     RdCollapseItem rootItem; rootItem.wide = 0; rootItem.bin = (n == 1) ? (RD_BIN_LEAF | 0u) : 0u;
     RdCollapseOut O; O.nodes = (RdNode8*)(base + oWide); O.leafPrim = out->leafPrim; O.counters = counters; O.next = 0;
+    if (deferredSummary) {
+        RD_CUDA(cudaMallocAsync(&out->nodes, ((size_t)n + 1) * sizeof(RdNode8), st));
+        O.nodes = out->nodes; summary = deferredSummary;
+    }
     rd_k_collapse_small<<<1, 256, 0, st>>>(T, O, (RdCollapseItem*)(base + oItemsA), (RdCollapseItem*)(base + oItemsB), rootItem, dbounds, summary);
     p->launches += n > 1 ? 8 : 5;
+    if (deferredSummary) { RD_CUDA(cudaGetLastError()); out->nodeCount = 0; out->levels = 0; return RD_OK; }
     rd_u32 hs[10];
     RD_CUDA(cudaMemcpyAsync(hs, summary, sizeof(hs), cudaMemcpyDeviceToHost, st));
     RD_CUDA(cudaStreamSynchronize(st));
@@ -410,7 +417,7 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
         return RD_OK;
     }
     if (n <= RD_PLOC_SMALL_MAX && n <= RD_SORT_SMALL_MAX && !getenv("RD_BUILD_GREEDY") && !getenv("RD_BUILD_LBVH") && !getenv("RD_BUILD_GENERAL"))
-        return rd_build_wide_bvh_small(p, dlo, dhi, n, out);
+        return rd_build_wide_bvh_small(p, p->stream, dlo, dhi, n, out);
     RdTmp tmp(st);
     unsigned* dbounds; rd_u64 *keysA, *keysB; rd_u32 *valsA, *valsB;
     RD_CUDA(tmp.alloc(&dbounds, 8));
@@ -531,28 +538,121 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     return RD_OK;
 }
 
-extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigned nv, const uint32_t* didx, unsigned nt, rd_blas** out)
+// ---- bottom-level builds ---------------------------------------------------------------------------------------------
+// Small meshes (<= RD_PLOC_SMALL_MAX triangles) build DEFERRED: upload, boxes, the one-block build kernels and the triangle
+// gather are queued on one of RD_BUILD_STREAMS side streams and the call returns without waiting, so the one-block kernels
+// of consecutive meshes overlap on the GPU (a scene of 4096 patch meshes: 3.1 s -> see profiles/README_r2.md). The node
+// count, the root box and the non-finite-input flag arrive in host-mapped memory; rd_blas_resolve reads them the first time
+// they are needed (rd_blas_stats, rd_tlas_build, rd_blas_free) and moves the nodes into an exact-size allocation. An error
+// of a deferred build (NaN / Inf vertices) is therefore reported by that later call. Option "async_build" = 0 resolves at once.
+#define RD_BUILD_STREAMS 8
+#define RD_SUMMARY_WORDS 16
+#define RD_SUMMARY_CHUNK 4096u
+
+static int rd_build_stream(rd_platform* p, cudaStream_t* out)
 {
-    if (!p || !out || (nt && (!dverts || !didx))) { rd_set_error("rd_blas_build: null argument"); return RD_E_ARG; }
+    if (p->buildStreams.empty()) {
+        for (int k = 0; k < RD_BUILD_STREAMS; ++k) { cudaStream_t s; RD_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); p->buildStreams.push_back(s); }
+    }
+    *out = p->buildStreams[p->buildNext++ % p->buildStreams.size()];
+    return RD_OK;
+}
+
+static int rd_summary_slot(rd_platform* p, volatile rd_u32** host, rd_u32** dev)
+{
+    if (p->summaryUsed == p->summaryHost.size() * RD_SUMMARY_CHUNK) {
+        void* h = 0; void* d = 0;
+        RD_CUDA(cudaHostAlloc(&h, (size_t)RD_SUMMARY_CHUNK * RD_SUMMARY_WORDS * 4, cudaHostAllocMapped));
+        RD_CUDA(cudaHostGetDevicePointer(&d, h, 0));
+        p->summaryHost.push_back((rd_u32*)h); p->summaryDev.push_back((rd_u32*)d);
+    }
+    const size_t chunk = p->summaryUsed / RD_SUMMARY_CHUNK, at = (p->summaryUsed % RD_SUMMARY_CHUNK) * RD_SUMMARY_WORDS;
+    p->summaryUsed += 1;
+    *host = p->summaryHost[chunk] + at; *dev = p->summaryDev[chunk] + at;
+    return RD_OK;
+}
+
+int rd_blas_resolve(rd_platform* p, rd_blas* b)
+{
+    if (!b || !b->pending) return b && b->failed ? RD_E_ARG : RD_OK;
     RD_CUDA(cudaSetDevice(p->device));
-    cudaStream_t st = p->stream;
+    RD_CUDA(cudaEventSynchronize(b->done));
+    cudaEventDestroy(b->done);
+    b->pending = 0;
+    const volatile rd_u32* hs = b->summary;
+    if (hs[3]) { b->failed = 1; rd_set_error("BuildAccelStruct: %u primitive(s) with NaN / Inf coordinates", hs[3]); return RD_E_ARG; }
+    if (hs[1] != b->triCount || hs[2] > 200u || hs[0] == 0u || hs[0] > b->triCount + 1u) {
+        b->failed = 1; rd_set_error("rd_build_wide_bvh: %u leaf records for %u primitives", hs[1], b->triCount); return RD_E_CUDA;
+    }
+    b->nodeCount = hs[0]; b->levels = hs[2];
+    for (int k = 0; k < 3; ++k) { rd_u32 u = hs[4 + k], v = hs[7 + k]; memcpy(&b->lo[k], &u, 4); memcpy(&b->hi[k], &v, 4); }
+    // the build wrote into a worst-case allocation: keep what is used (the build has completed, so the platform stream may copy)
+    RdNode8* exact = 0;
+    RD_CUDA(cudaMallocAsync(&exact, (size_t)b->nodeCount * sizeof(RdNode8), p->stream));
+    RD_CUDA(cudaMemcpyAsync(exact, b->nodes, (size_t)b->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, p->stream));
+    RD_CUDA(cudaFreeAsync(b->nodes, p->stream));
+    b->nodes = exact;
+    return RD_OK;
+}
+
+static int rd_blas_build_on(rd_platform* p, cudaStream_t st, bool deferred, const float* dverts, const uint32_t* didx, unsigned nt, rd_blas** out)
+{
     RdTmp tmp(st);
     RdF4 *plo, *phi;
     RD_CUDA(tmp.alloc(&plo, nt)); RD_CUDA(tmp.alloc(&phi, nt));
     if (nt) { rd_k_tri_boxes<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, nt, plo, phi); p->launches += 1; }
     RdBuildResult r;
-    int rc = rd_build_wide_bvh(p, plo, phi, nt, &r);
+    memset(&r, 0, sizeof(r));
+    volatile rd_u32* hostSummary = 0; rd_u32* devSummary = 0;
+    int rc;
+    if (deferred) {
+        rc = rd_summary_slot(p, &hostSummary, &devSummary);
+        if (rc) return rc;
+        rc = rd_build_wide_bvh_small(p, st, plo, phi, nt, &r, devSummary);
+    } else rc = rd_build_wide_bvh(p, plo, phi, nt, &r);
     if (rc) return rc;
     rd_blas* b = new rd_blas();
+    memset(b, 0, sizeof(*b));
+    b->owner = p;
     b->nodes = r.nodes; b->nodeCount = r.nodeCount; b->triCount = nt; b->levels = r.levels;
     memcpy(b->lo, r.lo, 12); memcpy(b->hi, r.hi, 12);
     RD_CUDA(cudaMallocAsync(&b->tris, nt ? (size_t)nt * sizeof(RdTri) : 48, st));
     if (nt) { rd_k_gather_tris<<<rd_grid(nt), RD_BT, 0, st>>>(dverts, didx, r.leafPrim, b->tris, nt); p->launches += 1; }
     RD_CUDA(cudaGetLastError());
-    RD_CUDA(cudaFreeAsync(r.leafPrim, st));   // everything that follows on the platform stream is ordered behind the build
-    (void)nv;
+    RD_CUDA(cudaFreeAsync(r.leafPrim, st));   // everything that follows on the same stream is ordered behind the build
+    if (deferred) {
+        b->pending = 1; b->summary = hostSummary;
+        RD_CUDA(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+        RD_CUDA(cudaEventRecord(b->done, st));
+        if (!p->optAsyncBuild) {
+            rc = rd_blas_resolve(p, b);
+            if (rc) { cudaFree(b->nodes); cudaFree(b->tris); delete b; return rc; }
+        }
+    }
     *out = b;
     return RD_OK;
+}
+
+static bool rd_build_deferrable(unsigned nt)
+{
+    return nt > 0 && nt <= RD_PLOC_SMALL_MAX && nt <= RD_SORT_SMALL_MAX && !getenv("RD_BUILD_GREEDY") && !getenv("RD_BUILD_LBVH") && !getenv("RD_BUILD_GENERAL");
+}
+
+extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigned nv, const uint32_t* didx, unsigned nt, rd_blas** out)
+{
+    if (!p || !out || (nt && (!dverts || !didx))) { rd_set_error("rd_blas_build: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    (void)nv;
+    if (!rd_build_deferrable(nt)) return rd_blas_build_on(p, p->stream, false, dverts, didx, nt, out);
+    // the caller's arrays were produced on the platform stream: the side stream starts behind what is queued there now
+    cudaStream_t st; int rc = rd_build_stream(p, &st);
+    if (rc) return rc;
+    cudaEvent_t ready;
+    RD_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    RD_CUDA(cudaEventRecord(ready, p->stream));
+    RD_CUDA(cudaStreamWaitEvent(st, ready, 0));
+    cudaEventDestroy(ready);
+    return rd_blas_build_on(p, st, true, dverts, didx, nt, out);
 }
 
 extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, const uint32_t* idx, unsigned nt, rd_blas** out)
@@ -561,18 +661,22 @@ extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, co
     RD_CUDA(cudaSetDevice(p->device));
     for (size_t k = 0; k < (size_t)nt * 3; ++k)
         if (idx[k] >= nv) { rd_set_error("rd_blas_build: index %u out of range (nv=%u)", idx[k], nv); return RD_E_ARG; }
-    RdTmp tmp(p->stream);
+    const bool deferred = rd_build_deferrable(nt);
+    cudaStream_t st = p->stream;
+    if (deferred) { int rc = rd_build_stream(p, &st); if (rc) return rc; }
+    RdTmp tmp(st);
     float* dv; uint32_t* di;
     RD_CUDA(tmp.alloc(&dv, (size_t)nv * 3)); RD_CUDA(tmp.alloc(&di, (size_t)nt * 3));
-    if (nv) RD_CUDA(cudaMemcpyAsync(dv, verts, (size_t)nv * 12, cudaMemcpyHostToDevice, p->stream));
-    if (nt) RD_CUDA(cudaMemcpyAsync(di, idx, (size_t)nt * 12, cudaMemcpyHostToDevice, p->stream));
-    return rd_blas_build_device(p, dv, nv, di, nt, out);
+    if (nv) RD_CUDA(cudaMemcpyAsync(dv, verts, (size_t)nv * 12, cudaMemcpyHostToDevice, st));
+    if (nt) RD_CUDA(cudaMemcpyAsync(di, idx, (size_t)nt * 12, cudaMemcpyHostToDevice, st));
+    return rd_blas_build_on(p, st, deferred, dv, di, nt, out);
 }
 
 extern "C" int rd_blas_free(rd_platform* p, rd_blas* b)
 {
     if (!b) return RD_OK;
     if (p) cudaSetDevice(p->device);
+    if (b->pending) { cudaEventSynchronize(b->done); cudaEventDestroy(b->done); b->pending = 0; }
     cudaFree(b->nodes); cudaFree(b->tris);
     delete b;
     return RD_OK;
@@ -581,6 +685,7 @@ extern "C" int rd_blas_free(rd_platform* p, rd_blas* b)
 extern "C" int rd_blas_stats(rd_blas* b, uint64_t out[4])
 {
     if (!b || !out) { rd_set_error("rd_blas_stats: null argument"); return RD_E_ARG; }
+    if (b->pending || b->failed) { int rc = rd_blas_resolve(b->owner, b); if (rc) return rc; }
     out[0] = b->nodeCount; out[1] = b->triCount; out[2] = b->levels;
     out[3] = (uint64_t)b->nodeCount * sizeof(RdNode8) + (uint64_t)b->triCount * sizeof(RdTri);
     return RD_OK;
@@ -594,8 +699,9 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
     std::vector<RdInstance> inst(n);
     std::vector<RdF4> lo(n), hi(n);
     for (unsigned i = 0; i < n; ++i) {
-        const rd_blas* b = instances[i].bottomAccelStruct;
+        rd_blas* b = instances[i].bottomAccelStruct;
         if (!b) { rd_set_error("rd_tlas_build: instance %u has no bottom-level structure", i); return RD_E_ARG; }
+        if (b->pending || b->failed) { int brc = rd_blas_resolve(p, b); if (brc) return brc; }   // deferred small builds: node count, root box, exact storage
         RdInstance& I = inst[i];
         memcpy(I.fwd, instances[i].transform, 64);
         float inv[16];

@@ -34,7 +34,10 @@ struct rd_blas {
     RdNode8* nodes; RdTri* tris;
     uint32_t nodeCount, triCount, levels;
     float lo[3], hi[3];
+    // deferred small build (rd_build.cu): node count / root box not read back yet
+    int pending, failed; cudaEvent_t done; volatile uint32_t* summary; struct rd_platform* owner;
 };
+int rd_blas_resolve(struct rd_platform* p, rd_blas* b);
 
 struct rd_module {
     CUmodule mod; CUfunction raygen;
@@ -78,6 +81,9 @@ struct rd_platform {
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
+    std::vector<cudaStream_t> buildStreams; size_t buildNext;   // side streams of deferred small bottom-level builds
+    std::vector<uint32_t*> summaryHost, summaryDev; size_t summaryUsed;   // host-mapped build summaries, RD_SUMMARY_CHUNK per chunk
+    long optAsyncBuild;
     void* comm;                                  // RdComm* (rd_comm.cu): the NCCL communicator of the multi-GPU frame gather
     volatile unsigned* unitSlots; unsigned* unitSlotsDev; cudaEvent_t unitEvent;   // rd_trace_rays_units: unit numbers land in host-mapped memory
     long optWfTimeline; std::vector<cudaEvent_t> tlEvents; std::vector<int> tlCodes; size_t tlUsed;   // rd_wf_timeline
