@@ -22,6 +22,11 @@
 // warp-cooperative triangle phase (RD_COOP_TRI, -6 %), pending group in registers (RD_PEND_REG, -13 %), software
 // prefetch (RD_PREFETCH, -2 %), triangle postponing by warp vote (RD_FLUSH_DIV, -3 %), PRMT / hybrid dequantisation
 // (RD_DEQUANT_I2F 0 / 2, -3 %).
+// Measured and dropped in round 2 (profiles/README_r2.md, code in the history at commit "Deferred multi-stream small ... RD_TRI_WAIT"):
+// lanes that hold pending triangles WAIT until k/8 of the warp hold some (RD_TRI_WAIT, warp-synchronous loop with votes
+// between the phases; the triangle phase is 40 % of the issued instructions at 5 of 32 lanes on the 10 M-triangle field):
+// k = 2: 10 M 2991 -> 3050 Mrays/s, C2 4520 -> 4290; k >= 6: -7 % .. -20 % -- what the fuller triangle phase saves, the
+// waiting lanes lose in extra node iterations. 256-byte nodes with float boxes: see RD_NODE_F32 in rd_types.h.
 #ifndef RD_TRAVERSE_H
 #define RD_TRAVERSE_H
 #include "rd_types.h"
@@ -73,21 +78,6 @@ static inline rd_u32 rd_prmt_(rd_u32 a, rd_u32 b, rd_u32 s)
 #endif
 #ifndef RD_STACK_ENTRIES
 #define RD_STACK_ENTRIES 48
-#endif
-// RD_TRI_WAIT = k (0..8): a lane that holds pending triangles stops walking and waits until k/8 of the warp's lanes in this
-// bottom-level structure hold some (or nobody else can make progress, or a lane has waited RD_TRI_WAIT_MAX iterations);
-// then ALL holders test. ncu on the 10 M-triangle field (profiles/ncu_r2_primary_2237.txt, source page): the triangle phase
-// is 40 % of the issued instructions at 5 of 32 lanes -- 15.7 executions per warp for 2.5 tests per ray.
-#ifndef RD_TRI_WAIT
-#define RD_TRI_WAIT 0
-#endif
-#ifndef RD_TRI_WAIT_MAX
-#define RD_TRI_WAIT_MAX 4
-#endif
-#if defined(__CUDA_ARCH__) && RD_TRI_WAIT
-#define RD_WAITING(np) ((np) > 0)
-#else
-#define RD_WAITING(np) false
 #endif
 
 struct RdHitRec {
@@ -339,20 +329,6 @@ struct RdTraversal {
     RdHitRec hit;
     bool any;
 
-#if defined(__CUDA_ARCH__) && RD_TRI_WAIT
-    int nwait;
-    __device__ __forceinline__ bool rd_tri_vote(bool holding, int& waited)
-    {
-        const unsigned act = __activemask();
-        const unsigned holders = __ballot_sync(act, holding);
-        if (!holders) return false;
-        const unsigned overdue = __ballot_sync(act, holding && waited >= RD_TRI_WAIT_MAX);
-        const bool fire = overdue != 0u || holders == act || __popc(holders) * 8 >= __popc(act) * RD_TRI_WAIT;
-        if (holding) waited = fire ? 0 : waited + 1;
-        return fire && holding;
-    }
-#endif
-
     RD_HD void push(const RdScene* scene, RdStackEntry e)
     {
         if (sp < RD_STACK_ENTRIES) stack[sp++] = e;
@@ -362,9 +338,6 @@ struct RdTraversal {
     RD_HD void begin(RdStackEntry* stackMemory, const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
     {
         stack = stackMemory; pend = stackMemory + RD_STACK_ENTRIES; sp = 0; blasSp = -1; np = 0;
-#if defined(__CUDA_ARCH__) && RD_TRI_WAIT
-        nwait = 0;
-#endif
         nodes = scene->nodes; tris = 0; curInst = 0;
         wox = ox; woy = oy; woz = oz; wdx = dx; wdy = dy; wdz = dz; tmin = tmin_; tmax = tmax_;
         rd_frame_set(f, ox, oy, oz, dx, dy, dz, scene->maxAbs);
@@ -383,7 +356,7 @@ struct RdTraversal {
     {
         RdStackEntry tg; tg.x = 0; tg.y = 0;   // top-level leaf records (instances) to enter now: x = first record, y = dense bits
         // ---- 1. node phase
-        if (ng.y > 0x00ffffffu && !RD_WAITING(np)) {
+        if (ng.y > 0x00ffffffu) {
             const rd_u32 bit = 31u - (rd_u32)RD_CLZ(ng.y);
             const rd_u32 imask = ng.y & 0xffu;   // low byte of an inner group = imask
             ng.y &= ~(1u << bit);
@@ -448,14 +421,7 @@ struct RdTraversal {
                 ng.x = 0; ng.y = 0x80000000u;
                 return true;
             }
-        } else if (
-#if defined(__CUDA_ARCH__) && RD_TRI_WAIT
-            // warp vote among the lanes that are inside a bottom-level structure right now
-            rd_tri_vote(np > 0, nwait)
-#else
-            np > 0
-#endif
-            ) {
+        } else if (np > 0) {
             // ---- 2. triangle phase
             RdStackEntry g; g.x = 0; g.y = 0;
             rd_u32 gnib = 0;
@@ -480,7 +446,7 @@ struct RdTraversal {
             }
         }
         // ---- 3. pop phase
-        if (ng.y <= 0x00ffffffu && !RD_WAITING(np)) {
+        if (ng.y <= 0x00ffffffu) {
             if (blasSp >= 0 && sp == blasSp) {
                 // bottom-level structure exhausted (its pending group was tested above): back to world space
                 blasSp = -1; nodes = scene->nodes;
