@@ -220,7 +220,8 @@ int rd_trace_counters(rd_platform* p, uint64_t out[3]);
 int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID, unsigned totalSamples,
                              unsigned width, unsigned height, rd_handle rayA, rd_handle rayB);
 
-/* runtime options: "fmad" (0/1, NVRTC contraction for user code), "tile" (0/1 8x4 pixel tiles per warp),
+/* runtime options: "fmad" (0/1, NVRTC contraction for user code), "prec_div" (0/1, default 0: user-program division at the
+ * 2.5 ulp OpenCL C asks for; 1 = correctly rounded), "async_build" (0/1, default 1: small bottom-level builds are deferred), "tile" (0/1 8x4 pixel tiles per warp),
  * "block" (threads per block of raygen launches), "count_rays" (0/1: modules created afterwards count
  * every traceRay invocation, the numerator of the Mrays/s metric; read with rd_ray_count),
  * "max_trace_depth" (1..8, default 2: how deep traceRay may nest -- raygen -> hit shader -> shadow ray is 2;

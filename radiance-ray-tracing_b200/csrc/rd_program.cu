@@ -117,6 +117,8 @@ static bool parse_sbt(const char* text, std::vector<SbtRow>* rows, std::string* 
     }
 }
 
+static bool g_precDiv = false;   // set from the platform option right before a module is compiled
+
 static std::string strip_comments(const std::string& src)
 {
     std::string o; o.reserve(src.size());
@@ -562,6 +564,12 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
     std::vector<const char*> opts = {"--gpu-architecture=sm_100a", "--std=c++17", "-default-device", "--pre-include=cl_compat.h",
                                      "-lineinfo", "-w", "--ptxas-options=-v"};
     opts.push_back(fmad ? "--fmad=true" : "--fmad=false");
+    // Single-precision division in user programs: OpenCL C requires 2.5 ulp of `/` (the reference builds its programs with
+    // clBuildProgram and no -cl-fp32-correctly-rounded-divide-sqrt, radiance/src/radiance.cpp:165-167), and the ~12-instruction
+    // IEEE sequence per division is 27 % of the path-tracing raygen (C3 inline 802 -> 1022, C1 910 -> 1296 Mrays/s, images as close
+    // to the reference as before: profiles/README_r2.md). The traversal and random_pcg3d round explicitly and are not affected.
+    // Option "prec_div" = 1 restores correctly rounded division.
+    opts.push_back(g_precDiv ? "--prec-div=true" : "--prec-div=false");
     if (countRays) opts.push_back("-DRD_COUNT_RAYS=1");
     opts.push_back(RD_NODE_F32 ? "-DRD_NODE_F32=1" : "-DRD_NODE_F32=0");   // user programs walk the node form this library builds
     // developer knob for ablations: extra NVRTC flags (e.g. "-DRD_FLUSH_DIV=2 -DRD_DEQUANT_I2F=0")
@@ -600,6 +608,7 @@ extern "C" int rd_shader_compile_check(const char* code, unsigned size, const ch
 {
     if (!code) { rd_set_error("rd_shader_compile_check: null argument"); return RD_E_ARG; }
     std::vector<char> cubin; std::string log;
+    g_precDiv = getenv("RD_PREC_DIV") != 0;
     int rc = rd_compile_program(code, size, sbt_json ? sbt_json : "", fmad != 0, &cubin, &log, false, 2, getenv("RD_CHECK_STEAL") != 0, getenv("RD_CHECK_BANDED") != 0);
     if (rc) return rc;
     if (cubinSize) *cubinSize = cubin.size();
@@ -614,6 +623,7 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
     RD_CUDA(cudaSetDevice(p->device));
     { int drc = rd_driver_init(); if (drc) return drc; }
     std::vector<char> cubin; std::string log;
+    g_precDiv = p->optPrecDiv != 0;
     int rc = rd_compile_program(code, size, p->sbtJson, p->optFmad != 0, &cubin, &log, p->optCountRays != 0, (int)p->optMaxDepth, p->optSteal != 0,
                                 p->optStreamImage != 0);
     if (rc) return rc;

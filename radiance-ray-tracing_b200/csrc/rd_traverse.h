@@ -162,7 +162,7 @@ RD_HD float rd_safe_rcp(float d)
 {
     const float tiny = 1e-20f;
     float a = fabsf(d) > tiny ? d : (RD_F2U(d) >> 31 ? -tiny : tiny);
-    return 1.0f / a;
+    return RD_RCP(a);   // correctly rounded whatever division mode the user program is compiled with
 }
 
 #ifdef __CUDA_ARCH__

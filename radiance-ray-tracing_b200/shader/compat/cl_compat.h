@@ -16,6 +16,7 @@
 
 #if defined(__CUDACC_RTC__) || defined(__CUDACC__)
 #define RD_DEVICE_BUILD 1
+#define RD_FDIV(a, b) __fdiv_rn((a), (b))
 #define RD_F __device__ __forceinline__
 #define RD_DEV __device__
 // the traversal core must be seen before the OpenCL spellings float4/uint4 are mapped onto the
@@ -23,6 +24,7 @@
 #include "rd_traverse.h"
 #else
 #define RD_DEVICE_BUILD 0
+#define RD_FDIV(a, b) ((a) / (b))
 #define RD_F inline
 #define RD_DEV
 #include <math.h>

@@ -23,7 +23,8 @@ RD_F float3 random_pcg3d(uint3 v)
     x ^= x >> 16; y ^= y >> 16; z ^= z >> 16;
     x += y * z; y += z * x; z += x * y;
     const float scale = (float)0xffffffffu;
-    return float3((float)x / scale, (float)y / scale, (float)z / scale);
+    // correctly rounded on purpose (the reference's CPU path divides exactly; user-program division is otherwise 2.5 ulp)
+    return float3(RD_FDIV((float)x, scale), RD_FDIV((float)y, scale), RD_FDIV((float)z, scale));
 }
 
 // out = a * b with b a column vector; each row is summed left to right
