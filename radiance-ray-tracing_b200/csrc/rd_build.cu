@@ -725,6 +725,28 @@ extern "C" int rd_tlas_build(rd_platform* p, const rd_instance_desc* instances, 
     RdBuildResult r;
     int rc = rd_build_wide_bvh(p, dlo, dhi, n, &r);
     if (rc) return rc;
+    // L2 residency of the hot node array (option "l2_persist", bytes; 0 = off): the node array of the largest bottom-level
+    // structure becomes a persisting access-policy window of the platform stream, its triangle records stream through --
+    // on a structure larger than L2 the 10 node fetches of a ray then hit L2 while the 3 triangle fetches go to HBM.
+    if (p->optL2Persist > 0 && n) {
+        const rd_blas* big = 0;
+        for (unsigned i = 0; i < n; ++i) { const rd_blas* b = instances[i].bottomAccelStruct; if (!big || b->nodeCount > big->nodeCount) big = b; }
+        int maxWin = 0, maxPersist = 0;
+        cudaDeviceGetAttribute(&maxWin, cudaDevAttrMaxAccessPolicyWindowSize, p->device);
+        cudaDeviceGetAttribute(&maxPersist, cudaDevAttrMaxPersistingL2CacheSize, p->device);
+        size_t want = (size_t)big->nodeCount * sizeof(RdNode8);
+        size_t carve = (size_t)p->optL2Persist < (size_t)maxPersist ? (size_t)p->optL2Persist : (size_t)maxPersist;
+        if (maxWin > 0 && carve > 0) {
+            cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, carve);
+            cudaStreamAttrValue attr; memset(&attr, 0, sizeof(attr));
+            attr.accessPolicyWindow.base_ptr = (void*)big->nodes;
+            attr.accessPolicyWindow.num_bytes = want < (size_t)maxWin ? want : (size_t)maxWin;
+            attr.accessPolicyWindow.hitRatio = want <= carve ? 1.0f : (float)carve / (float)want;
+            attr.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+            attr.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+            if (cudaStreamSetAttribute(p->stream, cudaStreamAttributeAccessPolicyWindow, &attr) != cudaSuccess) cudaGetLastError();
+        }
+    }
     RdHandleObj* o = new RdHandleObj();
     memset(o, 0, sizeof(*o));
     o->magic = RD_HANDLE_MAGIC; o->kind = RD_H_TLAS;

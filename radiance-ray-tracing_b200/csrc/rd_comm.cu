@@ -149,6 +149,7 @@ __global__ void rd_k_band_copy(unsigned char* __restrict__ image, unsigned char*
         const unsigned k = (unsigned)(i / vecPerRow), v = (unsigned)(i - (size_t)k * vecPerRow);
         const unsigned band = k / P.bandRows, within = k - band * P.bandRows;     // k-th owned row: owned band `band`, row `within`
         const unsigned tileRow = (band * P.world + rank) * P.bandRows + within;
+        if (tileRow >= P.tileRows) continue;   // cannot happen for the rows a rank owns; keeps a wrong plan from writing outside the frame
         uint4* a = (uint4*)(image + (size_t)tileRow * P.rowBytes) + v;
         uint4* s = (uint4*)(stage + (size_t)k * P.rowBytes) + v;
         if (toStage) *s = *a; else *a = *s;

@@ -45,7 +45,8 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->bandFlags = 0; p->bandFlagsDev = 0; p->bandCount = p->bandRows = p->bandTileRows = 0; p->bandCopied = 0; p->bandRowBytes = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
-    p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0;
+    p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0; p->optL2Persist = 96l << 20;   // 10 M-triangle field 3036 -> 3135 Mrays/s, C2 unchanged (profiles/exp_l2persist_r2f.log)
+    if (const char* e = getenv("RD_L2_PERSIST")) p->optL2Persist = atol(e);
     p->comm = 0; p->unitSlots = 0; p->unitSlotsDev = 0; p->unitEvent = 0; p->optWfTimeline = 0; p->tlUsed = 0;
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
@@ -402,6 +403,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
     else if (!strcmp(key, "wf_timeline")) p->optWfTimeline = value;
     else if (!strcmp(key, "async_build")) p->optAsyncBuild = value;
     else if (!strcmp(key, "prec_div")) p->optPrecDiv = value;
+    else if (!strcmp(key, "l2_persist")) p->optL2Persist = value;
     else if (!strcmp(key, "trim_pool")) {   // give the build scratch and the wavefront queues back to the driver (value ignored)
         cudaSetDevice(p->device);
         cudaStreamSynchronize(p->stream);

@@ -83,7 +83,7 @@ struct rd_platform {
     RdWfBuffers wf;
     std::vector<cudaStream_t> buildStreams; size_t buildNext;   // side streams of deferred small bottom-level builds
     std::vector<uint32_t*> summaryHost, summaryDev; size_t summaryUsed;   // host-mapped build summaries, RD_SUMMARY_CHUNK per chunk
-    long optAsyncBuild, optPrecDiv;
+    long optAsyncBuild, optPrecDiv, optL2Persist;
     void* comm;                                  // RdComm* (rd_comm.cu): the NCCL communicator of the multi-GPU frame gather
     volatile unsigned* unitSlots; unsigned* unitSlotsDev; cudaEvent_t unitEvent;   // rd_trace_rays_units: unit numbers land in host-mapped memory
     long optWfTimeline; std::vector<cudaEvent_t> tlEvents; std::vector<int> tlCodes; size_t tlUsed;   // rd_wf_timeline

@@ -282,6 +282,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    const RdWfState wf = *wfp;\n"
          "    const unsigned slot = blockIdx.x * blockDim.x + threadIdx.x;\n"
          "    if (slot >= wf.count * wf.samples) return;\n"
+         "    RD_BOUND(slot < wf.capacity, wf.status, return);\n"
          "    const unsigned sample = slot / wf.count, item = slot - sample * wf.count, frameID = wf.frameID + sample;\n"
          "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + item, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    struct SceneData sd; struct Payload pl;\n"
@@ -310,7 +311,9 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    const unsigned jj = blockIdx.x * blockDim.x + threadIdx.x;\n"
          "    if (jj >= n) return;\n"
          "    const unsigned j = wf.sortOn ? wf.order[jj] : jj;\n"
+         "    RD_BOUND(j < n, wf.status, return);\n"
          "    const unsigned slot = wf.pathOf[wf.cur][j];\n"
+         "    RD_BOUND(slot < wf.capacity && slot < wf.count * wf.samples, wf.status, return);\n"
          "    const unsigned sample = slot / wf.count, item = slot - sample * wf.count;\n"
          "    rd_wf_gid[threadIdx.x] = rd_wf_global_id(wf.first + item, wf.tileW, wf.ilWorld, wf.ilRank, wf.ilBandRows);\n"
          "    struct SceneData sd;\n"
@@ -348,6 +351,7 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    }\n"
          "    if (more) {\n"
          "        const unsigned k = base + (unsigned)__popc(live & ((1u << lane) - 1u));\n"
+         "        RD_BOUND(k < wf.capacity && k < n, wf.status, return);\n"
          "        RdF4 a, b;\n"
          "        a.x = pl.nextRayOrigin.x; a.y = pl.nextRayOrigin.y; a.z = pl.nextRayOrigin.z; a.w = wf.tmin;\n"
          "        b.x = pl.nextRayDirection.x; b.y = pl.nextRayDirection.y; b.z = pl.nextRayDirection.z; b.w = wf.tmax;\n"
@@ -571,7 +575,8 @@ static int rd_compile_program(const char* code, unsigned size, const std::string
     // Option "prec_div" = 1 restores correctly rounded division.
     opts.push_back(g_precDiv ? "--prec-div=true" : "--prec-div=false");
     if (countRays) opts.push_back("-DRD_COUNT_RAYS=1");
-    opts.push_back(RD_NODE_F32 ? "-DRD_NODE_F32=1" : "-DRD_NODE_F32=0");   // user programs walk the node form this library builds
+    opts.push_back(RD_NODE_F32 ? "-DRD_NODE_F32=1" : "-DRD_NODE_F32=0");
+    if (RD_BOUNDS_CHECK) opts.push_back("-DRD_BOUNDS_CHECK=1");   // user programs walk the node form this library builds
     // developer knob for ablations: extra NVRTC flags (e.g. "-DRD_FLUSH_DIV=2 -DRD_DEQUANT_I2F=0")
     std::vector<std::string> extra;
     if (const char* env = getenv("RD_NVRTC_FLAGS")) {
@@ -774,6 +779,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     S.frameID = rt[0]; S.samples = 1; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
     S.ilWorld = p->ilWorld; S.ilRank = p->ilRank; S.ilBandRows = p->ilBandRows ? p->ilBandRows : 1u;
     S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
+    S.status = p->dstatus; S.capacity = B.capacity;
     rc = rd_wf_upload_state(p, &S);
     if (rc) return rc;
     CUdeviceptr dinfo; size_t infoBytes = 0;
@@ -1113,6 +1119,17 @@ extern "C" int rd_trace_rays_units(rd_platform* p, unsigned width, unsigned heig
         RD_CUDA(cudaEventSynchronize(p->unitEvent));   // the next unit's number arrived while this one was being enqueued / rendered
         cur = p->unitSlots[which];
     }
+    return RD_OK;
+}
+
+// RD_BOUNDS_CHECK builds: bounds violations counted by the device since the last call (0 in a normal build)
+extern "C" int rd_debug_bounds_violations(rd_platform* p, unsigned* count, int* checkedBuild)
+{
+    if (!p || !count) { rd_set_error("rd_debug_bounds_violations: null argument"); return RD_E_ARG; }
+    RD_CUDA(cudaSetDevice(p->device));
+    RD_CUDA(cudaStreamSynchronize(p->stream));
+    *count = p->hstatus[2]; p->hstatus[2] = 0u;
+    if (checkedBuild) *checkedBuild = RD_BOUNDS_CHECK;
     return RD_OK;
 }
 

@@ -406,6 +406,9 @@ struct RdTraversal {
                 // top level: the first record is an instance -> descend into its bottom-level structure
                 const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
                 tg.y &= tg.y - 1u;
+#if defined(RD_BOUNDS_CHECK) && RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
+                if (tg.x + k >= scene->instanceCount) { if (scene->status) atomicAdd(scene->status + 2, 1u); return false; }
+#endif
                 const rd_u32 ii = scene->leafInstances[tg.x + k];
                 if (tg.y) push(scene, tg);
                 if (ng.y > 0x00ffffffu) push(scene, ng);
@@ -429,7 +432,11 @@ struct RdTraversal {
                 if (!g.y) { --np; g = pend[2 * np]; gnib = pend[2 * np + 1].x; }
                 const rd_u32 low = g.y & (0u - g.y);
                 g.y ^= low;
-                const RdTri* tr = tris + (g.x + (rd_u32)RD_POPC(gnib & (low - 1u)));
+                const rd_u32 rec = g.x + (rd_u32)RD_POPC(gnib & (low - 1u));
+#if defined(RD_BOUNDS_CHECK) && RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
+                if (rec >= curInst->flags) { if (scene->status) atomicAdd(scene->status + 2, 1u); continue; }   // flags = triangle records
+#endif
+                const RdTri* tr = tris + rec;
                 RdF4 a, b, c;
                 RD_LOAD_F4(a, &tr->v0); RD_LOAD_F4(b, &tr->v1); RD_LOAD_F4(c, &tr->v2);
                 onCandidate.countTri();

@@ -114,7 +114,11 @@ __global__ void rd_k_wf_hist(const RdWfState* __restrict__ wfp)
     for (unsigned b = threadIdx.x; b < RD_WF_KEY_BINS; b += blockDim.x) bins[b] = 0u;
     __syncthreads();
     for (unsigned j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x)
-        atomicAdd(&bins[wf.keys[j]], 1u);
+    {
+        const unsigned key = wf.keys[j];
+        RD_BOUND(key < RD_WF_KEY_BINS, wf.status, continue);
+        atomicAdd(&bins[key], 1u);
+    }
     __syncthreads();
     for (unsigned b = threadIdx.x; b < RD_WF_KEY_BINS; b += blockDim.x)
         if (bins[b]) atomicAdd(&wf.hist[b], bins[b]);
@@ -156,7 +160,9 @@ __global__ void rd_k_wf_scatter(const RdWfState* __restrict__ wfp)
     unsigned base = 0;
     if (lane == leader) base = atomicAdd(&wf.hist[key], (unsigned)__popc(same));
     base = __shfl_sync(same, base, leader);
-    wf.order[base + (unsigned)__popc(same & ((1u << lane) - 1u))] = j;
+    const unsigned at = base + (unsigned)__popc(same & ((1u << lane) - 1u));
+    RD_BOUND(at < n && key < RD_WF_KEY_BINS, wf.status, return);
+    wf.order[at] = j;
 }
 
 

@@ -42,7 +42,21 @@ struct RD_ALIGN(16) RdWfState {
     rd_u32 samples;               // samples in flight in this pass: path slot = sample * count + work-item, frame id = frameID + sample
     int sbtRecordOffset, missIndex;
     float tmin, tmax;
+    rd_u32* status;               // host-mapped platform flags; [2] counts bounds violations in RD_BOUNDS_CHECK builds
+    rd_u32 capacity, pad;         // path slots / queue entries the buffers above were allocated for
 };
+
+// RD_BOUNDS_CHECK=1 builds (libradiance_b200_bounds.so, tests/test_gpu_bounds.py): every queue / order / record index the
+// wavefront stages and the walk compute is checked against the size of what it indexes before the access; a violation is
+// counted in status[2] and the access skipped. compute-sanitizer is closed on this pool, this is the memcheck stand-in.
+#ifndef RD_BOUNDS_CHECK
+#define RD_BOUNDS_CHECK 0
+#endif
+#if RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
+#define RD_BOUND(ok, st, action) do { if (!(ok)) { if (st) atomicAdd((st) + 2, 1u); action; } } while (0)
+#else
+#define RD_BOUND(ok, st, action) do { } while (0)
+#endif
 
 // work-item t of the launch -> global id (pixel index), same mapping as get_global_id in cl_compat.h
 RD_HD rd_u32 rd_wf_global_id(rd_u32 t, rd_u32 tileW, rd_u32 world = 0, rd_u32 rank = 0, rd_u32 bandRows = 1)

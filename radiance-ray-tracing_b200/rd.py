@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "rd_steal_counter_export", "rd_steal_counter_import", "rd_steal_counter_adopt", "rd_trace_rays_steal", "rd_steal_owned", "rd_trace_rays_interleaved",
     "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
     "rd_comm_unique_id", "rd_comm_init", "rd_comm_adopt", "rd_comm_destroy", "rd_frame_gather", "rd_frame_gather_ranges",
-    "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline", "rd_debug_band_roundtrip",
+    "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline", "rd_debug_band_roundtrip", "rd_debug_bounds_violations",
 ]
 
 
@@ -86,6 +86,7 @@ def lib():
             "rd_frame_gather_units": [vp, vp, C.c_uint, C.c_uint, C.c_uint, C.c_uint, C.c_uint64],
             "rd_wf_timeline": [vp, vp, vp, C.c_uint, C.POINTER(C.c_uint)],
             "rd_debug_band_roundtrip": [vp, vp, vp] + [C.c_uint] * 6,
+            "rd_debug_bounds_violations": [vp, C.POINTER(C.c_uint), C.POINTER(C.c_int)],
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
@@ -135,6 +136,12 @@ class Platform:
         out = (C.c_uint32 * 2)()
         _check(lib().rd_status(self.handle, out, int(bool(clear))))
         return int(out[0]), int(out[1])
+
+    def bounds_violations(self):
+        """(violations since the last call, 1 if the library is an RD_BOUNDS_CHECK build)."""
+        n, chk = C.c_uint(0), C.c_int(0)
+        _check(lib().rd_debug_bounds_violations(self.handle, C.byref(n), C.byref(chk)))
+        return int(n.value), int(chk.value)
 
     def launch_count(self):
         return int(lib().rd_launch_count(self.handle))

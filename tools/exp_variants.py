@@ -17,6 +17,7 @@ W, H = 1920, 1080
 n_grid = int(sys.argv[1]) if len(sys.argv) > 1 else 708
 plt = rd.Platform.GetPlatform(0)
 stream = torch.cuda.ExternalStream(plt.stream(), device=0)
+plt.set_option("l2_persist", int(os.environ.get("RD_EXP_L2_PERSIST", "0")))
 bundle = scenes.heightfield_scene(n_grid, W, H)
 import time
 tlas, blas = scenes.build_scene(plt, bundle)

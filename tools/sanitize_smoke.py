@@ -51,5 +51,16 @@ t2, _ = scenes.build_scene(plt, hf)
 rays = scenes.pinhole_rays(hf.camera, stride=2)
 hitA, hitB = rd.trace_host_rays(plt, t2, rays)
 first, _ = rd.trace_host_rays(plt, t2, rays, rd.TRACE_TERMINATE_ON_FIRST_HIT)
+# determinism: the wavefront frame (atomics in the queues, the sort and the compaction) rendered five more times
+plt.set_option("wavefront", 1)
+frames = []
+for k in range(5):
+    ds.set_rtprop(0, 2, 3)
+    rd.TraceRays(plt, 0, 0, 0, w, h)
+    frames.append(ds.read_scratch().tobytes())
+plt.set_option("wavefront", 0)
+viol, checked = plt.bounds_violations()
+print("bounds-checked build: %d, violations: %d, wavefront frames identical over 5 runs: %s, device status %r" % (
+    checked, viol, all(f == frames[0] for f in frames), plt.status()))
 print("sanitize smoke done: inline mean %.2f, wavefront mean %.2f, units %x %x, hits %d" % (
     plain[..., :3].mean(), wave[..., :3].mean(), mask, mask2, int((hitA["t"] < 3e38).sum())))
