@@ -197,7 +197,7 @@ int rd_frame_gather_units(rd_platform* p, rd_handle image, unsigned width, unsig
 int rd_debug_band_roundtrip(rd_platform* p, rd_handle src, rd_handle dst, unsigned width, unsigned height, unsigned itemBytes,
                             unsigned bandTileRows, unsigned rank, unsigned world);
 /* memcheck stand-in (compute-sanitizer is closed on the GPU pool): a library built with -DRD_BOUNDS_CHECK=1 checks every queue /
- * order / record index against the size of what it indexes; this returns the violations counted since the last call. */
+ * order / record index against the size of what it indexes; *count is non-zero if any check failed since the last call. */
 int rd_debug_bounds_violations(rd_platform* p, unsigned* count, int* checkedBuild);
 /* Stage timeline of the last wavefront-mode call (option "wf_timeline" = 1): ms[i] = device time of stage i, codes[i] =
  * 1 generate, 2 trace, 3 sort, 4 shade, 5 accumulate, 6 resolve, 7 ray re-sort. Synchronises the platform stream. */

@@ -45,7 +45,8 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->bandFlags = 0; p->bandFlagsDev = 0; p->bandCount = p->bandRows = p->bandTileRows = 0; p->bandCopied = 0; p->bandRowBytes = 0;
     p->stealCounters = 0; p->stealOwned = 0; p->stealImported = 0; p->stealSlots = 0; p->stealOwnedCap = 0;
     memset(&p->wf, 0, sizeof(p->wf));
-    p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0; p->optL2Persist = 96l << 20;   // 10 M-triangle field 3036 -> 3135 Mrays/s, C2 unchanged (profiles/exp_l2persist_r2f.log)
+    p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0; p->optL2Persist = 0;   // off by default: +3 % on the 10 M-triangle primary frame at 96 MB, but the wavefront queues lose the L2 they
+    // stream through (C3 42.6 -> 58.0 ms, C5 488 -> 709 ms; profiles/README_r2.md)
     if (const char* e = getenv("RD_L2_PERSIST")) p->optL2Persist = atol(e);
     p->comm = 0; p->unitSlots = 0; p->unitSlotsDev = 0; p->unitEvent = 0; p->optWfTimeline = 0; p->tlUsed = 0;
     p->launches = 0;

@@ -1122,7 +1122,7 @@ extern "C" int rd_trace_rays_units(rd_platform* p, unsigned width, unsigned heig
     return RD_OK;
 }
 
-// RD_BOUNDS_CHECK builds: bounds violations counted by the device since the last call (0 in a normal build)
+// RD_BOUNDS_CHECK builds: non-zero if a bounds check failed on the device since the last call (always 0 in a normal build)
 extern "C" int rd_debug_bounds_violations(rd_platform* p, unsigned* count, int* checkedBuild)
 {
     if (!p || !count) { rd_set_error("rd_debug_bounds_violations: null argument"); return RD_E_ARG; }

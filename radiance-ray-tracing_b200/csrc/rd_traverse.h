@@ -407,7 +407,7 @@ struct RdTraversal {
                 const rd_u32 k = (rd_u32)RD_FFS(tg.y) - 1u;
                 tg.y &= tg.y - 1u;
 #if defined(RD_BOUNDS_CHECK) && RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
-                if (tg.x + k >= scene->instanceCount) { if (scene->status) atomicAdd(scene->status + 2, 1u); return false; }
+                if (tg.x + k >= scene->instanceCount) { if (scene->status) scene->status[2] = 1u; return false; }
 #endif
                 const rd_u32 ii = scene->leafInstances[tg.x + k];
                 if (tg.y) push(scene, tg);
@@ -434,7 +434,7 @@ struct RdTraversal {
                 g.y ^= low;
                 const rd_u32 rec = g.x + (rd_u32)RD_POPC(gnib & (low - 1u));
 #if defined(RD_BOUNDS_CHECK) && RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
-                if (rec >= curInst->flags) { if (scene->status) atomicAdd(scene->status + 2, 1u); continue; }   // flags = triangle records
+                if (rec >= curInst->flags) { if (scene->status) scene->status[2] = 1u; continue; }   // flags = triangle records
 #endif
                 const RdTri* tr = tris + rec;
                 RdF4 a, b, c;

@@ -42,18 +42,19 @@ struct RD_ALIGN(16) RdWfState {
     rd_u32 samples;               // samples in flight in this pass: path slot = sample * count + work-item, frame id = frameID + sample
     int sbtRecordOffset, missIndex;
     float tmin, tmax;
-    rd_u32* status;               // host-mapped platform flags; [2] counts bounds violations in RD_BOUNDS_CHECK builds
+    rd_u32* status;               // host-mapped platform flags; [2] is raised by a bounds violation in RD_BOUNDS_CHECK builds
     rd_u32 capacity, pad;         // path slots / queue entries the buffers above were allocated for
 };
 
 // RD_BOUNDS_CHECK=1 builds (libradiance_b200_bounds.so, tests/test_gpu_bounds.py): every queue / order / record index the
-// wavefront stages and the walk compute is checked against the size of what it indexes before the access; a violation is
-// counted in status[2] and the access skipped. compute-sanitizer is closed on this pool, this is the memcheck stand-in.
+// wavefront stages and the walk compute is checked against the size of what it indexes before the access; a violation
+// raises status[2] (a plain store: an atomicAdd on the host-mapped word made the instrumented kernels hang although it never
+// executed -- profiles/README_r2.md) and the access is skipped. compute-sanitizer is closed on this pool, this is the memcheck stand-in.
 #ifndef RD_BOUNDS_CHECK
 #define RD_BOUNDS_CHECK 0
 #endif
 #if RD_BOUNDS_CHECK && defined(__CUDA_ARCH__)
-#define RD_BOUND(ok, st, action) do { if (!(ok)) { if (st) atomicAdd((st) + 2, 1u); action; } } while (0)
+#define RD_BOUND(ok, st, action) do { if (!(ok)) { if (st) (st)[2] = 1u; action; } } while (0)
 #else
 #define RD_BOUND(ok, st, action) do { } while (0)
 #endif

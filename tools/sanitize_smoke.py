@@ -4,7 +4,17 @@ pack / unpack kernels, a deferred small build, a general (multi-launch) build an
 import os
 import sys
 
+import faulthandler
+
 import numpy as np
+
+if os.environ.get("RD_SMOKE_WATCHDOG"):
+    faulthandler.dump_traceback_later(int(os.environ["RD_SMOKE_WATCHDOG"]), exit=True)
+
+
+def stage(msg):
+    print("[smoke] " + msg, flush=True)
+
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -25,16 +35,22 @@ rd.BindPipeline(plt, pipe)
 rd.BindDescriptorSet(plt, ds.descriptors)
 rd.TraceRays(plt, 0, 0, 0, w, h)
 plain = ds.read_image()
+stage("inline done")
 plt.set_option("wavefront", 1)
 ds.set_rtprop(0, 2, 3)
 rd.TraceRays(plt, 0, 0, 0, w, h)
 wave = ds.read_image()
+stage("wavefront done")
 mask = rd.TraceRaysUnits(plt, w, h, 6, 300)
+stage("units wavefront done")
 plt.sync()
 plt.set_option("wavefront", 0)
-rd.TraceRaysSteal(plt, w, h, 301, 64)
+if "steal" not in os.environ.get("RD_SMOKE_SKIP", ""):
+    rd.TraceRaysSteal(plt, w, h, 301, 64)
+stage("steal done")
 plt.sync()
 mask2 = rd.TraceRaysUnits(plt, w, h, 9, 302)
+stage("units inline done")
 plt.sync()
 dst = rd.CreateBuffer(plt, w * h * 4)
 for r in range(3):
@@ -46,11 +62,13 @@ ds.set_rtprop(0, 2, 3)
 rd.TraceRays(plt, 0, 0, 0, w, h)
 rd.ReadBuffer(plt, ds.rdImage, w * h * 4, host.data_ptr())
 rd.StreamBufferToHost(plt, None, None)
+stage("banded done")
 hf = scenes.heightfield_scene(72, 64, 48)       # 10 368 triangles: the general multi-launch build
 t2, _ = scenes.build_scene(plt, hf)
 rays = scenes.pinhole_rays(hf.camera, stride=2)
 hitA, hitB = rd.trace_host_rays(plt, t2, rays)
 first, _ = rd.trace_host_rays(plt, t2, rays, rd.TRACE_TERMINATE_ON_FIRST_HIT)
+stage("ray lists done")
 # determinism: the wavefront frame (atomics in the queues, the sort and the compaction) rendered five more times
 plt.set_option("wavefront", 1)
 frames = []
