@@ -304,7 +304,8 @@ __global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollap
 {
     __shared__ rd_u32 sCount;
     RdCollapseItem* cur = itemsA;
-    if (threadIdx.x == 0) { itemsA[0] = rootItem; sCount = 1u; }
+    // non-finite input (flagged by rd_k_centroid_bounds): the build is refused by the host, nothing is collapsed
+    if (threadIdx.x == 0) { itemsA[0] = rootItem; sCount = bounds[6] ? 0u : 1u; }
     O.next = itemsB;
     __syncthreads();
     rd_u32 levels = 0;

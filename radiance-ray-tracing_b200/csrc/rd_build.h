@@ -313,6 +313,10 @@ RD_HD void rd_collapse_item(const RdBinTree& T, const RdCollapseOut& O, RdCollap
                 if (score > bscore) { bscore = score; bk = k; bs = s; }
             }
         }
+        if (bk < 0) {   // every remaining score is NaN (non-finite boxes): any free slot will do, nothing may index with -1
+            for (int k = 0; k < n && bk < 0; ++k) if (slotOf[k] < 0) bk = k;
+            for (int q = 0; q < 8 && bs < 0; ++q) if (childAt[q] == RD_INVALID) bs = q;
+        }
         slotOf[bk] = bs; childAt[bs] = ch[bk];
     }
 #if RD_NODE_F32
