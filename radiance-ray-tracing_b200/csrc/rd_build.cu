@@ -307,6 +307,8 @@ __global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollap
     // non-finite input (flagged by rd_k_centroid_bounds): the build is refused by the host, nothing is collapsed
     if (threadIdx.x == 0) { itemsA[0] = rootItem; sCount = bounds[6] ? 0u : 1u; }
     O.next = itemsB;
+    // ... but the leaf-record gather that follows on the stream still reads leafPrim: give it valid primitive numbers
+    if (bounds[6]) for (rd_u32 i = threadIdx.x; i < T.n; i += blockDim.x) O.leafPrim[i] = i;
     __syncthreads();
     rd_u32 levels = 0;
     for (;;) {
