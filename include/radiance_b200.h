@@ -254,6 +254,18 @@ int rd_ray_count(rd_platform* p, uint64_t* out, int reset);
  * exclusive scan, run on host arrays in place. The parity tests compare them with numpy. */
 int rd_debug_sort_pairs(rd_platform* p, uint64_t* keys, uint32_t* vals, unsigned n, int bits);
 int rd_debug_exclusive_scan(rd_platform* p, uint32_t* data, unsigned n, uint32_t* total);
+/* No counterpart in the reference. The same pair sort (stable, by the low
+ * `bits` key bits, 8 per pass) for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc): inputs and outputs are DEVICE pointers the caller owns (n keys / n values each, outputs distinct from the
+ * inputs, inputs are left unchanged); the ping-pong buffers and digit tables are a file-scope static device array of the
+ * library (6.4 MB, held by every GPU that loads the library until exit), so the call performs no cudaMalloc / cudaFree and
+ * no host synchronisation -- it is asynchronous on the platform stream (rd_platform_sync to wait). n is limited to
+ * RD_SORT_NOALLOC_MAX_PAIRS; more is RD_E_ARG with the limit in rd_last_error(). All calls on one GPU share the array:
+ * calls that overlap on the GPU (two platforms / streams of one device) race; calls on one platform are stream-ordered.
+ * The first call on a device resolves the array's address (cudaGetSymbolAddress); make it outside a capture. */
+#define RD_SORT_NOALLOC_MAX_PAIRS (1u << 18)
+int rd_sort_pairs_noalloc(rd_platform* p, const uint64_t* dkeysIn, const uint32_t* dvalsIn, uint64_t* dkeysOut,
+                          uint32_t* dvalsOut, unsigned n, int bits);
 /* number of kernels this library launched since platform creation */
 uint64_t rd_launch_count(rd_platform* p);
 

@@ -6,6 +6,7 @@
 #include <float.h>
 #include <string.h>
 #include <stdlib.h>
+#include <mutex>
 #include "rd_internal.h"
 #include "rd_build.h"
 #include "rd_sort.h"
@@ -816,6 +817,86 @@ extern "C" int rd_debug_exclusive_scan(rd_platform* p, uint32_t* data, unsigned 
     if (n) RD_CUDA(cudaMemcpyAsync(data, d, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
     if (total) RD_CUDA(cudaMemcpyAsync(total, dt, 4, cudaMemcpyDeviceToHost, st));
     RD_CUDA(cudaStreamSynchronize(st));
+    RD_CUDA(cudaGetLastError());
+    return RD_OK;
+}
+
+// ---- rd_sort_pairs_noalloc ------------------------------------------------------------------------------------------
+// The pair sort of rd_sort.h (count / scan / scatter per 8-bit digit) for callers that cannot allocate: its ping-pong
+// buffers, the digit table and the scan counters live in ONE file-scope device array, so the call touches no allocator.
+// No counterpart in the reference (include/radiance_b200.h).
+// Layout of the array (RD_NOALLOC_MAX_PAIRS = 2^18 pairs): keys A | keys B | values A | values B | table | scan counters.
+// Nothing in it has to start at zero: every pass's count kernel writes all 256 x blocks table entries and the scan writes
+// every tile sum it later reads, so stale contents of the previous call are never read. Two calls that overlap on the GPU
+// (different streams / platforms of one device) race on the array.
+#define RD_NOALLOC_MAX_PAIRS RD_SORT_NOALLOC_MAX_PAIRS
+#define RD_NOALLOC_TABLE_COUNT (256u * (RD_NOALLOC_MAX_PAIRS / RD_SORT_TILE))        // 16384 counters
+#define RD_NOALLOC_SCAN_COUNT 64u                                                     // >= rd_scan_scratch_count(16384) = 9
+#define RD_NOALLOC_OFF_KEYS_B ((size_t)RD_NOALLOC_MAX_PAIRS * 8u)
+#define RD_NOALLOC_OFF_VALS_A ((size_t)RD_NOALLOC_MAX_PAIRS * 16u)
+#define RD_NOALLOC_OFF_VALS_B ((size_t)RD_NOALLOC_MAX_PAIRS * 20u)
+#define RD_NOALLOC_OFF_TABLE ((size_t)RD_NOALLOC_MAX_PAIRS * 24u)
+#define RD_NOALLOC_OFF_SCAN (RD_NOALLOC_OFF_TABLE + (size_t)RD_NOALLOC_TABLE_COUNT * 4u)
+#define RD_NOALLOC_BYTES (RD_NOALLOC_OFF_SCAN + (size_t)RD_NOALLOC_SCAN_COUNT * 4u)  // 6 357 248 B per GPU that loads the library
+static __device__ __align__(256) unsigned char rd_noalloc_scratch[RD_NOALLOC_BYTES];
+
+#define RD_NOALLOC_MAX_DEVICES 64
+static void* g_noallocBase[RD_NOALLOC_MAX_DEVICES];   // device address of rd_noalloc_scratch per device (the symbol itself is only a host stand-in)
+static std::mutex g_noallocMutex;
+
+// the array's address on `device`, which must be current; resolved once per device
+static int rd_noalloc_base(int device, unsigned char** base)
+{
+    if (device < 0 || device >= RD_NOALLOC_MAX_DEVICES) { rd_set_error("rd_sort_pairs_noalloc: device %d out of range", device); return RD_E_ARG; }
+    std::lock_guard<std::mutex> lock(g_noallocMutex);
+    if (!g_noallocBase[device]) {
+        void* ptr = 0;
+        RD_CUDA(cudaGetSymbolAddress((void**)&ptr, rd_noalloc_scratch));
+        if (!ptr || ((uintptr_t)ptr & 255u)) { rd_set_error("rd_sort_pairs_noalloc: scratch symbol resolved to %p", ptr); return RD_E_CUDA; }
+        g_noallocBase[device] = ptr;
+    }
+    *base = (unsigned char*)g_noallocBase[device];
+    return RD_OK;
+}
+
+extern "C" int rd_sort_pairs_noalloc(rd_platform* p, const uint64_t* dkeysIn, const uint32_t* dvalsIn, uint64_t* dkeysOut,
+                                     uint32_t* dvalsOut, unsigned n, int bits)
+{
+    if (!p || bits < 1 || bits > 64 || (n && (!dkeysIn || !dvalsIn || !dkeysOut || !dvalsOut))) { rd_set_error("rd_sort_pairs_noalloc: bad argument"); return RD_E_ARG; }
+    if (n > RD_NOALLOC_MAX_PAIRS) {
+        rd_set_error("rd_sort_pairs_noalloc: n = %u exceeds the static scratch (at most %u pairs)", n, RD_NOALLOC_MAX_PAIRS);
+        return RD_E_ARG;
+    }
+    if (n && ((const void*)dkeysIn == (const void*)dkeysOut || (const void*)dvalsIn == (const void*)dvalsOut)) {
+        rd_set_error("rd_sort_pairs_noalloc: outputs must not alias inputs"); return RD_E_ARG;
+    }
+    if (!n) return RD_OK;
+    RD_CUDA(cudaSetDevice(p->device));
+    unsigned char* base = 0;
+    const int rc = rd_noalloc_base(p->device, &base);
+    if (rc != RD_OK) return rc;
+    cudaStream_t st = p->stream;
+    rd_u64* keysT[2] = { (rd_u64*)base, (rd_u64*)(base + RD_NOALLOC_OFF_KEYS_B) };
+    rd_u32* valsT[2] = { (rd_u32*)(base + RD_NOALLOC_OFF_VALS_A), (rd_u32*)(base + RD_NOALLOC_OFF_VALS_B) };
+    rd_u32* table = (rd_u32*)(base + RD_NOALLOC_OFF_TABLE);
+    rd_u32* scan = (rd_u32*)(base + RD_NOALLOC_OFF_SCAN);
+    // every pass runs (no histogram read-back, so no host synchronisation): pass 0 reads the caller's input, the last pass
+    // scatters into the caller's output, the passes between alternate over the two halves of the static array
+    const int passes = (bits + 7) / 8;
+    const rd_u32 blocks = rd_sort_blocks(n);
+    unsigned long long launches = 0;
+    const rd_u64* kin = (const rd_u64*)dkeysIn; const rd_u32* vin = dvalsIn;
+    for (int q = 0; q < passes; ++q) {
+        rd_u64* kout = q == passes - 1 ? (rd_u64*)dkeysOut : keysT[q & 1];
+        rd_u32* vout = q == passes - 1 ? dvalsOut : valsT[q & 1];
+        rd_k_sort_count<<<blocks, RD_SORT_THREADS, 0, st>>>(kin, n, 8 * q, table);
+        launches += 1;
+        rd_exclusive_scan_u32(st, table, table, 256u * blocks, scan, 0, &launches);
+        rd_k_sort_scatter<<<blocks, RD_SORT_THREADS, 0, st>>>(kin, vin, kout, vout, n, 8 * q, table);
+        launches += 1;
+        kin = kout; vin = vout;
+    }
+    p->launches += launches;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
 }

@@ -31,6 +31,7 @@ ABI_SYMBOLS = [
     "rd_debug_sort_pairs", "rd_debug_exclusive_scan", "rd_buffer_stream_to_host", "rd_status",
     "rd_comm_unique_id", "rd_comm_init", "rd_comm_adopt", "rd_comm_destroy", "rd_frame_gather", "rd_frame_gather_ranges",
     "rd_trace_rays_units", "rd_frame_gather_units", "rd_wf_timeline", "rd_debug_band_roundtrip", "rd_debug_bounds_violations",
+    "rd_sort_pairs_noalloc",
 ]
 
 
@@ -90,7 +91,7 @@ def lib():
             "rd_tlas_load": [vp, C.c_char_p, C.POINTER(vp)], "rd_tlas_load_memory": [vp, vp, sz, C.POINTER(vp), vp, vp],
             "rd_steal_counter_export": [vp, vp], "rd_steal_counter_import": [vp, vp], "rd_trace_rays_steal": [vp, u, u, u, u],
             "rd_steal_owned": [vp, vp, u, C.POINTER(u)], "rd_trace_rays_interleaved": [vp, u, u, u, u, u],
-            "rd_debug_sort_pairs": [vp, vp, vp, u, C.c_int], "rd_debug_exclusive_scan": [vp, vp, u, C.POINTER(u)],
+            "rd_debug_sort_pairs": [vp, vp, vp, u, C.c_int], "rd_sort_pairs_noalloc": [vp, vp, vp, vp, vp, u, C.c_int], "rd_debug_exclusive_scan": [vp, vp, u, C.POINTER(u)],
             "rd_tlas_save": [vp, vp, C.c_char_p], "rd_tlas_save_memory": [vp, vp, C.POINTER(vp), C.POINTER(sz)],
         }
         L.rd_free_host.argtypes, L.rd_free_host.restype = [vp], None
@@ -473,6 +474,16 @@ def debug_sort_pairs(plt, keys, vals, bits=64):
     k, v = np.ascontiguousarray(keys, np.uint64).copy(), np.ascontiguousarray(vals, np.uint32).copy()
     _check(lib().rd_debug_sort_pairs(plt.handle, k.ctypes.data, v.ctypes.data, k.size, bits))
     return k, v
+
+
+SORT_NOALLOC_MAX_PAIRS = 1 << 18
+
+
+def sort_pairs_noalloc(plt, keysIn, valsIn, keysOut, valsOut, n, bits=64):
+    """rd_sort_pairs_noalloc: the same sort on buffers in HBM (Buffer handles or raw device addresses) with its scratch in
+    the library's static device array -- no allocation, asynchronous on the platform stream."""
+    ptr = lambda b: b if isinstance(b, int) else lib().rd_handle_device_ptr(b.handle)
+    _check(lib().rd_sort_pairs_noalloc(plt.handle, ptr(keysIn), ptr(valsIn), ptr(keysOut), ptr(valsOut), n, bits))
 
 
 def debug_exclusive_scan(plt, data):
