@@ -33,10 +33,10 @@ __global__ void rd_k_tri_boxes(const float* verts, const rd_u32* idx, rd_u32 n, 
 }
 
 // bounds[0..2] = min centroid (ordered uint), bounds[3..5] = max centroid
-__global__ void rd_k_centroid_bounds(const RdF4* lo, const RdF4* hi, rd_u32 n, unsigned* bounds)
+__device__ __forceinline__ void rd_centroid_bounds_part(const RdF4* lo, const RdF4* hi, rd_u32 n, unsigned* bounds, rd_u32 first, rd_u32 stride)
 {
     float mn[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, mx[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-    for (rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    for (rd_u32 i = first; i < n; i += stride) {
         const RdF4 l = lo[i], h = hi[i];
         const float c[3] = {0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z)};
         // a NaN / Inf coordinate (or a box whose centre overflows) is refused by the host: bounds[6] = count of such primitives
@@ -59,10 +59,13 @@ __global__ void rd_k_centroid_bounds(const RdF4* lo, const RdF4* hi, rd_u32 n, u
     }
 }
 
-__global__ void rd_k_morton(const RdF4* lo, const RdF4* hi, rd_u32 n, const unsigned* bounds, rd_u64* keys, rd_u32* vals)
+__global__ void rd_k_centroid_bounds(const RdF4* lo, const RdF4* hi, rd_u32 n, unsigned* bounds)
 {
-    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    rd_centroid_bounds_part(lo, hi, n, bounds, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x);
+}
+
+__device__ __forceinline__ void rd_morton_item(const RdF4* lo, const RdF4* hi, rd_u32 i, const unsigned* bounds, rd_u64* keys, rd_u32* vals)
+{
     float cmin[3], cinv[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) {
@@ -73,6 +76,12 @@ __global__ void rd_k_morton(const RdF4* lo, const RdF4* hi, rd_u32 n, const unsi
     const RdF4 l = lo[i], h = hi[i];
     keys[i] = rd_morton63(0.5f * (l.x + h.x), 0.5f * (l.y + h.y), 0.5f * (l.z + h.z), cmin, cinv);
     vals[i] = i;
+}
+
+__global__ void rd_k_morton(const RdF4* lo, const RdF4* hi, rd_u32 n, const unsigned* bounds, rd_u64* keys, rd_u32* vals)
+{
+    rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) rd_morton_item(lo, hi, i, bounds, keys, vals);
 }
 
 __global__ void rd_k_leaf_boxes(RdBinTree T, const RdF4* plo, const RdF4* phi)
@@ -174,7 +183,7 @@ __global__ void rd_k_ploc_compact(RdPlocSide A, RdPlocSide B, rd_u32 m, const rd
 // Small inputs (the 4096 patch meshes of C4 have 2450 triangles each): all rounds in ONE block, the cluster arrays in
 // global memory, rounds separated by __syncthreads -- no launch / host round trip per round.
 #define RD_PLOC_SMALL_MAX 8192u
-__global__ void __launch_bounds__(1024) rd_k_ploc_small(RdBinTree T, RdPlocSide A, RdPlocSide B, rd_u32* nearest, int radius)
+__device__ __forceinline__ void rd_ploc_small_block(RdBinTree T, RdPlocSide A, RdPlocSide B, rd_u32* nearest, int radius)
 {
     __shared__ rd_u32 warpSum[32];
     __shared__ rd_u32 sBase, sNext;
@@ -251,6 +260,11 @@ __global__ void __launch_bounds__(1024) rd_k_ploc_small(RdBinTree T, RdPlocSide 
     }
 }
 
+__global__ void __launch_bounds__(1024) rd_k_ploc_small(RdBinTree T, RdPlocSide A, RdPlocSide B, rd_u32* nearest, int radius)
+{
+    rd_ploc_small_block(T, A, B, nearest, radius);
+}
+
 __global__ void rd_k_collapse(RdBinTree T, RdCollapseOut O, const RdCollapseItem* items, rd_u32 count)
 {
     rd_u32 i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -300,8 +314,8 @@ __global__ void rd_k_small_settle(const rd_u32* where, const rd_u64* keysA, cons
 }
 
 // all levels of the wide-node collapse in one block; summary = { nodes, leaf records, levels, non-finite boxes, root lo.xyz, root hi.xyz }
-__global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollapseOut O, RdCollapseItem* itemsA, RdCollapseItem* itemsB,
-                                                          RdCollapseItem rootItem, const unsigned* bounds, rd_u32* summary)
+__device__ __forceinline__ void rd_collapse_small_block(RdBinTree T, RdCollapseOut O, RdCollapseItem* itemsA, RdCollapseItem* itemsB,
+                                                        RdCollapseItem rootItem, const unsigned* bounds, rd_u32* summary)
 {
     __shared__ rd_u32 sCount;
     RdCollapseItem* cur = itemsA;
@@ -331,6 +345,12 @@ __global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollap
         summary[4] = RD_F2U(T.lo[rootSlot].x); summary[5] = RD_F2U(T.lo[rootSlot].y); summary[6] = RD_F2U(T.lo[rootSlot].z);
         summary[7] = RD_F2U(T.hi[rootSlot].x); summary[8] = RD_F2U(T.hi[rootSlot].y); summary[9] = RD_F2U(T.hi[rootSlot].z);
     }
+}
+
+__global__ void __launch_bounds__(256) rd_k_collapse_small(RdBinTree T, RdCollapseOut O, RdCollapseItem* itemsA, RdCollapseItem* itemsB,
+                                                          RdCollapseItem rootItem, const unsigned* bounds, rd_u32* summary)
+{
+    rd_collapse_small_block(T, O, itemsA, itemsB, rootItem, bounds, summary);
 }
 
 // deferredSummary != 0: nothing waits for the device -- the nodes go straight into an allocation of the worst-case size
@@ -549,14 +569,16 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
 // count, the root box and the non-finite-input flag arrive in host-mapped memory; rd_blas_resolve reads them the first time
 // they are needed (rd_blas_stats, rd_tlas_build, rd_blas_free) and moves the nodes into an exact-size allocation. An error
 // of a deferred build (NaN / Inf vertices) is therefore reported by that later call. Option "async_build" = 0 resolves at once.
-#define RD_BUILD_STREAMS 8
+#define RD_BUILD_STREAMS 32
 #define RD_SUMMARY_WORDS 16
 #define RD_SUMMARY_CHUNK 4096u
 
 static int rd_build_stream(rd_platform* p, cudaStream_t* out)
 {
     if (p->buildStreams.empty()) {
-        for (int k = 0; k < RD_BUILD_STREAMS; ++k) { cudaStream_t s; RD_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); p->buildStreams.push_back(s); }
+        int count = RD_BUILD_STREAMS;
+        if (const char* e = getenv("RD_BUILD_STREAMS")) { count = atoi(e); if (count < 1) count = 1; if (count > 64) count = 64; }   // developer knob
+        for (int k = 0; k < count; ++k) { cudaStream_t s; RD_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); p->buildStreams.push_back(s); }
     }
     *out = p->buildStreams[p->buildNext++ % p->buildStreams.size()];
     return RD_OK;
@@ -596,6 +618,158 @@ int rd_blas_resolve(rd_platform* p, rd_blas* b)
     RD_CUDA(cudaMemcpyAsync(exact, b->nodes, (size_t)b->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, p->stream));
     RD_CUDA(cudaFreeAsync(b->nodes, p->stream));
     b->nodes = exact;
+    return RD_OK;
+}
+
+// ---- small triangle meshes: the WHOLE bottom-level build in one launch ----------------------------------------------------
+// Every step of the small path above runs in one block already; a scene of thousands of small meshes (C4: 4096 patch meshes)
+// then pays for the ~10 launches and ~12 stream-ordered allocations per mesh on the host. Here the steps are the phases of ONE
+// 1024-thread block (primitive boxes, centroid bounds, Morton codes, sort, leaf boxes, PLOC, collapse, leaf-record gather;
+// the same device functions, so the structure is bit-identical), over ONE scratch allocation that also holds the uploaded mesh.
+struct RdSmallBuild {
+    const float* verts; const rd_u32* idx; rd_u32 n; int radius;
+    RdF4 *plo, *phi;
+    unsigned* bounds; rd_u32* counters; rd_u32* where;
+    rd_u64 *keysA, *keysB; rd_u32 *valsA, *valsB;
+    RdBinTree T; RdPlocSide A, B; rd_u32* nearest;
+    RdCollapseOut O; RdCollapseItem *itemsA, *itemsB;
+    rd_u32* summary; RdTri* tris;
+};
+
+__global__ void __launch_bounds__(1024) rd_k_small_build_fused(const RdSmallBuild S)
+{
+    const rd_u32 tid = threadIdx.x, nth = blockDim.x, n = S.n;
+    if (tid < 3) S.bounds[tid] = 0xffffffffu;
+    else if (tid < 8) S.bounds[tid] = 0u;
+    if (tid == 0) { S.counters[0] = 1u; S.counters[1] = 0u; S.counters[2] = 0u; S.counters[3] = 0u; }
+    for (rd_u32 q = tid; q < n; q += nth) rd_prim_box_tri(S.verts, S.idx, q, S.plo, S.phi);
+    __syncthreads();
+    rd_centroid_bounds_part(S.plo, S.phi, n, S.bounds, tid, nth);
+    __syncthreads();
+    for (rd_u32 i = tid; i < n; i += nth) rd_morton_item(S.plo, S.phi, i, S.bounds, S.keysA, S.valsA);
+    __syncthreads();
+    if (n > 1u) {
+        rd_sort_small_block(S.keysA, S.valsA, S.keysB, S.valsB, n, 8, S.where);
+        __syncthreads();
+        if (*S.where == 0u) for (rd_u32 i = tid; i < n; i += nth) { S.keysB[i] = S.keysA[i]; S.valsB[i] = S.valsA[i]; }
+    } else if (tid == 0) { S.keysB[0] = S.keysA[0]; S.valsB[0] = S.valsA[0]; }
+    __syncthreads();
+    for (rd_u32 i = tid; i < n; i += nth) { const rd_u32 q = S.T.prim[i]; S.T.lo[n - 1u + i] = S.plo[q]; S.T.hi[n - 1u + i] = S.phi[q]; }
+    __syncthreads();
+    if (n > 1u) rd_ploc_small_block(S.T, S.A, S.B, S.nearest, S.radius);
+    __syncthreads();
+    RdCollapseItem rootItem; rootItem.wide = 0; rootItem.bin = (n == 1u) ? (RD_BIN_LEAF | 0u) : 0u;
+    rd_collapse_small_block(S.T, S.O, S.itemsA, S.itemsB, rootItem, S.bounds, S.summary);
+    __syncthreads();
+    for (rd_u32 r = tid; r < n; r += nth) rd_gather_tri(S.verts, S.idx, S.O.leafPrim, S.tris, r);
+}
+
+// Page-locked staging for the uploads of small meshes. cudaMemcpyAsync from pageable memory costs ~20 us of host time per call
+// (two per mesh: 40 of the ~50 us a 2450-triangle mesh took, profiles/exp_smallbuilds_r2g.log); a memcpy into a pinned ring
+// and ONE asynchronous copy of vertices + indices costs ~5. A segment is reused only after everything copied out of it has
+// been consumed: leaving a segment records a fence event on every side stream.
+#define RD_UPLOAD_SEGMENTS 4
+#define RD_UPLOAD_SEGMENT_BYTES ((size_t)8 << 20)
+static int rd_upload_stage(rd_platform* p, size_t bytes, unsigned char** host)
+{
+    *host = 0;
+    if (bytes > RD_UPLOAD_SEGMENT_BYTES || getenv("RD_BUILD_PAGEABLE")) return RD_OK;   // caller copies from pageable memory (developer knob)
+    if (!p->upHost) {
+        void* h = 0;
+        RD_CUDA(cudaHostAlloc(&h, RD_UPLOAD_SEGMENTS * RD_UPLOAD_SEGMENT_BYTES, cudaHostAllocDefault));
+        p->upHost = (unsigned char*)h; p->upSegBytes = RD_UPLOAD_SEGMENT_BYTES; p->upSeg = 0; p->upOff = 0;
+    }
+    if (p->upOff + bytes > p->upSegBytes) {
+        std::vector<cudaEvent_t>& fence = p->upFence[p->upSeg];
+        while (fence.size() < p->buildStreams.size()) { cudaEvent_t e; RD_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); fence.push_back(e); }
+        for (size_t k = 0; k < p->buildStreams.size(); ++k) RD_CUDA(cudaEventRecord(fence[k], p->buildStreams[k]));
+        p->upFenced[p->upSeg] = true;
+        p->upSeg = (p->upSeg + 1u) % RD_UPLOAD_SEGMENTS; p->upOff = 0;
+        if (p->upFenced[p->upSeg]) {
+            for (cudaEvent_t e : p->upFence[p->upSeg]) RD_CUDA(cudaEventSynchronize(e));
+            p->upFenced[p->upSeg] = false;
+        }
+    }
+    *host = p->upHost + (size_t)p->upSeg * p->upSegBytes + p->upOff;
+    p->upOff += (bytes + 255u) & ~(size_t)255u;
+    return RD_OK;
+}
+
+// hverts / hidx != 0: the mesh is uploaded into the head of the same scratch block (dverts / didx are ignored)
+static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, const float* hverts, unsigned nv, const uint32_t* hidx,
+                                     const float* dverts, const uint32_t* didx, unsigned nt, rd_blas** out)
+{
+    const size_t n = nt, ni = n > 1 ? n - 1 : 1;
+    size_t off = 0;
+    auto carve = [&off](size_t bytes) { const size_t at = off; off += (bytes + 255u) & ~(size_t)255u; return at; };
+    const size_t oVerts = carve(hverts ? (size_t)nv * 12 : 0), oIdx = carve(hidx ? n * 12 : 0);
+    const size_t oPlo = carve(n * 16), oPhi = carve(n * 16), oBounds = carve(8 * 4), oCounters = carve(4 * 4), oWhere = carve(4);
+    const size_t oKeysA = carve(n * 8), oKeysB = carve(n * 8), oValsA = carve(n * 4), oValsB = carve(n * 4);
+    const size_t oLeft = carve(ni * 4), oRight = carve(ni * 4), oFirst = carve(ni * 4), oLast = carve(ni * 4);
+    const size_t oParent = carve(2 * n * 4), oCount = carve(ni * 4);
+    const size_t oLo = carve(2 * n * 16), oHi = carve(2 * n * 16), oCost = carve(8 * ni * 4), oDec = carve(8 * ni);
+    const size_t oARef = carve(n * 4), oALo = carve(n * 16), oAHi = carve(n * 16);
+    const size_t oBRef = carve(n * 4), oBLo = carve(n * 16), oBHi = carve(n * 16), oNearest = carve(n * 4);
+    const size_t oItemsA = carve((n + 1) * sizeof(RdCollapseItem)), oItemsB = carve((n + 1) * sizeof(RdCollapseItem)), oLeafPrim = carve(n * 4);
+    RdTmp tmp(st);
+    char* base;
+    RD_CUDA(tmp.alloc(&base, off));
+    if (hidx) {
+        // vertices and indices sit at the head of the block in the layout of the staging copy: one transfer
+        unsigned char* stage = 0;
+        int src = rd_upload_stage(p, oIdx + n * 12, &stage);
+        if (src) return src;
+        if (stage) {
+            if (nv) memcpy(stage + oVerts, hverts, (size_t)nv * 12);
+            memcpy(stage + oIdx, hidx, n * 12);
+            RD_CUDA(cudaMemcpyAsync(base, stage, oIdx + n * 12, cudaMemcpyHostToDevice, st));
+        } else {
+            if (nv) RD_CUDA(cudaMemcpyAsync(base + oVerts, hverts, (size_t)nv * 12, cudaMemcpyHostToDevice, st));
+            RD_CUDA(cudaMemcpyAsync(base + oIdx, hidx, n * 12, cudaMemcpyHostToDevice, st));
+        }
+    }
+    volatile rd_u32* hostSummary = 0; rd_u32* devSummary = 0;
+    int rc = rd_summary_slot(p, &hostSummary, &devSummary);
+    if (rc) return rc;
+    rd_blas* b = new rd_blas();
+    memset(b, 0, sizeof(*b));
+    b->owner = p; b->triCount = nt;
+    if (cudaMallocAsync(&b->nodes, (n + 1) * sizeof(RdNode8), st) != cudaSuccess || cudaMallocAsync(&b->tris, n * sizeof(RdTri), st) != cudaSuccess) {
+        rd_set_error("rd_blas_build: %s", cudaGetErrorString(cudaGetLastError()));
+        if (b->nodes) cudaFreeAsync(b->nodes, st);
+        delete b; return RD_E_CUDA;
+    }
+    RdSmallBuild S;
+    S.verts = hverts ? (const float*)(base + oVerts) : dverts; S.idx = hidx ? (const rd_u32*)(base + oIdx) : didx; S.n = nt;
+    S.radius = 32;
+    if (const char* e = getenv("RD_PLOC_RADIUS")) { S.radius = atoi(e); if (S.radius < 1) S.radius = 1; }
+    S.plo = (RdF4*)(base + oPlo); S.phi = (RdF4*)(base + oPhi);
+    S.bounds = (unsigned*)(base + oBounds); S.counters = (rd_u32*)(base + oCounters); S.where = (rd_u32*)(base + oWhere);
+    S.keysA = (rd_u64*)(base + oKeysA); S.keysB = (rd_u64*)(base + oKeysB); S.valsA = (rd_u32*)(base + oValsA); S.valsB = (rd_u32*)(base + oValsB);
+    RdBinTree& T = S.T;
+    T.n = nt; T.keys = S.keysB; T.prim = S.valsB;
+    T.left = (rd_u32*)(base + oLeft); T.right = (rd_u32*)(base + oRight); T.first = (rd_u32*)(base + oFirst); T.last = (rd_u32*)(base + oLast);
+    T.parent = (rd_u32*)(base + oParent); T.arrive = 0; T.count = (rd_u32*)(base + oCount);
+    T.lo = (RdF4*)(base + oLo); T.hi = (RdF4*)(base + oHi); T.cost = (float*)(base + oCost); T.dec = (rd_u8*)(base + oDec);
+    S.A.ref = (rd_u32*)(base + oARef); S.A.lo = (RdF4*)(base + oALo); S.A.hi = (RdF4*)(base + oAHi);
+    S.B.ref = (rd_u32*)(base + oBRef); S.B.lo = (RdF4*)(base + oBLo); S.B.hi = (RdF4*)(base + oBHi);
+    S.nearest = (rd_u32*)(base + oNearest);
+    S.O.nodes = b->nodes; S.O.leafPrim = (rd_u32*)(base + oLeafPrim); S.O.counters = S.counters; S.O.next = 0;
+    S.itemsA = (RdCollapseItem*)(base + oItemsA); S.itemsB = (RdCollapseItem*)(base + oItemsB);
+    S.summary = devSummary; S.tris = b->tris;
+    rd_k_small_build_fused<<<1, 1024, 0, st>>>(S);
+    p->launches += 1;
+    b->pending = 1; b->summary = hostSummary;
+    if (cudaGetLastError() != cudaSuccess || cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventRecord(b->done, st) != cudaSuccess) {
+        rd_set_error("rd_blas_build: %s", cudaGetErrorString(cudaGetLastError()));
+        cudaFreeAsync(b->nodes, st); cudaFreeAsync(b->tris, st); delete b; return RD_E_CUDA;
+    }
+    if (!p->optAsyncBuild) {
+        rc = rd_blas_resolve(p, b);
+        if (rc) { cudaFree(b->nodes); cudaFree(b->tris); delete b; return rc; }
+    }
+    *out = b;
     return RD_OK;
 }
 
@@ -656,6 +830,7 @@ extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigne
     RD_CUDA(cudaEventRecord(ready, p->stream));
     RD_CUDA(cudaStreamWaitEvent(st, ready, 0));
     cudaEventDestroy(ready);
+    if (!getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, 0, nv, 0, dverts, didx, nt, out);
     return rd_blas_build_on(p, st, true, dverts, didx, nt, out);
 }
 
@@ -668,6 +843,7 @@ extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, co
     const bool deferred = rd_build_deferrable(nt);
     cudaStream_t st = p->stream;
     if (deferred) { int rc = rd_build_stream(p, &st); if (rc) return rc; }
+    if (deferred && !getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, verts, nv, idx, 0, 0, nt, out);   // developer knob: the multi-launch small path
     RdTmp tmp(st);
     float* dv; uint32_t* di;
     RD_CUDA(tmp.alloc(&dv, (size_t)nv * 3)); RD_CUDA(tmp.alloc(&di, (size_t)nt * 3));

@@ -27,7 +27,9 @@ static inline rd_u32 rd_host_atomic_add_(rd_u32* p, rd_u32 v) { rd_u32 o = *p; *
 #define RD_CLZ64(x) ((x) ? __builtin_clzll(x) : 64)
 #endif
 
-#define RD_LEAF_MAX 3            // primitives per leaf slot (unary count in 3 meta bits)
+#ifndef RD_LEAF_MAX
+#define RD_LEAF_MAX 3            // primitives per leaf slot (one bit of the slot's leaf nibble each: at most 4)
+#endif
 #define RD_BIN_LEAF 0x80000000u  // binary child reference: top bit = leaf, low bits = sorted position
 
 // Binary hierarchy over n sorted primitives (Karras 2012 or PLOC, rd_build.cu): n-1 inner nodes [0, n-2], node 0 = root.

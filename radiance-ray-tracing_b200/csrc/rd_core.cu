@@ -81,6 +81,8 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     rd_comm_destroy(p);
     for (cudaStream_t bs : p->buildStreams) { cudaStreamSynchronize(bs); cudaStreamDestroy(bs); }
     for (uint32_t* hsum : p->summaryHost) cudaFreeHost(hsum);
+    for (int k = 0; k < 4; ++k) for (cudaEvent_t e : p->upFence[k]) cudaEventDestroy(e);
+    if (p->upHost) cudaFreeHost(p->upHost);
     for (cudaEvent_t e : p->tlEvents) cudaEventDestroy(e);
     if (p->unitSlots) { cudaFreeHost((void*)p->unitSlots); cudaEventDestroy(p->unitEvent); }
     rd_wf_release(p);

@@ -84,6 +84,10 @@ struct rd_platform {
     std::vector<cudaStream_t> buildStreams; size_t buildNext;   // side streams of deferred small bottom-level builds
     std::vector<uint32_t*> summaryHost, summaryDev; size_t summaryUsed;   // host-mapped build summaries, RD_SUMMARY_CHUNK per chunk
     long optAsyncBuild, optPrecDiv, optL2Persist;
+    // page-locked staging ring of the small-mesh uploads (rd_build.cu): RD_UPLOAD_SEGMENTS segments, a segment is reused once the
+    // fence events recorded on every side stream when it was left have fired
+    unsigned char* upHost; size_t upSegBytes, upOff; unsigned upSeg;
+    std::vector<cudaEvent_t> upFence[4]; bool upFenced[4];
     void* comm;                                  // RdComm* (rd_comm.cu): the NCCL communicator of the multi-GPU frame gather
     volatile unsigned* unitSlots; unsigned* unitSlotsDev; cudaEvent_t unitEvent;   // rd_trace_rays_units: unit numbers land in host-mapped memory
     long optWfTimeline; std::vector<cudaEvent_t> tlEvents; std::vector<int> tlCodes; size_t tlUsed;   // rd_wf_timeline

@@ -187,7 +187,9 @@ __global__ void __launch_bounds__(RD_SORT_THREADS) rd_k_sort_scatter(const rd_u6
 }
 
 // all passes in one block, for small inputs; result ends in (keysA, valsA) or (keysB, valsB): returns via *where (0 = A, 1 = B)
-__global__ void __launch_bounds__(1024) rd_k_sort_small(rd_u64* keysA, rd_u32* valsA, rd_u64* keysB, rd_u32* valsB, rd_u32 n, int passes, rd_u32* where)
+// (the body is a device function so that the fused small-mesh build of rd_build.cu can run it as one of its phases;
+// every thread of a 1024-thread block must call it)
+__device__ __forceinline__ void rd_sort_small_block(rd_u64* keysA, rd_u32* valsA, rd_u64* keysB, rd_u32* valsB, rd_u32 n, int passes, rd_u32* where)
 {
     __shared__ rd_u32 counts[32][256];     // [warp][digit] of the current chunk
     __shared__ rd_u32 digitStart[256];     // running output position per digit
@@ -235,6 +237,11 @@ __global__ void __launch_bounds__(1024) rd_k_sort_small(rd_u64* keysA, rd_u32* v
         __syncthreads();
     }
     if (tid == 0) *where = side;
+}
+
+__global__ void __launch_bounds__(1024) rd_k_sort_small(rd_u64* keysA, rd_u32* valsA, rd_u64* keysB, rd_u32* valsB, rd_u32 n, int passes, rd_u32* where)
+{
+    rd_sort_small_block(keysA, valsA, keysB, valsB, n, passes, where);
 }
 
 struct RdSortScratch {

@@ -213,7 +213,7 @@ def BuildAccelStruct(plt, arg):
     instances = list(arg)
     arr = (InstanceDesc * max(1, len(instances)))()
     for k, inst in enumerate(instances):
-        arr[k].transform[:] = [float(x) for x in inst.transform.reshape(16)]
+        C.memmove(arr[k].transform, inst.transform.ctypes.data, 64)   # (4,4) float32, C-contiguous (Instance.__init__)
         arr[k].SBTOffset, arr[k].customInstanceID = inst.SBTOffset, inst.customInstanceID
         arr[k].bottomAccelStruct = inst.bottomAccelStruct.handle
     out = C.c_void_p()

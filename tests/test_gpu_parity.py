@@ -666,6 +666,46 @@ def test_streamed_readback_delivers_the_same_frame(pkg, plt):
     assert np.array_equal(host.numpy().reshape(360, 640, 4), ds.read_image())
 
 
+def test_fused_small_build_is_the_multi_launch_small_build(pkg, plt):
+    """Meshes of up to 8192 triangles are built by ONE launch (csrc/rd_build.cu, rd_k_small_build_fused): the same device
+    functions as the multi-launch small path (developer knob RD_BUILD_UNFUSED), so the structure must be the same tree --
+    compared through node / level counts, the size of the exported blob and the hits of a ray list; also built from device arrays."""
+    import os
+    rd, scenes = pkg.rd, pkg.scenes
+    rng = np.random.default_rng(11)
+    for nt in (1, 2, 7, 300, 2450, 8192):
+        v = rng.normal(size=(nt * 3, 3)).astype(np.float32)
+        t = rng.permutation(nt * 3).astype(np.uint32).reshape(nt, 3)
+        rays = np.zeros((256, 8), np.float32)
+        rays[:, 0:3] = rng.normal(size=(256, 3)) * 3.0
+        rays[:, 4:7] = v[rng.integers(0, nt * 3, 256)] - rays[:, 0:3]
+        rays[:, 3], rays[:, 7] = 1e-3, 1e3
+        got = {}
+        for mode in ("fused", "unfused", "fused_device"):
+            os.environ.pop("RD_BUILD_UNFUSED", None)
+            if mode == "unfused":
+                os.environ["RD_BUILD_UNFUSED"] = "1"
+            try:
+                if mode == "fused_device":
+                    dv, di = rd.CreateBuffer(plt, v.nbytes), rd.CreateBuffer(plt, t.nbytes)
+                    rd.WriteBuffer(plt, dv, v.nbytes, v)
+                    rd.WriteBuffer(plt, di, t.nbytes, t)
+                    out = rd.C.c_void_p()
+                    rd._check(rd.lib().rd_blas_build_device(plt.handle, dv.device_ptr(), nt * 3, di.device_ptr(), nt, rd.C.byref(out)))
+                    blas = rd.BottomAccelStruct(plt, out)
+                else:
+                    blas = rd.BuildAccelStruct(plt, rd.Mesh(v, t))
+            finally:
+                os.environ.pop("RD_BUILD_UNFUSED", None)
+            tlas = rd.BuildAccelStruct(plt, [rd.Instance(np.eye(4), 0, 0, blas)])
+            hitA, hitB = rd.trace_host_rays(plt, tlas, rays)
+            # node and leaf-record NUMBERS come from atomic counters (allocation order may differ between a 256- and a
+            # 1024-thread block), so the comparison is on what does not depend on them: counts, levels, blob size, hits
+            got[mode] = (blas.stats(), rd.TopAccelStructToBytes(plt, tlas).size, hitA.tobytes(), hitB.tobytes())
+        assert got["fused"] == got["unfused"], "fused small build differs from the multi-launch one at nt=%d" % nt
+        assert got["fused_device"] == got["unfused"], "fused small build from device arrays differs at nt=%d" % nt
+
+
 def test_non_finite_vertices_do_not_hang_the_build(pkg, plt):
     """a NaN / Inf vertex made a cluster unmergeable and the one-block PLOC loop of small meshes never ended.
     Areas are now sanitised (a round always merges), and primitives with non-finite boxes are refused with RD_E_ARG."""
