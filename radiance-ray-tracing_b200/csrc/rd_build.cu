@@ -423,155 +423,6 @@ static int rd_build_wide_bvh_small(rd_platform* p, cudaStream_t st, const RdF4* 
     return RD_OK;
 }
 
-// ---- experiment (developer knob RD_BUILD_COMPLETE = primitives per leaf slot, 1..4): complete 8-ary tree over the Morton order --
-// Every level splits the sorted primitives into aligned blocks of 8 children, so ALL leaves sit at the same depth: the lanes of a
-// warp of coherent rays reach their triangles in the same iteration (the triangle phase of the walk runs at 5 of 32 lanes on the
-// SAH tree because they do not). No SAH, no clustering: topology quality is that of a linear BVH.
-#if !RD_NODE_F32
-__global__ void rd_k_ct_slot_boxes(const rd_u32* prim, const RdF4* plo, const RdF4* phi, rd_u32 n, rd_u32 per, rd_u32 slots, RdF4* lo, RdF4* hi)
-{
-    const rd_u32 j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= slots) return;
-    RdF4 l, h; l.x = l.y = l.z = 3.0e38f; h.x = h.y = h.z = -3.0e38f; l.w = h.w = 0.0f;
-    for (rd_u32 t = 0; t < per && per * j + t < n; ++t) {
-        const rd_u32 q = prim[per * j + t];
-        const RdF4 a = plo[q], b = phi[q];
-        l.x = fminf(l.x, a.x); l.y = fminf(l.y, a.y); l.z = fminf(l.z, a.z);
-        h.x = fmaxf(h.x, b.x); h.y = fmaxf(h.y, b.y); h.z = fmaxf(h.z, b.z);
-    }
-    lo[j] = l; hi[j] = h;
-}
-
-__global__ void rd_k_ct_reduce8(const RdF4* clo, const RdF4* chi, rd_u32 childCount, RdF4* lo, RdF4* hi, rd_u32 count)
-{
-    const rd_u32 k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= count) return;
-    RdF4 l, h; l.x = l.y = l.z = 3.0e38f; h.x = h.y = h.z = -3.0e38f; l.w = h.w = 0.0f;
-    for (rd_u32 c = 8u * k; c < 8u * k + 8u && c < childCount; ++c) {
-        const RdF4 a = clo[c], b = chi[c];
-        l.x = fminf(l.x, a.x); l.y = fminf(l.y, a.y); l.z = fminf(l.z, a.z);
-        h.x = fmaxf(h.x, b.x); h.y = fmaxf(h.y, b.y); h.z = fmaxf(h.z, b.z);
-    }
-    lo[k] = l; hi[k] = h;
-}
-
-// One level. Thread m = memory position inside the level; blockOf[m] = which aligned block of the Morton order the node covers.
-// Children of block k are blocks 8k .. 8k+7 of the level below (leaf level: leaf slots), stored at childOffset + 8k in SLOT order.
-__global__ void rd_k_ct_emit(RdNode8* nodes, rd_u32 levelOffset, rd_u32 count, const rd_u32* blockOf, const RdF4* lo, const RdF4* hi,
-                             const RdF4* clo, const RdF4* chi, rd_u32 childCount, rd_u32 childOffset, rd_u32* childBlockOf,
-                             int leafLevel, const rd_u32* prim, rd_u32 n, rd_u32 per, rd_u32* leafPrim)
-{
-    const rd_u32 m = blockIdx.x * blockDim.x + threadIdx.x;
-    if (m >= count) return;
-    const rd_u32 k = blockOf ? blockOf[m] : m;
-    const RdF4 nlo = lo[k], nhi = hi[k];
-    int nc = 0;
-    RdF4 bl[8], bh[8];
-    for (rd_u32 c = 8u * k; c < 8u * k + 8u && c < childCount; ++c) { bl[nc] = clo[c]; bh[nc] = chi[c]; ++nc; }
-    // octant-keyed slot assignment, as in rd_collapse_item
-    const float ccx = 0.5f * (nlo.x + nhi.x), ccy = 0.5f * (nlo.y + nhi.y), ccz = 0.5f * (nlo.z + nhi.z);
-    float ox[8], oy[8], oz[8];
-    for (int c = 0; c < nc; ++c) { ox[c] = 0.5f * (bl[c].x + bh[c].x) - ccx; oy[c] = 0.5f * (bl[c].y + bh[c].y) - ccy; oz[c] = 0.5f * (bl[c].z + bh[c].z) - ccz; }
-    int childAt[8], slotOf[8];
-    for (int q = 0; q < 8; ++q) { childAt[q] = -1; slotOf[q] = -1; }
-    for (int round = 0; round < nc; ++round) {
-        int bk = -1, bs = -1; float bscore = -3.0e38f;
-        for (int c = 0; c < nc; ++c) {
-            if (slotOf[c] >= 0) continue;
-            for (int q = 0; q < 8; ++q) {
-                if (childAt[q] >= 0) continue;
-                const float score = ((q & 4) ? ox[c] : -ox[c]) + ((q & 2) ? oy[c] : -oy[c]) + ((q & 1) ? oz[c] : -oz[c]);
-                if (score > bscore) { bscore = score; bk = c; bs = q; }
-            }
-        }
-        if (bk < 0) {
-            for (int c = 0; c < nc && bk < 0; ++c) if (slotOf[c] < 0) bk = c;
-            for (int q = 0; q < 8 && bs < 0; ++q) if (childAt[q] < 0) bs = q;
-        }
-        slotOf[bk] = bs; childAt[bs] = bk;
-    }
-    const rd_u32 ex = rd_grid_exponent(nhi.x - nlo.x), ey = rd_grid_exponent(nhi.y - nlo.y), ez = rd_grid_exponent(nhi.z - nlo.z);
-    const float isx = 1.0f / RD_U2F(ex << 23), isy = 1.0f / RD_U2F(ey << 23), isz = 1.0f / RD_U2F(ez << 23);
-    rd_u8 q[6][8];
-    rd_u32 imask = 0, leafNib = 0, innerNib = 0, rank = 0, off = 0;
-    for (int sl = 0; sl < 8; ++sl) {
-        for (int a = 0; a < 6; ++a) q[a][sl] = 0;
-        if (childAt[sl] < 0) { q[0][sl] = q[1][sl] = q[2][sl] = 255; continue; }
-        const int c = childAt[sl];
-        const RdF4 l = bl[c], h = bh[c];
-        float v;
-        v = floorf((l.x - nlo.x) * isx); q[0][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        v = floorf((l.y - nlo.y) * isy); q[1][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        v = floorf((l.z - nlo.z) * isz); q[2][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        v = ceilf((h.x - nlo.x) * isx); q[3][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        v = ceilf((h.y - nlo.y) * isy); q[4][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        v = ceilf((h.z - nlo.z) * isz); q[5][sl] = (rd_u8)(v < 0.0f ? 0.0f : (v > 255.0f ? 255.0f : v));
-        if (!leafLevel) {
-            imask |= 1u << sl; innerNib |= 1u << (4 * sl);
-            childBlockOf[8u * k + rank] = 8u * k + (rd_u32)c;
-            ++rank;
-        } else {
-            const rd_u32 j = 8u * k + (rd_u32)c;
-            rd_u32 cnt = n - per * j; if (cnt > per) cnt = per;
-            leafNib |= ((1u << cnt) - 1u) << (4 * sl);
-            for (rd_u32 t = 0; t < cnt; ++t) leafPrim[per * 8u * k + off + t] = prim[per * j + t];
-            off += cnt;
-        }
-    }
-    RdNode8 node;
-    node.w[0].x = RD_F2U(nlo.x); node.w[0].y = RD_F2U(nlo.y); node.w[0].z = RD_F2U(nlo.z);
-    node.w[0].w = ex | (ey << 8) | (ez << 16) | (imask << 24);
-    node.w[1].x = leafLevel ? 0u : childOffset + 8u * k; node.w[1].y = leafLevel ? per * 8u * k : 0u;
-    node.w[1].z = leafNib; node.w[1].w = innerNib;
-#define RD_PACK4(a, o) ((rd_u32)(a)[o] | ((rd_u32)(a)[o + 1] << 8) | ((rd_u32)(a)[o + 2] << 16) | ((rd_u32)(a)[o + 3] << 24))
-    node.w[2].x = RD_PACK4(q[0], 0); node.w[2].y = RD_PACK4(q[0], 4); node.w[2].z = RD_PACK4(q[1], 0); node.w[2].w = RD_PACK4(q[1], 4);
-    node.w[3].x = RD_PACK4(q[2], 0); node.w[3].y = RD_PACK4(q[2], 4); node.w[3].z = RD_PACK4(q[3], 0); node.w[3].w = RD_PACK4(q[3], 4);
-    node.w[4].x = RD_PACK4(q[4], 0); node.w[4].y = RD_PACK4(q[4], 4); node.w[4].z = RD_PACK4(q[5], 0); node.w[4].w = RD_PACK4(q[5], 4);
-#undef RD_PACK4
-    nodes[levelOffset + m] = node;
-}
-
-// prim = primitive indices in Morton order (device); plo / phi = primitive boxes
-static int rd_build_complete_tree(rd_platform* p, cudaStream_t st, const RdF4* plo, const RdF4* phi, const rd_u32* prim, uint32_t n, rd_u32 per, RdBuildResult* out)
-{
-    const rd_u32 slots = (n + per - 1u) / per;
-    std::vector<rd_u32> cnt;   // bottom-up: cnt[0] = leaf nodes
-    cnt.push_back((slots + 7u) / 8u);
-    while (cnt.back() > 1u) cnt.push_back((cnt.back() + 7u) / 8u);
-    const int D = (int)cnt.size();
-    std::vector<rd_u32> offset(D + 1, 0u);   // top-down memory offsets: level 0 = root
-    for (int l = 0; l < D; ++l) offset[l + 1] = offset[l] + cnt[D - 1 - l];
-    RdTmp tmp(st);
-    RdF4 *slo, *shi;
-    RD_CUDA(tmp.alloc(&slo, slots)); RD_CUDA(tmp.alloc(&shi, slots));
-    rd_k_ct_slot_boxes<<<rd_grid(slots), RD_BT, 0, st>>>(prim, plo, phi, n, per, slots, slo, shi);
-    std::vector<RdF4*> blo(D), bhi(D); std::vector<rd_u32*> blockOf(D);
-    for (int b = 0; b < D; ++b) {   // bottom-up index b
-        RD_CUDA(tmp.alloc(&blo[b], cnt[b])); RD_CUDA(tmp.alloc(&bhi[b], cnt[b])); RD_CUDA(tmp.alloc(&blockOf[b], (size_t)cnt[b] + 8));
-        rd_k_ct_reduce8<<<rd_grid(cnt[b]), RD_BT, 0, st>>>(b ? blo[b - 1] : slo, b ? bhi[b - 1] : shi, b ? cnt[b - 1] : slots, blo[b], bhi[b], cnt[b]);
-    }
-    out->nodeCount = offset[D]; out->levels = (rd_u32)D;
-    RD_CUDA(cudaMallocAsync(&out->nodes, (size_t)out->nodeCount * sizeof(RdNode8), st));
-    RD_CUDA(cudaMallocAsync(&out->leafPrim, (size_t)n * sizeof(rd_u32), st));
-    for (int l = 0; l < D; ++l) {   // top-down
-        const int b = D - 1 - l;
-        const bool leaf = b == 0;
-        rd_k_ct_emit<<<rd_grid(cnt[b]), RD_BT, 0, st>>>(out->nodes, offset[l], cnt[b], l ? blockOf[b] : (const rd_u32*)0, blo[b], bhi[b],
-                                                       leaf ? slo : blo[b - 1], leaf ? shi : bhi[b - 1], leaf ? slots : cnt[b - 1], offset[l + 1],
-                                                       leaf ? (rd_u32*)0 : blockOf[b - 1], leaf ? 1 : 0, prim, n, per, out->leafPrim);
-    }
-    p->launches += 1 + 2 * D;
-    RdF4 rl, rh;
-    RD_CUDA(cudaMemcpyAsync(&rl, blo[D - 1], sizeof(RdF4), cudaMemcpyDeviceToHost, st));
-    RD_CUDA(cudaMemcpyAsync(&rh, bhi[D - 1], sizeof(RdF4), cudaMemcpyDeviceToHost, st));
-    RD_CUDA(cudaStreamSynchronize(st));
-    RD_CUDA(cudaGetLastError());
-    out->lo[0] = rl.x; out->lo[1] = rl.y; out->lo[2] = rl.z;
-    out->hi[0] = rh.x; out->hi[1] = rh.y; out->hi[2] = rh.z;
-    return RD_OK;
-}
-#endif
-
 int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t n, RdBuildResult* out)
 {
     cudaStream_t st = p->stream;
@@ -615,12 +466,6 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
     p->launches += sortLaunches;
     if (sortedSide < 0) { rd_set_error("rd_build_wide_bvh: radix sort failed: %s", cudaGetErrorString(cudaGetLastError())); return RD_E_CUDA; }
     if (sortedSide == 0) { rd_u64* tk = keysA; keysA = keysB; keysB = tk; rd_u32* tv = valsA; valsA = valsB; valsB = tv; }   // sorted pairs are (keysB, valsB) below
-#if !RD_NODE_F32
-    if (const char* e = getenv("RD_BUILD_COMPLETE")) {   // developer knob / experiment: complete 8-ary tree over the Morton order
-        int per = atoi(e); if (per < 1) per = 1; if (per > 4) per = 4;
-        return rd_build_complete_tree(p, st, dlo, dhi, valsB, n, (rd_u32)per, out);
-    }
-#endif
 
     const rd_u32 ni = n > 1 ? n - 1 : 1;
     RdBinTree T;
