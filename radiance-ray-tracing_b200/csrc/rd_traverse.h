@@ -329,11 +329,24 @@ struct RdTraversal {
     RdHitRec hit;
     bool any;
 
+#if defined(__CUDA_ARCH__) && defined(RD_SMEM_STACK) && RD_SMEM_STACK > 0
+    // ablation (north_star names it): the first RD_SMEM_STACK entries of every lane's stack in shared memory, [entry][thread]
+    // so that a warp's accesses are conflict-free, the rest spills to the thread-local array. Blocks of <= 128 threads only.
+    RdStackEntry (*sst)[128];
+    RD_HD void push(const RdScene* scene, RdStackEntry e)
+    {
+        if (sp < RD_STACK_ENTRIES) { if (sp < RD_SMEM_STACK) sst[sp][threadIdx.x & 127u] = e; else stack[sp - RD_SMEM_STACK] = e; ++sp; }
+        else if (scene->status) scene->status[0] = 1u;
+    }
+    RD_HD RdStackEntry pop() { --sp; return sp < RD_SMEM_STACK ? sst[sp][threadIdx.x & 127u] : stack[sp - RD_SMEM_STACK]; }
+#else
     RD_HD void push(const RdScene* scene, RdStackEntry e)
     {
         if (sp < RD_STACK_ENTRIES) stack[sp++] = e;
         else if (scene->status) scene->status[0] = 1u;
     }
+    RD_HD RdStackEntry pop() { return stack[--sp]; }
+#endif
 
     RD_HD void begin(RdStackEntry* stackMemory, const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
     {
@@ -460,7 +473,7 @@ struct RdTraversal {
                 rd_frame_set(f, wox, woy, woz, wdx, wdy, wdz, scene->maxAbs);
             }
             if (sp == 0) return false;
-            ng = stack[--sp];
+            ng = pop();
         }
         return true;
     }
@@ -480,6 +493,10 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
     // the next traceRay) on their own -- measured 2.2 of 32 lanes active in programs/path.cl. The lanes
     // that enter together therefore wait for each other here before returning.
     const unsigned together = __activemask();
+#endif
+#if defined(__CUDA_ARCH__) && defined(RD_SMEM_STACK) && RD_SMEM_STACK > 0
+    __shared__ RdStackEntry rd_shared_stack[RD_SMEM_STACK][128];
+    T.sst = rd_shared_stack;
 #endif
     T.begin(stackMemory, scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
     while (T.step(scene, onCandidate)) {}

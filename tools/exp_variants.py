@@ -27,7 +27,22 @@ for _k in range(3):
     tlas, blas = scenes.build_scene(plt, bundle)
     plt.sync()
     print("bvh", blas[0].stats(), "build_ms(rebuild %d, incl upload) %.1f" % (_k, (time.perf_counter() - t0) * 1e3), flush=True)
+def fetch_counts():
+    """wide nodes / triangle records fetched per primary ray (counters-on build of the library's own traversal kernel)"""
+    n = W * H
+    ra, rb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 16)
+    ha, hb = rd.CreateBuffer(plt, n * 16), rd.CreateBuffer(plt, n * 4)
+    rd.GeneratePrimaryRays(plt, ds.rdCam, 0, 0, W, H, ra, rb)
+    rd.TraceRayList(plt, tlas, ra, rb, ha, hb, n, rd.TRACE_COUNTERS)
+    plt.sync()
+    c = rd.TraceCounters(plt)
+    for hnd in (ra, rb, ha, hb):
+        hnd.free()
+    return c["nodes"] / c["rays"], c["tris"] / c["rays"]
+
+
 ds = scenes.DeviceScene(plt, bundle, tlas, W, H, scenes.rtprop(0, int(os.environ.get('RD_EXP_SPP', '1')), int(os.environ.get('RD_EXP_DEPTH', '1')), 0))
+print("fetches per primary ray: %.2f wide nodes, %.2f triangle records" % fetch_counts(), flush=True)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 VARIANTS = json.loads(os.environ.get("RD_EXP_VARIANTS", "null")) or [
     {"flags": ""}, {"flags": "-DRD_DEQUANT_I2F=1"}, {"flags": "-DRD_POSTPONE=5"}, {"flags": "-DRD_POSTPONE=3"},
