@@ -27,6 +27,9 @@
 // between the phases; the triangle phase is 40 % of the issued instructions at 5 of 32 lanes on the 10 M-triangle field):
 // k = 2: 10 M 2991 -> 3050 Mrays/s, C2 4520 -> 4290; k >= 6: -7 % .. -20 % -- what the fuller triangle phase saves, the
 // waiting lanes lose in extra node iterations. 256-byte nodes with float boxes: see RD_NODE_F32 in rd_types.h.
+// The first 4 / 8 / 12 stack entries of every lane in shared memory ([entry][thread], the rest thread-local; RD_SMEM_STACK,
+// code in the history at commit "north_star ablations with numbers"): 10 M 3022 -> 2918 / 2935 / 2923, C2 4665 -> 4561 / 4581 /
+// 4581 Mrays/s, same image -- the thread-local stack lives in the same L1 and needs no index arithmetic per access.
 #ifndef RD_TRAVERSE_H
 #define RD_TRAVERSE_H
 #include "rd_types.h"
@@ -329,24 +332,12 @@ struct RdTraversal {
     RdHitRec hit;
     bool any;
 
-#if defined(__CUDA_ARCH__) && defined(RD_SMEM_STACK) && RD_SMEM_STACK > 0
-    // ablation (north_star names it): the first RD_SMEM_STACK entries of every lane's stack in shared memory, [entry][thread]
-    // so that a warp's accesses are conflict-free, the rest spills to the thread-local array. Blocks of <= 128 threads only.
-    RdStackEntry (*sst)[128];
-    RD_HD void push(const RdScene* scene, RdStackEntry e)
-    {
-        if (sp < RD_STACK_ENTRIES) { if (sp < RD_SMEM_STACK) sst[sp][threadIdx.x & 127u] = e; else stack[sp - RD_SMEM_STACK] = e; ++sp; }
-        else if (scene->status) scene->status[0] = 1u;
-    }
-    RD_HD RdStackEntry pop() { --sp; return sp < RD_SMEM_STACK ? sst[sp][threadIdx.x & 127u] : stack[sp - RD_SMEM_STACK]; }
-#else
     RD_HD void push(const RdScene* scene, RdStackEntry e)
     {
         if (sp < RD_STACK_ENTRIES) stack[sp++] = e;
         else if (scene->status) scene->status[0] = 1u;
     }
     RD_HD RdStackEntry pop() { return stack[--sp]; }
-#endif
 
     RD_HD void begin(RdStackEntry* stackMemory, const RdScene* scene, float ox, float oy, float oz, float dx, float dy, float dz, float tmin_, float tmax_)
     {
@@ -493,10 +484,6 @@ RD_HD bool rd_traverse(const RdScene* scene, float ox, float oy, float oz, float
     // the next traceRay) on their own -- measured 2.2 of 32 lanes active in programs/path.cl. The lanes
     // that enter together therefore wait for each other here before returning.
     const unsigned together = __activemask();
-#endif
-#if defined(__CUDA_ARCH__) && defined(RD_SMEM_STACK) && RD_SMEM_STACK > 0
-    __shared__ RdStackEntry rd_shared_stack[RD_SMEM_STACK][128];
-    T.sst = rd_shared_stack;
 #endif
     T.begin(stackMemory, scene, ox, oy, oz, dx, dy, dz, tmin, tmax);
     while (T.step(scene, onCandidate)) {}
