@@ -490,7 +490,7 @@ RD_F rd_uint4 read_imageui(image2d_array_t img, sampler_t smp, const rd_float4& 
 {
     uint mode = (uint)(smp & 0xffffu), filter = (uint)((smp >> 16) & 0xffffu);
     bool normalised = ((smp >> 32) & 1u) != 0;
-    int layer = (int)floorf(coord.z + 0.5f);
+    int layer = (int)rintf(coord.z);   // OpenCL 1.2 8.2: l = clamp(rint(w), 0, d - 1), round half to even
     layer = layer < 0 ? 0 : (layer >= (int)img->layers ? (int)img->layers - 1 : layer);
     float u = coord.x, v = coord.y;
     if (normalised) {
