@@ -36,7 +36,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     rd_platform* p = new rd_platform();
     p->device = device;
     p->boundModule = 0;
-    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 25;
+    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 25; p->optWfLanes = 2;
     p->ilWorld = p->ilRank = p->ilBandRows = 0;
     p->optStreamImage = 0;
     p->mirrorObj = 0; p->mirrorHost = 0; p->mirrorItemBytes = 0; p->mirrorBands = 0; p->mirrorValidBytes = 0; p->mirrorFresh = 0; p->copyPending = 0;
@@ -48,6 +48,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0; p->optL2Persist = 0;   // off by default: +3 % on the 10 M-triangle primary frame at 96 MB, but the wavefront queues lose the L2 they
     // stream through (C3 42.6 -> 58.0 ms, C5 488 -> 709 ms; profiles/README_r2.md)
     if (const char* e = getenv("RD_L2_PERSIST")) p->optL2Persist = atol(e);
+    if (const char* e = getenv("RD_WF_LANES")) p->optWfLanes = atol(e) >= 2 ? 2 : 1;   // developer knob for A/B runs of bench.py
     p->comm = 0; p->unitSlots = 0; p->unitSlotsDev = 0; p->unitEvent = 0; p->optWfTimeline = 0; p->tlUsed = 0;
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
@@ -86,6 +87,7 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     for (cudaEvent_t e : p->tlEvents) cudaEventDestroy(e);
     if (p->unitSlots) { cudaFreeHost((void*)p->unitSlots); cudaEventDestroy(p->unitEvent); }
     rd_wf_release(p);
+    if (p->wfStreamB) { cudaStreamDestroy(p->wfStreamB); for (int k = 0; k < 4; ++k) cudaEventDestroy(p->wfEvents[k]); }
     { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
     cudaFreeHost((void*)p->hstatus);
     cudaFree(p->dRayCounter);
@@ -414,6 +416,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
         cudaMemPool_t pool;
         if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
     }
+    else if (!strcmp(key, "wf_lanes")) p->optWfLanes = value >= 2 ? 2 : 1;
     else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)
     else if (!strcmp(key, "stealing")) p->optSteal = value;
     else if (!strcmp(key, "stream_image")) p->optStreamImage = value;   // modules created from now on carry the band-reporting raygen

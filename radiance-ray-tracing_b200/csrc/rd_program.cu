@@ -742,6 +742,7 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
                                    unsigned long long count, const unsigned* rtKnown = 0, bool resetTimeline = true)
 {
     rd_module* m = p->boundModule;
+    p->wfLane = 0;
     if (!m->wfGenerate) {
         rd_set_error("rd_trace_rays: option wavefront is on but the program defines no wavefrontScene / wavefrontPrimary hooks");
         return RD_E_STATE;
@@ -756,66 +757,99 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     }
     if (resetTimeline) p->tlUsed = 0;
     const unsigned stride = (m->wfPayloadSize + 15u) & ~15u;
+    // two lanes (option wf_lanes): the passes of the frame alternate between two queue sets on two streams
+    const int lanes = (p->optWfLanes >= 2 && rt[1] >= 2 && !rt[3] && !p->optWfTimeline) ? 2 : 1;
     // samples in flight per pass: as many as option wf_paths allows (HBM: ~200 B per path)
-    unsigned long long inFlight = (unsigned long long)p->optWfPaths / count;
+    unsigned long long inFlight = (unsigned long long)p->optWfPaths / ((unsigned long long)lanes * count);
     if (inFlight < 1) inFlight = 1;
     if (inFlight > rt[1]) inFlight = rt[1] ? rt[1] : 1;
+    if (lanes == 2 && inFlight > (rt[1] + 1u) / 2u) inFlight = (rt[1] + 1u) / 2u;   // at least one pass per lane
     if (rt[3]) inFlight = 1;                       // debug views stop after one bounce of one sample at a time
     while (inFlight * count > 0x7fffffffull) --inFlight;
     const unsigned paths = (unsigned)(inFlight * count);
-    int rc = rd_wf_reserve(p, paths, stride);
-    if (rc) return rc;
     // the scene header is whichever descriptor is a top-level structure
     const void* scene = 0;
     for (size_t i = 0; i < p->boundKinds.size(); ++i) if (p->boundKinds[i] == RD_H_TLAS) scene = (const void*)p->boundArgs[i];
     if (!scene) { rd_set_error("rd_trace_rays: no top-level acceleration structure in the descriptor set"); return RD_E_STATE; }
-    RdWfBuffers& B = p->wf;
-    RdWfState S; memset(&S, 0, sizeof(S));
-    S.payload = B.payload; S.color = (RdF4*)B.color; S.contrib = (RdF4*)B.contrib;
-    for (int q = 0; q < 2; ++q) { S.rayA[q] = (RdF4*)B.rayA[q]; S.rayB[q] = (RdF4*)B.rayB[q]; S.pathOf[q] = B.pathOf[q]; }
-    S.hitA = (RdF4*)B.hitA; S.hitB = B.hitB; S.keys = B.keys; S.order = B.order; S.counts = B.counts; S.hist = B.hist;
-    S.payloadStride = stride; S.cur = 0; S.first = (unsigned)first; S.count = (unsigned)count; S.total = total;
-    S.tileW = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
-    S.frameID = rt[0]; S.samples = 1; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
-    S.ilWorld = p->ilWorld; S.ilRank = p->ilRank; S.ilBandRows = p->ilBandRows ? p->ilBandRows : 1u;
-    S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
-    S.status = p->dstatus; S.capacity = B.capacity;
-    rc = rd_wf_upload_state(p, &S);
-    if (rc) return rc;
     CUdeviceptr dinfo; size_t infoBytes = 0;
     RD_CU(cuModuleGetGlobal(&dinfo, &infoBytes, m->mod, "rd_launch_info"));
-    const unsigned info[8] = {(unsigned)first, total, S.tileW, 1u, 0u, 0u, 0u, 0u};
-    RD_CU(cuMemcpyHtoDAsync(dinfo, info, sizeof(info), (CUstream)p->stream));
-    std::vector<uint64_t> args(p->boundArgs);
-    args.push_back((uint64_t)(uintptr_t)B.dstate);
-    std::vector<void*> argv(args.size());
-    for (size_t i = 0; i < argv.size(); ++i) argv[i] = &args[i];
+    const unsigned info[8] = {(unsigned)first, total, 0u, 1u, 0u, 0u, 0u, 0u};
+    unsigned infoTiled[8]; memcpy(infoTiled, info, sizeof(info));
+    infoTiled[2] = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
+    RD_CU(cuMemcpyHtoDAsync(dinfo, infoTiled, sizeof(infoTiled), (CUstream)p->stream));
+    if (lanes == 2) {
+        if (!p->wfStreamB) {
+            RD_CUDA(cudaStreamCreateWithFlags(&p->wfStreamB, cudaStreamNonBlocking));
+            for (int k = 0; k < 4; ++k) RD_CUDA(cudaEventCreateWithFlags(&p->wfEvents[k], cudaEventDisableTiming));
+        }
+        // lane 1 starts behind everything queued on the platform stream so far (descriptor writes, the launch info above)
+        RD_CUDA(cudaEventRecord(p->wfEvents[2], p->stream));
+        RD_CUDA(cudaStreamWaitEvent(p->wfStreamB, p->wfEvents[2], 0));
+    }
+    int rc = RD_OK;
+    RdWfState S; memset(&S, 0, sizeof(S));
+    std::vector<uint64_t> args[2];
+    std::vector<void*> argv[2];
+    for (int lane = 0; lane < lanes; ++lane) {
+        p->wfLane = lane;
+        rc = rd_wf_reserve(p, paths, stride);
+        if (rc) { p->wfLane = 0; return rc; }
+        RdWfBuffers& B = rd_wf_buffers(p);
+        memset(&S, 0, sizeof(S));
+        S.payload = B.payload; S.color = (RdF4*)B.color; S.contrib = (RdF4*)B.contrib;
+        for (int q = 0; q < 2; ++q) { S.rayA[q] = (RdF4*)B.rayA[q]; S.rayB[q] = (RdF4*)B.rayB[q]; S.pathOf[q] = B.pathOf[q]; }
+        S.hitA = (RdF4*)B.hitA; S.hitB = B.hitB; S.keys = B.keys; S.order = B.order; S.counts = B.counts; S.hist = B.hist;
+        S.payloadStride = stride; S.cur = 0; S.first = (unsigned)first; S.count = (unsigned)count; S.total = total;
+        S.tileW = infoTiled[2];
+        S.frameID = rt[0]; S.samples = 1; S.totalSamples = rt[0]; S.depth = 0; S.maxDepth = rt[2]; S.debug = rt[3]; S.sortOn = p->optWfSort ? 1u : 0u;
+        S.ilWorld = p->ilWorld; S.ilRank = p->ilRank; S.ilBandRows = p->ilBandRows ? p->ilBandRows : 1u;
+        S.sbtRecordOffset = (int)m->wfRay[0]; S.missIndex = (int)m->wfRay[1]; S.tmin = m->wfRay[2]; S.tmax = m->wfRay[3];
+        S.status = p->dstatus; S.capacity = B.capacity;
+        rc = rd_wf_upload_state(p, &S);
+        if (rc) { p->wfLane = 0; return rc; }
+        args[lane] = p->boundArgs;
+        args[lane].push_back((uint64_t)(uintptr_t)B.dstate);
+        argv[lane].resize(args[lane].size());
+        for (size_t i = 0; i < argv[lane].size(); ++i) argv[lane][i] = &args[lane][i];
+    }
     const unsigned blocks = (unsigned)((count + 127) / 128);
-    for (unsigned k = 0; k < rt[1]; k += (unsigned)inFlight) {
+    unsigned pass = 0;
+    for (unsigned k = 0; k < rt[1]; k += (unsigned)inFlight, ++pass) {
+        const int lane = (int)(pass % (unsigned)lanes);
+        p->wfLane = lane;
+        CUstream st = (CUstream)rd_wf_stream(p);
         const unsigned samples = rt[1] - k < (unsigned)inFlight ? rt[1] - k : (unsigned)inFlight;
         const unsigned live = samples * (unsigned)count, pathBlocks = (live + 127u) / 128u;
-        rc = rd_wf_advance(p, 0u, rt[0] + k, samples); if (rc) return rc;
+        rc = rd_wf_advance(p, 0u, rt[0] + k, samples); if (rc) break;
         rd_tl_mark(p, 1);
-        RD_CU(cuLaunchKernel(m->wfGenerate, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+        RD_CU(cuLaunchKernel(m->wfGenerate, pathBlocks, 1, 1, 128, 1, 1, 0, st, argv[lane].data(), 0));
         p->launches += 1;
-        for (unsigned d = 0; d < rt[2]; ++d) {
-            if (d > 0 && p->optWfRaySort) { rd_tl_mark(p, 7); rc = rd_wf_reorder_rays(p, scene, live); if (rc) return rc; }
+        for (unsigned d = 0; d < rt[2] && !rc; ++d) {
+            if (d > 0 && p->optWfRaySort) { rd_tl_mark(p, 7); rc = rd_wf_reorder_rays(p, scene, live); if (rc) break; }
             rd_tl_mark(p, 2);
             // primary rays are coherent (static batches); bounce rays are not (dynamic fetch), option wf_dynamic: 0 never, 1 bounces, 2 always
-            rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) return rc;
-            if (S.sortOn) { rd_tl_mark(p, 3); rc = rd_wf_sort(p, live); if (rc) return rc; }
+            rc = rd_wf_trace(p, scene, p->optWfDynamic == 2 || (p->optWfDynamic == 1 && d > 0)); if (rc) break;
+            if (S.sortOn) { rd_tl_mark(p, 3); rc = rd_wf_sort(p, live); if (rc) break; }
             rd_tl_mark(p, 4);
-            RD_CU(cuLaunchKernel(m->wfShade, pathBlocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+            RD_CU(cuLaunchKernel(m->wfShade, pathBlocks, 1, 1, 128, 1, 1, 0, st, argv[lane].data(), 0));
             p->launches += 1;
-            rc = rd_wf_advance(p, 2u, 0u); if (rc) return rc;
+            rc = rd_wf_advance(p, 2u, 0u); if (rc) break;
             if (rt[3]) break;
         }
+        if (rc) break;
         rd_tl_mark(p, 5);
-        RD_CU(cuLaunchKernel(m->wfAccumulate, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+        // the running mean is taken in frame order: this pass's accumulate runs behind the previous pass's (the other lane's)
+        if (lanes == 2 && pass > 0) RD_CUDA(cudaStreamWaitEvent((cudaStream_t)st, p->wfEvents[1 - lane], 0));
+        RD_CU(cuLaunchKernel(m->wfAccumulate, blocks, 1, 1, 128, 1, 1, 0, st, argv[lane].data(), 0));
         p->launches += 1;
+        if (lanes == 2) RD_CUDA(cudaEventRecord(p->wfEvents[lane], (cudaStream_t)st));
     }
+    const int lastLane = pass ? (int)((pass - 1u) % (unsigned)lanes) : 0;
+    p->wfLane = 0;
+    if (rc) return rc;
+    if (lanes == 2 && lastLane == 1) RD_CUDA(cudaStreamWaitEvent(p->stream, p->wfEvents[1], 0));   // resolve (and whatever follows) behind lane 1
     rd_tl_mark(p, 6);
-    RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv.data(), 0));
+    RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv[0].data(), 0));
     p->launches += 1;
     rd_tl_mark(p, 0);
     return RD_OK;

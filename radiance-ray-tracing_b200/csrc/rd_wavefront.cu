@@ -244,9 +244,9 @@ __global__ void rd_k_wf_advance(RdWfState* wf, unsigned op, unsigned a, unsigned
 // ---- launch wrappers used by the stage sequencer in rd_program.cu -------------------------------
 int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride)
 {
-    RdWfBuffers& B = p->wf;
+    RdWfBuffers& B = rd_wf_buffers(p);
     if (B.capacity >= count && B.payloadStride >= payloadStride && B.dstate) return RD_OK;
-    RD_CUDA(cudaStreamSynchronize(p->stream));
+    RD_CUDA(cudaStreamSynchronize(rd_wf_stream(p)));
     void** all[] = {(void**)&B.payload, (void**)&B.color, (void**)&B.contrib, (void**)&B.rayA[0], (void**)&B.rayA[1], (void**)&B.rayB[0],
                     (void**)&B.rayB[1], (void**)&B.pathOf[0], (void**)&B.pathOf[1], (void**)&B.hitA, (void**)&B.hitB, (void**)&B.keys,
                     (void**)&B.order, (void**)&B.counts, (void**)&B.hist, (void**)&B.dstate};
@@ -268,22 +268,24 @@ int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride)
 
 void rd_wf_release(rd_platform* p)
 {
-    RdWfBuffers& B = p->wf;
-    void* all[] = {B.payload, B.color, B.contrib, B.rayA[0], B.rayA[1], B.rayB[0], B.rayB[1], B.pathOf[0], B.pathOf[1],
-                   B.hitA, B.hitB, B.keys, B.order, B.counts, B.hist, B.dstate};
-    for (void* q : all) if (q) cudaFree(q);
-    memset(&B, 0, sizeof(B));
+    for (int lane = 0; lane < 2; ++lane) {
+        RdWfBuffers& B = lane ? p->wfB : p->wf;
+        void* all[] = {B.payload, B.color, B.contrib, B.rayA[0], B.rayA[1], B.rayB[0], B.rayB[1], B.pathOf[0], B.pathOf[1],
+                       B.hitA, B.hitB, B.keys, B.order, B.counts, B.hist, B.dstate};
+        for (void* q : all) if (q) cudaFree(q);
+        memset(&B, 0, sizeof(B));
+    }
 }
 
 int rd_wf_upload_state(rd_platform* p, const RdWfState* host)
 {
-    RD_CUDA(cudaMemcpyAsync(p->wf.dstate, host, sizeof(RdWfState), cudaMemcpyHostToDevice, p->stream));
+    RD_CUDA(cudaMemcpyAsync(rd_wf_buffers(p).dstate, host, sizeof(RdWfState), cudaMemcpyHostToDevice, rd_wf_stream(p)));
     return RD_OK;
 }
 
 int rd_wf_advance(rd_platform* p, unsigned op, unsigned a, unsigned b)
 {
-    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, op, a, b);
+    rd_k_wf_advance<<<1, 32, 0, rd_wf_stream(p)>>>((RdWfState*)rd_wf_buffers(p).dstate, op, a, b);
     p->launches += 1;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
@@ -298,12 +300,12 @@ int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
             const char* m = getenv("RD_WF_MINB"); minb = m ? atoi(m) : 7;
         }
         if (minb >= 8)
-            rd_k_wf_trace_dyn<8><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+            rd_k_wf_trace_dyn<8><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, rd_wf_stream(p)>>>((const RdScene*)scene, (const RdWfState*)rd_wf_buffers(p).dstate);
         else
-            rd_k_wf_trace_dyn<7><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+            rd_k_wf_trace_dyn<7><<<(unsigned)p->smCount * (unsigned)perSm, 128, 0, rd_wf_stream(p)>>>((const RdScene*)scene, (const RdWfState*)rd_wf_buffers(p).dstate);
     }
     else
-        rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, p->stream>>>((const RdScene*)scene, (const RdWfState*)p->wf.dstate);
+        rd_k_wf_trace<<<(unsigned)p->smCount * 12u, 128, 0, rd_wf_stream(p)>>>((const RdScene*)scene, (const RdWfState*)rd_wf_buffers(p).dstate);
     p->launches += 1;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
@@ -311,14 +313,14 @@ int rd_wf_trace(rd_platform* p, const void* scene, int dynamicFetch)
 
 int rd_wf_reorder_rays(rd_platform* p, const void* scene, unsigned count)
 {
-    const RdWfState* S = (const RdWfState*)p->wf.dstate;
-    RD_CUDA(cudaMemsetAsync(p->wf.hist, 0, RD_WF_KEY_BINS * 4, p->stream));
+    const RdWfState* S = (const RdWfState*)rd_wf_buffers(p).dstate;
+    RD_CUDA(cudaMemsetAsync(rd_wf_buffers(p).hist, 0, RD_WF_KEY_BINS * 4, rd_wf_stream(p)));
     unsigned hb = (count + 255u) / 256u; if (hb > (unsigned)p->smCount * 8u) hb = (unsigned)p->smCount * 8u; if (!hb) hb = 1;
-    rd_k_wf_ray_keys<<<(count + 255u) / 256u, 256, 0, p->stream>>>((const RdScene*)scene, S);
-    rd_k_wf_hist<<<hb, 256, 0, p->stream>>>(S);
-    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, p->stream>>>(S);
-    rd_k_wf_ray_scatter<<<(count + 255u) / 256u, 256, 0, p->stream>>>(S);
-    rd_k_wf_advance<<<1, 32, 0, p->stream>>>((RdWfState*)p->wf.dstate, 3u, 0u, 0u);
+    rd_k_wf_ray_keys<<<(count + 255u) / 256u, 256, 0, rd_wf_stream(p)>>>((const RdScene*)scene, S);
+    rd_k_wf_hist<<<hb, 256, 0, rd_wf_stream(p)>>>(S);
+    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, rd_wf_stream(p)>>>(S);
+    rd_k_wf_ray_scatter<<<(count + 255u) / 256u, 256, 0, rd_wf_stream(p)>>>(S);
+    rd_k_wf_advance<<<1, 32, 0, rd_wf_stream(p)>>>((RdWfState*)rd_wf_buffers(p).dstate, 3u, 0u, 0u);
     p->launches += 5;
     RD_CUDA(cudaGetLastError());
     return RD_OK;
@@ -326,12 +328,12 @@ int rd_wf_reorder_rays(rd_platform* p, const void* scene, unsigned count)
 
 int rd_wf_sort(rd_platform* p, unsigned count)
 {
-    const RdWfState* S = (const RdWfState*)p->wf.dstate;
-    RD_CUDA(cudaMemsetAsync(p->wf.hist, 0, RD_WF_KEY_BINS * 4, p->stream));
+    const RdWfState* S = (const RdWfState*)rd_wf_buffers(p).dstate;
+    RD_CUDA(cudaMemsetAsync(rd_wf_buffers(p).hist, 0, RD_WF_KEY_BINS * 4, rd_wf_stream(p)));
     unsigned hb = (count + 255u) / 256u; if (hb > (unsigned)p->smCount * 8u) hb = (unsigned)p->smCount * 8u; if (!hb) hb = 1;
-    rd_k_wf_hist<<<hb, 256, 0, p->stream>>>(S);
-    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, p->stream>>>(S);
-    rd_k_wf_scatter<<<(count + 255u) / 256u, 256, 0, p->stream>>>(S);
+    rd_k_wf_hist<<<hb, 256, 0, rd_wf_stream(p)>>>(S);
+    rd_k_wf_scan<<<1, RD_WF_KEY_BINS, 0, rd_wf_stream(p)>>>(S);
+    rd_k_wf_scatter<<<(count + 255u) / 256u, 256, 0, rd_wf_stream(p)>>>(S);
     p->launches += 3;
     RD_CUDA(cudaGetLastError());
     return RD_OK;

@@ -532,6 +532,43 @@ def test_c3_full_size_properties(pkg, plt):
         assert k == -1
 
 
+def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
+    """Option wf_lanes = 2: the passes of a frame alternate between two queue sets on two streams (stage tails of one pass overlap
+    the other pass's stages); the running mean is still taken in frame order, so scratch and image are bit-identical with the
+    single-lane frame -- for an even and an odd number of passes, with the hit-group sort on and off, and when a second call
+    continues the accumulation."""
+    rd, scenes = pkg.rd, pkg.scenes
+    b = offcentre_cornell(scenes)
+    tlas, _ = scenes.build_scene(plt, b)
+    w, h = 168, 100
+    ds = scenes.DeviceScene(plt, b, tlas, w, h, scenes.rtprop(0, 5, 4, 0))
+    pipe, _ = scenes.make_pipeline(plt, "path")
+    rd.BindPipeline(plt, pipe)
+    rd.BindDescriptorSet(plt, ds.descriptors)
+    plt.set_option("wavefront", 1)
+    try:
+        for paths, srt in ((1 << 25, 1), (2 * w * h, 1), (w * h, 0)):
+            got = {}
+            for lanes in (1, 2):
+                plt.set_option("wf_lanes", lanes)
+                plt.set_option("wf_paths", paths)
+                plt.set_option("wf_sort", srt)
+                ds.set_rtprop(0, 5, 4)
+                rd.TraceRays(plt, 0, 0, 0, w, h)
+                first = ds.read_scratch()
+                ds.set_rtprop(5, 5, 4)
+                rd.TraceRays(plt, 0, 0, 0, w, h)
+                got[lanes] = (first, ds.read_scratch(), ds.read_image())
+                assert plt.status() == (0, 0)
+            for a, c in zip(got[1], got[2]):
+                assert np.array_equal(a, c), "two-lane frame differs (wf_paths %d, sort %d)" % (paths, srt)
+    finally:
+        plt.set_option("wavefront", 0)
+        plt.set_option("wf_lanes", 1)
+        plt.set_option("wf_paths", 1 << 25)
+        plt.set_option("wf_sort", 1)
+
+
 def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
     """Option wf_paths: 1 sample per pass, 2 of 5 (ragged last pass), all 5 at once -- the float scratch and the image
     are bit-identical, also when the frame continues an accumulation (totalSamples > 0)."""
