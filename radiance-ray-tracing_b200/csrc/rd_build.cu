@@ -573,15 +573,76 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
 #define RD_SUMMARY_WORDS 16
 #define RD_SUMMARY_CHUNK 4096u
 
-static int rd_build_stream(rd_platform* p, cudaStream_t* out)
+static int rd_build_stream(rd_platform* p, cudaStream_t* out, size_t* index = 0)
 {
     if (p->buildStreams.empty()) {
         int count = RD_BUILD_STREAMS;
         if (const char* e = getenv("RD_BUILD_STREAMS")) { count = atoi(e); if (count < 1) count = 1; if (count > 64) count = 64; }   // developer knob
         for (int k = 0; k < count; ++k) { cudaStream_t s; RD_CUDA(cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking)); p->buildStreams.push_back(s); }
     }
-    *out = p->buildStreams[p->buildNext++ % p->buildStreams.size()];
+    const size_t k = p->buildNext++ % p->buildStreams.size();
+    *out = p->buildStreams[k];
+    if (index) *index = k;
     return RD_OK;
+}
+
+// ---- chunked device memory for small bottom-level structures (RdArenaChunk, rd_internal.h) --------------------------------
+// Host-side bump allocation out of 64 MB chunks: no allocator call per mesh. A chunk whose structures have all been released
+// (or, for the staging kind, resolved) is kept and reused once the platform stream has passed the point of its release.
+#define RD_ARENA_CHUNK_BYTES ((size_t)64 << 20)
+static int rd_arena_take(rd_platform* p, int kind, size_t bytes, void** ptr, RdArenaChunk** chunk)
+{
+    bytes = (bytes + 255u) & ~(size_t)255u;
+    if (!bytes) bytes = 256;
+    RdArenaChunk* c = p->arenaCur[kind];
+    if (c && c->live == 0u && c->idleRecorded) {   // the current chunk ran empty: it starts over once the platform stream has let go of it
+        RD_CUDA(cudaEventSynchronize(c->idle)); c->idleRecorded = false; c->used = 0;
+    }
+    if (!c || c->used + bytes > c->size) {
+        c = 0;
+        for (RdArenaChunk* q : p->arenaChunks)   // an empty chunk of this kind
+            if (q->kind == kind && q->live == 0u && q != p->arenaCur[kind] && q->size >= bytes) { c = q; break; }
+        if (c) {
+            if (c->idleRecorded) { RD_CUDA(cudaEventSynchronize(c->idle)); c->idleRecorded = false; }
+            c->used = 0;
+        } else {
+            c = new RdArenaChunk();
+            memset(c, 0, sizeof(*c));
+            c->size = bytes > RD_ARENA_CHUNK_BYTES ? bytes : RD_ARENA_CHUNK_BYTES; c->kind = kind;
+            if (cudaMalloc(&c->base, c->size) != cudaSuccess || cudaEventCreateWithFlags(&c->idle, cudaEventDisableTiming) != cudaSuccess) {
+                rd_set_error("BuildAccelStruct: %s", cudaGetErrorString(cudaGetLastError()));
+                if (c->base) cudaFree(c->base);
+                delete c; return RD_E_CUDA;
+            }
+            p->arenaChunks.push_back(c);
+        }
+        p->arenaCur[kind] = c;
+    }
+    *ptr = c->base + c->used; *chunk = c;
+    c->used += bytes; c->live += 1u;
+    return RD_OK;
+}
+
+// one structure less in the chunk; the platform stream may still be reading it (the resolve copy): mark the point
+static void rd_arena_drop(rd_platform* p, RdArenaChunk* c)
+{
+    if (!c || !c->live) return;
+    c->live -= 1u;
+    if (c->live == 0u) c->idleRecorded = cudaEventRecord(c->idle, p->stream) == cudaSuccess;
+}
+
+// option trim_pool / tests: release the chunks nothing lives in
+void rd_arena_trim(rd_platform* p)
+{
+    std::vector<RdArenaChunk*> keep;
+    for (RdArenaChunk* c : p->arenaChunks) {
+        if (c->live == 0u) {
+            if (p->arenaCur[c->kind] == c) p->arenaCur[c->kind] = 0;
+            cudaFree(c->base); cudaEventDestroy(c->idle); delete c;
+        } else keep.push_back(c);
+    }
+    p->arenaChunks.swap(keep);
+    for (size_t k = 0; k < p->buildScratch.size(); ++k) { if (p->buildScratch[k]) cudaFree(p->buildScratch[k]); p->buildScratch[k] = 0; p->buildScratchBytes[k] = 0; }
 }
 
 static int rd_summary_slot(rd_platform* p, volatile rd_u32** host, rd_u32** dev)
@@ -614,6 +675,15 @@ int rd_blas_resolve(rd_platform* p, rd_blas* b)
     for (int k = 0; k < 3; ++k) { rd_u32 u = hs[4 + k], v = hs[7 + k]; memcpy(&b->lo[k], &u, 4); memcpy(&b->hi[k], &v, 4); }
     // the build wrote into a worst-case allocation: keep what is used (the build has completed, so the platform stream may copy)
     RdNode8* exact = 0;
+    if (b->nodesChunk) {   // staging chunk -> exact-size place in a final chunk; the staging chunk is reusable once all of it has moved
+        RdArenaChunk* fin = 0;
+        int rc = rd_arena_take(p, 1, (size_t)b->nodeCount * sizeof(RdNode8), (void**)&exact, &fin);
+        if (rc) return rc;
+        RD_CUDA(cudaMemcpyAsync(exact, b->nodes, (size_t)b->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, p->stream));
+        rd_arena_drop(p, b->nodesChunk);
+        b->nodes = exact; b->nodesChunk = fin;
+        return RD_OK;
+    }
     RD_CUDA(cudaMallocAsync(&exact, (size_t)b->nodeCount * sizeof(RdNode8), p->stream));
     RD_CUDA(cudaMemcpyAsync(exact, b->nodes, (size_t)b->nodeCount * sizeof(RdNode8), cudaMemcpyDeviceToDevice, p->stream));
     RD_CUDA(cudaFreeAsync(b->nodes, p->stream));
@@ -696,7 +766,7 @@ static int rd_upload_stage(rd_platform* p, size_t bytes, unsigned char** host)
 }
 
 // hverts / hidx != 0: the mesh is uploaded into the head of the same scratch block (dverts / didx are ignored)
-static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, const float* hverts, unsigned nv, const uint32_t* hidx,
+static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, size_t streamIndex, const float* hverts, unsigned nv, const uint32_t* hidx,
                                      const float* dverts, const uint32_t* didx, unsigned nt, rd_blas** out)
 {
     const size_t n = nt, ni = n > 1 ? n - 1 : 1;
@@ -711,9 +781,17 @@ static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, const floa
     const size_t oARef = carve(n * 4), oALo = carve(n * 16), oAHi = carve(n * 16);
     const size_t oBRef = carve(n * 4), oBLo = carve(n * 16), oBHi = carve(n * 16), oNearest = carve(n * 4);
     const size_t oItemsA = carve((n + 1) * sizeof(RdCollapseItem)), oItemsB = carve((n + 1) * sizeof(RdCollapseItem)), oLeafPrim = carve(n * 4);
-    RdTmp tmp(st);
-    char* base;
-    RD_CUDA(tmp.alloc(&base, off));
+    // the scratch block of this side stream (stream order makes the reuse by consecutive meshes safe)
+    if (p->buildScratch.size() < p->buildStreams.size()) { p->buildScratch.resize(p->buildStreams.size(), 0); p->buildScratchBytes.resize(p->buildStreams.size(), 0); }
+    if (p->buildScratchBytes[streamIndex] < off) {
+        RD_CUDA(cudaStreamSynchronize(st));
+        if (p->buildScratch[streamIndex]) cudaFree(p->buildScratch[streamIndex]);
+        p->buildScratch[streamIndex] = 0; p->buildScratchBytes[streamIndex] = 0;
+        const size_t want = off + off / 2 > ((size_t)1 << 20) ? off + off / 2 : ((size_t)1 << 20);
+        RD_CUDA(cudaMalloc(&p->buildScratch[streamIndex], want));
+        p->buildScratchBytes[streamIndex] = want;
+    }
+    char* base = (char*)p->buildScratch[streamIndex];
     if (hidx) {
         // vertices and indices sit at the head of the block in the layout of the staging copy: one transfer
         unsigned char* stage = 0;
@@ -734,11 +812,10 @@ static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, const floa
     rd_blas* b = new rd_blas();
     memset(b, 0, sizeof(*b));
     b->owner = p; b->triCount = nt;
-    if (cudaMallocAsync(&b->nodes, (n + 1) * sizeof(RdNode8), st) != cudaSuccess || cudaMallocAsync(&b->tris, n * sizeof(RdTri), st) != cudaSuccess) {
-        rd_set_error("rd_blas_build: %s", cudaGetErrorString(cudaGetLastError()));
-        if (b->nodes) cudaFreeAsync(b->nodes, st);
-        delete b; return RD_E_CUDA;
-    }
+    // triangle records in their final place, the worst-case node array in a staging chunk (rd_blas_resolve keeps what is used)
+    rc = rd_arena_take(p, 1, n * sizeof(RdTri), (void**)&b->tris, &b->trisChunk);
+    if (!rc) rc = rd_arena_take(p, 0, (n + 1) * sizeof(RdNode8), (void**)&b->nodes, &b->nodesChunk);
+    if (rc) { rd_arena_drop(p, b->trisChunk); delete b; return rc; }
     RdSmallBuild S;
     S.verts = hverts ? (const float*)(base + oVerts) : dverts; S.idx = hidx ? (const rd_u32*)(base + oIdx) : didx; S.n = nt;
     S.radius = 32;
@@ -763,11 +840,11 @@ static int rd_blas_build_small_fused(rd_platform* p, cudaStream_t st, const floa
     if (cudaGetLastError() != cudaSuccess || cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventRecord(b->done, st) != cudaSuccess) {
         rd_set_error("rd_blas_build: %s", cudaGetErrorString(cudaGetLastError()));
-        cudaFreeAsync(b->nodes, st); cudaFreeAsync(b->tris, st); delete b; return RD_E_CUDA;
+        rd_arena_drop(p, b->nodesChunk); rd_arena_drop(p, b->trisChunk); delete b; return RD_E_CUDA;
     }
     if (!p->optAsyncBuild) {
         rc = rd_blas_resolve(p, b);
-        if (rc) { cudaFree(b->nodes); cudaFree(b->tris); delete b; return rc; }
+        if (rc) { rd_arena_drop(p, b->nodesChunk); rd_arena_drop(p, b->trisChunk); delete b; return rc; }
     }
     *out = b;
     return RD_OK;
@@ -823,14 +900,14 @@ extern "C" int rd_blas_build_device(rd_platform* p, const float* dverts, unsigne
     (void)nv;
     if (!rd_build_deferrable(nt)) return rd_blas_build_on(p, p->stream, false, dverts, didx, nt, out);
     // the caller's arrays were produced on the platform stream: the side stream starts behind what is queued there now
-    cudaStream_t st; int rc = rd_build_stream(p, &st);
+    cudaStream_t st; size_t streamIndex = 0; int rc = rd_build_stream(p, &st, &streamIndex);
     if (rc) return rc;
     cudaEvent_t ready;
     RD_CUDA(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
     RD_CUDA(cudaEventRecord(ready, p->stream));
     RD_CUDA(cudaStreamWaitEvent(st, ready, 0));
     cudaEventDestroy(ready);
-    if (!getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, 0, nv, 0, dverts, didx, nt, out);
+    if (!getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, streamIndex, 0, nv, 0, dverts, didx, nt, out);
     return rd_blas_build_on(p, st, true, dverts, didx, nt, out);
 }
 
@@ -842,8 +919,9 @@ extern "C" int rd_blas_build(rd_platform* p, const float* verts, unsigned nv, co
         if (idx[k] >= nv) { rd_set_error("rd_blas_build: index %u out of range (nv=%u)", idx[k], nv); return RD_E_ARG; }
     const bool deferred = rd_build_deferrable(nt);
     cudaStream_t st = p->stream;
-    if (deferred) { int rc = rd_build_stream(p, &st); if (rc) return rc; }
-    if (deferred && !getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, verts, nv, idx, 0, 0, nt, out);   // developer knob: the multi-launch small path
+    size_t streamIndex = 0;
+    if (deferred) { int rc = rd_build_stream(p, &st, &streamIndex); if (rc) return rc; }
+    if (deferred && !getenv("RD_BUILD_UNFUSED")) return rd_blas_build_small_fused(p, st, streamIndex, verts, nv, idx, 0, 0, nt, out);   // developer knob: the multi-launch small path
     RdTmp tmp(st);
     float* dv; uint32_t* di;
     RD_CUDA(tmp.alloc(&dv, (size_t)nv * 3)); RD_CUDA(tmp.alloc(&di, (size_t)nt * 3));
@@ -857,7 +935,8 @@ extern "C" int rd_blas_free(rd_platform* p, rd_blas* b)
     if (!b) return RD_OK;
     if (p) cudaSetDevice(p->device);
     if (b->pending) { cudaEventSynchronize(b->done); cudaEventDestroy(b->done); b->pending = 0; }
-    cudaFree(b->nodes); cudaFree(b->tris);
+    if (b->nodesChunk) rd_arena_drop(b->owner ? b->owner : p, b->nodesChunk); else cudaFree(b->nodes);
+    if (b->trisChunk) rd_arena_drop(b->owner ? b->owner : p, b->trisChunk); else cudaFree(b->tris);
     delete b;
     return RD_OK;
 }

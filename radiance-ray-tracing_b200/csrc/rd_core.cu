@@ -82,6 +82,8 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     rd_comm_destroy(p);
     for (cudaStream_t bs : p->buildStreams) { cudaStreamSynchronize(bs); cudaStreamDestroy(bs); }
     for (uint32_t* hsum : p->summaryHost) cudaFreeHost(hsum);
+    for (RdArenaChunk* c : p->arenaChunks) { cudaFree(c->base); cudaEventDestroy(c->idle); delete c; }
+    for (void* q : p->buildScratch) if (q) cudaFree(q);
     for (int k = 0; k < 4; ++k) for (cudaEvent_t e : p->upFence[k]) cudaEventDestroy(e);
     if (p->upHost) cudaFreeHost(p->upHost);
     for (cudaEvent_t e : p->tlEvents) cudaEventDestroy(e);
@@ -415,6 +417,8 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
         rd_wf_release(p);
         cudaMemPool_t pool;
         if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);
+        for (cudaStream_t bs : p->buildStreams) cudaStreamSynchronize(bs);
+        rd_arena_trim(p);
     }
     else if (!strcmp(key, "wf_lanes")) p->optWfLanes = value >= 2 ? 2 : 1;
     else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)

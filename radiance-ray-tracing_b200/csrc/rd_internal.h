@@ -30,14 +30,21 @@ struct RdHandleObj {
 };
 #define RD_HANDLE_MAGIC 0x4f484452u
 
+// Device memory of small bottom-level structures comes out of big chunks (rd_build.cu): a scene of thousands of small meshes
+// otherwise makes tens of thousands of stream-ordered allocations, and from a cold pool those cost more than the builds.
+// kind 0 = staging (worst-case node arrays of unresolved builds), kind 1 = final (triangle records, exact node arrays).
+struct RdArenaChunk { char* base; size_t size, used; unsigned live; int kind; cudaEvent_t idle; bool idleRecorded; };
+
 struct rd_blas {
     RdNode8* nodes; RdTri* tris;
+    RdArenaChunk *nodesChunk, *trisChunk;   // 0: the array is an allocation of its own (cudaFree)
     uint32_t nodeCount, triCount, levels;
     float lo[3], hi[3];
     // deferred small build (rd_build.cu): node count / root box not read back yet
     int pending, failed; cudaEvent_t done; volatile uint32_t* summary; struct rd_platform* owner;
 };
 int rd_blas_resolve(struct rd_platform* p, rd_blas* b);
+void rd_arena_trim(struct rd_platform* p);   // rd_build.cu: release the chunks nothing lives in and the per-stream build scratch
 
 struct rd_module {
     CUmodule mod; CUfunction raygen;
@@ -90,6 +97,8 @@ struct rd_platform {
     long optAsyncBuild, optPrecDiv, optL2Persist;
     // page-locked staging ring of the small-mesh uploads (rd_build.cu): RD_UPLOAD_SEGMENTS segments, a segment is reused once the
     // fence events recorded on every side stream when it was left have fired
+    std::vector<RdArenaChunk*> arenaChunks; RdArenaChunk* arenaCur[2];
+    std::vector<void*> buildScratch; std::vector<size_t> buildScratchBytes;   // one persistent scratch block per side stream
     unsigned char* upHost; size_t upSegBytes, upOff; unsigned upSeg;
     std::vector<cudaEvent_t> upFence[4]; bool upFenced[4];
     void* comm;                                  // RdComm* (rd_comm.cu): the NCCL communicator of the multi-GPU frame gather

@@ -235,10 +235,10 @@ __global__ void rd_k_wf_ray_scatter(const RdWfState* __restrict__ wfp)
 __global__ void rd_k_wf_advance(RdWfState* wf, unsigned op, unsigned a, unsigned b)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    if (op == 0) { wf->frameID = a; wf->samples = b; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; }   // new pass: first frame id, samples in flight
+    if (op == 0) { wf->frameID = a; wf->samples = b; wf->depth = 0; wf->cur = 0; wf->counts[2] = 0; wf->counts[3] = 0; }   // new pass: first frame id, samples in flight
     else if (op == 1) { wf->counts[2] = 0; }                                                           // before trace
     else if (op == 3) { const unsigned n = wf->counts[wf->cur]; wf->counts[wf->cur] = 0; wf->cur ^= 1u; wf->counts[wf->cur] = n; }   // after a ray reorder
-    else if (op == 2) { wf->cur ^= 1u; wf->counts[wf->cur ^ 1u] = 0; wf->depth += 1; wf->counts[2] = 0; } // after shade
+    else if (op == 2) { wf->cur ^= 1u; wf->counts[wf->cur ^ 1u] = 0; wf->depth += 1; wf->counts[2] = 0; wf->counts[3] = 0; } // after shade
 }
 
 // ---- launch wrappers used by the stage sequencer in rd_program.cu -------------------------------

@@ -564,7 +564,7 @@ def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
                 assert np.array_equal(a, c), "two-lane frame differs (wf_paths %d, sort %d)" % (paths, srt)
     finally:
         plt.set_option("wavefront", 0)
-        plt.set_option("wf_lanes", 1)
+        plt.set_option("wf_lanes", 2)   # the default
         plt.set_option("wf_paths", 1 << 25)
         plt.set_option("wf_sort", 1)
 
@@ -582,6 +582,7 @@ def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
     rd.BindDescriptorSet(plt, ds.descriptors)
     out = []
     plt.set_option("wavefront", 1)
+    plt.set_option("wf_lanes", 1)   # one lane: the pass counts asserted below are those of a single queue set
     try:
         for paths in (1, 2 * w * h, 1 << 25):
             plt.set_option("wf_paths", paths)
@@ -594,6 +595,7 @@ def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
             out.append((first, ds.read_scratch(), ds.read_image(), plt.launch_count() - l0))
     finally:
         plt.set_option("wavefront", 0)
+        plt.set_option("wf_lanes", 2)
         plt.set_option("wf_paths", 1 << 25)
     for first, second, image, _ in out[1:]:
         assert np.array_equal(first, out[0][0]) and np.array_equal(second, out[0][1]) and np.array_equal(image, out[0][2])

@@ -73,6 +73,10 @@ def run_device(label, env):
             b.free()
 
 
+if len(sys.argv) > 2 and sys.argv[2] == "once":   # one cold run under the environment as given (first build of a fresh process)
+    env = {k: os.environ[k] for k in ("RD_BUILD_UNFUSED", "RD_BUILD_STREAMS", "RD_BUILD_PAGEABLE") if k in os.environ}
+    run("cold: %s prewarm %s" % (env, os.environ.get("RD_POOL_PREWARM_MB", "default")), env)
+    sys.exit(0)
 for ns in (8, 16, 32, 64):
     run("fused, %d streams" % ns, {"RD_BUILD_STREAMS": str(ns)})
 run_device("device arrays, fused, 32", {"RD_BUILD_STREAMS": "32"})
