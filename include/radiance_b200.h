@@ -241,8 +241,9 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wf_paths" (default 2^25: paths in flight per wavefront pass -- RTProp.batchSize samples of every work-item are
  * generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path; 1 = one sample
  * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order),
- * "wf_lanes" (1 / 2, default 2: the sample passes of a wavefront frame alternate between two queue sets on two streams, so the
- * tail of one pass's stage -- its longest rays -- overlaps the other pass's stages; same image bit for bit, same HBM),
+ * "wf_lanes" (1..4, default 2: the sample passes of a wavefront frame go round robin over that many queue sets, each on its own
+ * stream, so the tail of one pass's stage -- its longest rays -- overlaps the other passes' stages; same image bit for bit, same
+ * HBM; 3 and 4 lanes measured no faster than 2),
  * "stream_image" (default 0; modules created while it is 1 also carry the band-reporting raygen that
  * rd_buffer_stream_to_host needs),
  * "trim_pool" (any value: releases what the library keeps between calls -- the stream-ordered build scratch held in the

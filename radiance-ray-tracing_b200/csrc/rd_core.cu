@@ -48,7 +48,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     p->buildNext = 0; p->summaryUsed = 0; p->optAsyncBuild = 1; p->optPrecDiv = 0; p->optL2Persist = 0;   // off by default: +3 % on the 10 M-triangle primary frame at 96 MB, but the wavefront queues lose the L2 they
     // stream through (C3 42.6 -> 58.0 ms, C5 488 -> 709 ms; profiles/README_r2.md)
     if (const char* e = getenv("RD_L2_PERSIST")) p->optL2Persist = atol(e);
-    if (const char* e = getenv("RD_WF_LANES")) p->optWfLanes = atol(e) >= 2 ? 2 : 1;   // developer knob for A/B runs of bench.py
+    if (const char* e = getenv("RD_WF_LANES")) { p->optWfLanes = atol(e); if (p->optWfLanes < 1) p->optWfLanes = 1; if (p->optWfLanes > RD_WF_MAX_LANES) p->optWfLanes = RD_WF_MAX_LANES; }   // developer knob for A/B runs of bench.py
     p->comm = 0; p->unitSlots = 0; p->unitSlotsDev = 0; p->unitEvent = 0; p->optWfTimeline = 0; p->tlUsed = 0;
     p->launches = 0;
     RD_CUDA(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
@@ -89,7 +89,7 @@ extern "C" int rd_platform_destroy(rd_platform* p)
     for (cudaEvent_t e : p->tlEvents) cudaEventDestroy(e);
     if (p->unitSlots) { cudaFreeHost((void*)p->unitSlots); cudaEventDestroy(p->unitEvent); }
     rd_wf_release(p);
-    if (p->wfStreamB) { cudaStreamDestroy(p->wfStreamB); for (int k = 0; k < 4; ++k) cudaEventDestroy(p->wfEvents[k]); }
+    if (p->wfStreamX[0]) { for (int k = 0; k < RD_WF_MAX_LANES - 1; ++k) cudaStreamDestroy(p->wfStreamX[k]); for (int k = 0; k <= RD_WF_MAX_LANES; ++k) cudaEventDestroy(p->wfEvents[k]); }
     { cudaMemPool_t pool; if (cudaDeviceGetDefaultMemPool(&pool, p->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0); }
     cudaFreeHost((void*)p->hstatus);
     cudaFree(p->dRayCounter);
@@ -420,7 +420,7 @@ extern "C" int rd_set_option(rd_platform* p, const char* key, long value)
         for (cudaStream_t bs : p->buildStreams) cudaStreamSynchronize(bs);
         rd_arena_trim(p);
     }
-    else if (!strcmp(key, "wf_lanes")) p->optWfLanes = value >= 2 ? 2 : 1;
+    else if (!strcmp(key, "wf_lanes")) p->optWfLanes = value < 1 ? 1 : (value > RD_WF_MAX_LANES ? RD_WF_MAX_LANES : value);
     else if (!strcmp(key, "wf_paths")) p->optWfPaths = value < 1 ? 1 : value;   // paths in flight per wavefront pass (0/1 = one sample per pass)
     else if (!strcmp(key, "stealing")) p->optSteal = value;
     else if (!strcmp(key, "stream_image")) p->optStreamImage = value;   // modules created from now on carry the band-reporting raygen

@@ -65,6 +65,7 @@ struct RdWfBuffers {
 
 int rd_check_status(struct rd_platform* p, const char* where);   // rd_core.cu
 
+#define RD_WF_MAX_LANES 4
 struct rd_platform {
     int device;
     cudaStream_t stream;
@@ -88,10 +89,10 @@ struct rd_platform {
     unsigned ilWorld, ilRank, ilBandRows;        // interleaved multi-GPU partition of the launch being issued
     unsigned* stealCounters; unsigned* stealOwned; int stealImported; unsigned stealSlots, stealOwnedCap;
     RdWfBuffers wf;
-    // second wavefront lane (option "wf_lanes" = 2): the sample passes of a frame alternate between two sets of queues on two
-    // streams, so the tail of one pass's stage (its longest rays) overlaps the other pass's stages; wfLane selects the set the
-    // rd_wf_* launch wrappers work on
-    RdWfBuffers wfB; cudaStream_t wfStreamB; cudaEvent_t wfEvents[4]; int wfLane; long optWfLanes;
+    // further wavefront lanes (option "wf_lanes" = 2..4): the sample passes of a frame go round robin over that many sets of
+    // queues, each on its own stream, so the tail of one pass's stage (its longest rays) overlaps the other passes' stages;
+    // wfLane selects the set the rd_wf_* launch wrappers work on (0 = wf on the platform stream)
+    RdWfBuffers wfX[RD_WF_MAX_LANES - 1]; cudaStream_t wfStreamX[RD_WF_MAX_LANES - 1]; cudaEvent_t wfEvents[RD_WF_MAX_LANES + 1]; int wfLane; long optWfLanes;
     std::vector<cudaStream_t> buildStreams; size_t buildNext;   // side streams of deferred small bottom-level builds
     std::vector<uint32_t*> summaryHost, summaryDev; size_t summaryUsed;   // host-mapped build summaries, RD_SUMMARY_CHUNK per chunk
     long optAsyncBuild, optPrecDiv, optL2Persist;
@@ -144,8 +145,8 @@ int rd_build_wide_bvh(rd_platform* p, const RdF4* dlo, const RdF4* dhi, uint32_t
 
 // rd_wavefront.cu
 struct RdWfState;
-static inline RdWfBuffers& rd_wf_buffers(rd_platform* p) { return p->wfLane ? p->wfB : p->wf; }
-static inline cudaStream_t rd_wf_stream(rd_platform* p) { return p->wfLane ? p->wfStreamB : p->stream; }
+static inline RdWfBuffers& rd_wf_buffers(rd_platform* p) { return p->wfLane ? p->wfX[p->wfLane - 1] : p->wf; }
+static inline cudaStream_t rd_wf_stream(rd_platform* p) { return p->wfLane ? p->wfStreamX[p->wfLane - 1] : p->stream; }
 int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride);
 void rd_wf_release(rd_platform* p);
 int rd_wf_upload_state(rd_platform* p, const RdWfState* host);

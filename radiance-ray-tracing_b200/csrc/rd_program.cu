@@ -775,12 +775,13 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     if (resetTimeline) p->tlUsed = 0;
     const unsigned stride = (m->wfPayloadSize + 15u) & ~15u;
     // two lanes (option wf_lanes): the passes of the frame alternate between two queue sets on two streams
-    const int lanes = (p->optWfLanes >= 2 && rt[1] >= 2 && !rt[3] && !p->optWfTimeline) ? 2 : 1;
+    int lanes = (p->optWfLanes >= 2 && !rt[3] && !p->optWfTimeline) ? (int)p->optWfLanes : 1;
+    if (lanes > (int)rt[1]) lanes = rt[1] ? (int)rt[1] : 1;   // no more lanes than samples
     // samples in flight per pass: as many as option wf_paths allows (HBM: ~200 B per path)
     unsigned long long inFlight = (unsigned long long)p->optWfPaths / ((unsigned long long)lanes * count);
     if (inFlight < 1) inFlight = 1;
     if (inFlight > rt[1]) inFlight = rt[1] ? rt[1] : 1;
-    if (lanes == 2 && inFlight > (rt[1] + 1u) / 2u) inFlight = (rt[1] + 1u) / 2u;   // at least one pass per lane
+    if (lanes > 1 && inFlight > (rt[1] + (unsigned)lanes - 1u) / (unsigned)lanes) inFlight = (rt[1] + (unsigned)lanes - 1u) / (unsigned)lanes;   // at least one pass per lane
     if (rt[3]) inFlight = 1;                       // debug views stop after one bounce of one sample at a time
     while (inFlight * count > 0x7fffffffull) --inFlight;
     const unsigned paths = (unsigned)(inFlight * count);
@@ -794,19 +795,19 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
     unsigned infoTiled[8]; memcpy(infoTiled, info, sizeof(info));
     infoTiled[2] = (p->optTile && (width % 8u) == 0 && (height % 4u) == 0) ? width : 0u;
     RD_CU(cuMemcpyHtoDAsync(dinfo, infoTiled, sizeof(infoTiled), (CUstream)p->stream));
-    if (lanes == 2) {
-        if (!p->wfStreamB) {
-            RD_CUDA(cudaStreamCreateWithFlags(&p->wfStreamB, cudaStreamNonBlocking));
-            for (int k = 0; k < 4; ++k) RD_CUDA(cudaEventCreateWithFlags(&p->wfEvents[k], cudaEventDisableTiming));
+    if (lanes > 1) {
+        if (!p->wfStreamX[0]) {
+            for (int k = 0; k < RD_WF_MAX_LANES - 1; ++k) RD_CUDA(cudaStreamCreateWithFlags(&p->wfStreamX[k], cudaStreamNonBlocking));
+            for (int k = 0; k <= RD_WF_MAX_LANES; ++k) RD_CUDA(cudaEventCreateWithFlags(&p->wfEvents[k], cudaEventDisableTiming));
         }
-        // lane 1 starts behind everything queued on the platform stream so far (descriptor writes, the launch info above)
-        RD_CUDA(cudaEventRecord(p->wfEvents[2], p->stream));
-        RD_CUDA(cudaStreamWaitEvent(p->wfStreamB, p->wfEvents[2], 0));
+        // the other lanes start behind everything queued on the platform stream so far (descriptor writes, the launch info above)
+        RD_CUDA(cudaEventRecord(p->wfEvents[RD_WF_MAX_LANES], p->stream));
+        for (int k = 1; k < lanes; ++k) RD_CUDA(cudaStreamWaitEvent(p->wfStreamX[k - 1], p->wfEvents[RD_WF_MAX_LANES], 0));
     }
     int rc = RD_OK;
     RdWfState S; memset(&S, 0, sizeof(S));
-    std::vector<uint64_t> args[2];
-    std::vector<void*> argv[2];
+    std::vector<uint64_t> args[RD_WF_MAX_LANES];
+    std::vector<void*> argv[RD_WF_MAX_LANES];
     for (int lane = 0; lane < lanes; ++lane) {
         p->wfLane = lane;
         rc = rd_wf_reserve(p, paths, stride);
@@ -860,15 +861,15 @@ static int rd_trace_rays_wavefront(rd_platform* p, unsigned width, unsigned heig
         if (rc) break;
         rd_tl_mark(p, 5);
         // the running mean is taken in frame order: this pass's accumulate runs behind the previous pass's (the other lane's)
-        if (lanes == 2 && pass > 0) RD_CUDA(cudaStreamWaitEvent((cudaStream_t)st, p->wfEvents[1 - lane], 0));
+        if (lanes > 1 && pass > 0) RD_CUDA(cudaStreamWaitEvent((cudaStream_t)st, p->wfEvents[(pass - 1u) % (unsigned)lanes], 0));
         RD_CU(cuLaunchKernel(m->wfAccumulate, blocks, 1, 1, 128, 1, 1, 0, st, argv[lane].data(), 0));
         p->launches += 1;
-        if (lanes == 2) RD_CUDA(cudaEventRecord(p->wfEvents[lane], (cudaStream_t)st));
+        if (lanes > 1) RD_CUDA(cudaEventRecord(p->wfEvents[lane], (cudaStream_t)st));
     }
     const int lastLane = pass ? (int)((pass - 1u) % (unsigned)lanes) : 0;
     p->wfLane = 0;
     if (rc) return rc;
-    if (lanes == 2 && lastLane == 1) RD_CUDA(cudaStreamWaitEvent(p->stream, p->wfEvents[1], 0));   // resolve (and whatever follows) behind lane 1
+    if (lanes > 1 && lastLane != 0) RD_CUDA(cudaStreamWaitEvent(p->stream, p->wfEvents[lastLane], 0));   // resolve (and whatever follows) behind the last pass
     rd_tl_mark(p, 6);
     RD_CU(cuLaunchKernel(m->wfResolve, blocks, 1, 1, 128, 1, 1, 0, (CUstream)p->stream, argv[0].data(), 0));
     p->launches += 1;

@@ -268,8 +268,8 @@ int rd_wf_reserve(rd_platform* p, unsigned count, unsigned payloadStride)
 
 void rd_wf_release(rd_platform* p)
 {
-    for (int lane = 0; lane < 2; ++lane) {
-        RdWfBuffers& B = lane ? p->wfB : p->wf;
+    for (int lane = 0; lane < RD_WF_MAX_LANES; ++lane) {
+        RdWfBuffers& B = lane ? p->wfX[lane - 1] : p->wf;
         void* all[] = {B.payload, B.color, B.contrib, B.rayA[0], B.rayA[1], B.rayB[0], B.rayB[1], B.pathOf[0], B.pathOf[1],
                        B.hitA, B.hitB, B.keys, B.order, B.counts, B.hist, B.dstate};
         for (void* q : all) if (q) cudaFree(q);

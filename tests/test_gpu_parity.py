@@ -533,7 +533,7 @@ def test_c3_full_size_properties(pkg, plt):
 
 
 def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
-    """Option wf_lanes = 2: the passes of a frame alternate between two queue sets on two streams (stage tails of one pass overlap
+    """Option wf_lanes = 2..4: the passes of a frame go round robin over that many queue sets on as many streams (stage tails of one pass overlap
     the other pass's stages); the running mean is still taken in frame order, so scratch and image are bit-identical with the
     single-lane frame -- for an even and an odd number of passes, with the hit-group sort on and off, and when a second call
     continues the accumulation."""
@@ -549,7 +549,7 @@ def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
     try:
         for paths, srt in ((1 << 25, 1), (2 * w * h, 1), (w * h, 0)):
             got = {}
-            for lanes in (1, 2):
+            for lanes in (1, 2, 3, 4):
                 plt.set_option("wf_lanes", lanes)
                 plt.set_option("wf_paths", paths)
                 plt.set_option("wf_sort", srt)
@@ -560,8 +560,9 @@ def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
                 rd.TraceRays(plt, 0, 0, 0, w, h)
                 got[lanes] = (first, ds.read_scratch(), ds.read_image())
                 assert plt.status() == (0, 0)
-            for a, c in zip(got[1], got[2]):
-                assert np.array_equal(a, c), "two-lane frame differs (wf_paths %d, sort %d)" % (paths, srt)
+            for lanes in (2, 3, 4):
+                for a, c in zip(got[1], got[lanes]):
+                    assert np.array_equal(a, c), "%d-lane frame differs (wf_paths %d, sort %d)" % (lanes, paths, srt)
     finally:
         plt.set_option("wavefront", 0)
         plt.set_option("wf_lanes", 2)   # the default

@@ -29,7 +29,7 @@ plt.set_option("wavefront", 1)
 L = rd.lib()
 base = {}
 for world in (1, 8):
-    for lanes in (1, 2):
+    for lanes in (1, 2, 3, 4):
         plt.set_option("wf_lanes", lanes)
         ms = []
         for it in range(5):
