@@ -311,11 +311,25 @@ def c1_config(torch, pkg, plt, stream, flush):
     pipe, module = scenes.make_pipeline(plt, source=src, sbt=sbt_text)
     rd.BindPipeline(plt, pipe)
     ms = time_frames(torch, plt, rd, stream, flush, w, h, reps=5)
+    out = {"workload": "C1: samples/shader.cl + samples/sbt.json as shipped, Cornell-like scene (%d triangles), 800x600, 16 spp, depth 8" % b.triangle_count(),
+           "rays_per_frame": rays, "value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "raygen": module.info(),
+           "parity": "tests/test_gpu_c1.py compares this frame with the reference runtime (profiles/parity_r2.json)"}
+    # the same unmodified file with the two wavefront hooks a host appends (programs/shader_wavefront_hooks.cl): stage launches
+    hooks = os.path.join(ROOT, "radiance-ray-tracing_b200", "programs", "shader_wavefront_hooks.cl")
+    try:
+        pipe, module = scenes.make_pipeline(plt, source=src + "\n" + open(hooks).read(), sbt=sbt_text)
+        rd.BindPipeline(plt, pipe)
+        plt.set_option("wavefront", 1)
+        wms = time_frames(torch, plt, rd, stream, flush, w, h, reps=5)
+        out["wavefront_with_hooks"] = {"ms_per_frame": wms, "value": rays / wms / 1e3,
+                                       "program": "samples/shader.cl + programs/shader_wavefront_hooks.cl (two functions appended by the host)"}
+    except Exception as e:
+        out["wavefront_with_hooks"] = {"error": repr(e)[:300]}
+    finally:
+        plt.set_option("wavefront", 0)
     for hnd in [tlas] + list(blas):
         hnd.free()
-    return {"workload": "C1: samples/shader.cl + samples/sbt.json as shipped, Cornell-like scene (%d triangles), 800x600, 16 spp, depth 8" % b.triangle_count(),
-            "rays_per_frame": rays, "value": rays / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms, "raygen": module.info(),
-            "parity": "tests/test_gpu_c1.py compares this frame with the reference runtime (profiles/parity_r2.json)"}
+    return out
 
 
 _UNIT_FRAME = [1000]

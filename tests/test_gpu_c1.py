@@ -111,6 +111,31 @@ def test_c1_shader_cl_as_shipped_matches_reference(pkg, plt, ref, c1_sources, pa
         assert len(np.unique(img[..., :3].reshape(-1, 3), axis=0)) > 2000
 
 
+def test_c1_shader_cl_in_wavefront_mode(pkg, plt, ref, c1_sources, parity_log):
+    """samples/shader.cl, unmodified, with the two wavefront hooks a host appends (programs/shader_wavefront_hooks.cl): the
+    stage launches render the frame of the inline raygen (same float sequence per sample; the shade stage evaluates a path's
+    hit shader in another order than a neighbour's, not another arithmetic) and the reference's frame within the C1 bar."""
+    import os
+    rd, scenes = pkg.rd, pkg.scenes
+    src, sbt = c1_sources
+    hooks = open(os.path.join(os.path.dirname(scenes.__file__), "programs", "shader_wavefront_hooks.cl")).read()
+    b = c1_bundle(scenes)
+    rt = scenes.rtprop(0, 16, 8, 0)
+    inline_img, inline_scr, _ = gpu_frame(pkg, plt, b, rt, src, sbt)
+    plt.set_option("wavefront", 1)
+    try:
+        wf_img, wf_scr, ds = gpu_frame(pkg, plt, b, rt, src + "\n" + hooks, sbt)
+        assert plt.status() == (0, 0)
+    finally:
+        plt.set_option("wavefront", 0)
+    d = wf_img[..., :3].astype(np.float64) - inline_img[..., :3].astype(np.float64)
+    rmse_inline = float(np.sqrt((d * d).mean()))
+    exp, exp_scratch = reference_frame(ref, scenes, b, rt)
+    rmse = compare(wf_img, wf_scr, exp, exp_scratch, C1_RMSE_U8_16, parity_log, "C1_shader_cl_wavefront_16spp")
+    parity_log.record("C1_shader_cl_wavefront_16spp", rmse_u8_vs_inline=rmse_inline)
+    assert rmse_inline <= 0.5, "wavefront vs inline RMSE %g" % rmse_inline
+
+
 def test_c1_generated_dispatchers_equal_handwritten(pkg, plt, ref, c1_sources):
     """The same file with callHit / callMiss / callAnyHit removed: generated from sbt.json, bit-identical frame."""
     scenes = pkg.scenes
