@@ -158,6 +158,16 @@ def reference_arm(args, rank, world):
                       "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
 
 
+def opencl_cpu_device_note():
+    """the reference's true path is clBuildProgram on a PoCL CPU device; it is timed only where an OpenCL
+    platform exists at run time. This box has no ICD, so the row reads 'PoCL not present' (the timed arm is the reference's own
+    sources compiled as C++)."""
+    import ctypes.util
+    if not (ctypes.util.find_library("OpenCL") and os.path.isdir("/etc/OpenCL/vendors") and os.listdir("/etc/OpenCL/vendors")):
+        return "PoCL not present"
+    return "an OpenCL ICD is installed on this box; the PoCL path is not wired into this bench"
+
+
 def cpu_baseline_leg(pkg, ref, bundle):
     """Reference CPU path on a bounded sample (rank 0, N=1 only): see reference_arm for the sample."""
     scenes = pkg.scenes
@@ -180,7 +190,8 @@ def cpu_baseline_leg(pkg, ref, bundle):
         best = dt if best is None or dt < best else best
     return {"value": count / best / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
             "sample": "%d of %d image rows (%d rays), best of 3, all host threads; reference SAH build took %.1f s (not timed)"
-                      % (rows, HEIGHT, count, build_s)}
+                      % (rows, HEIGHT, count, build_s),
+            "opencl_path": opencl_cpu_device_note()}
 
 
 def time_frames(torch, plt, rd, stream, flush, w, h, reps=3):
