@@ -247,7 +247,8 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "stream_image" (default 0; modules created while it is 1 also carry the band-reporting raygen that
  * rd_buffer_stream_to_host needs),
  * "trim_pool" (any value: releases what the library keeps between calls -- the stream-ordered build scratch held in the
- * device's memory pool and the wavefront queues, up to ~200 B x wf_paths -- they are allocated again on demand) */
+ * device's memory pool, the per-stream scratch blocks and the empty 64 MB chunks of the small-mesh builds, and the wavefront
+ * queues, up to ~200 B x wf_paths -- they are allocated again on demand) */
 int rd_set_option(rd_platform* p, const char* key, long value);
 /* traceRay invocations counted by modules compiled with option count_rays (primary + bounce + shadow
  * rays, radiance/shader/radiance.cl:254); synchronises the platform stream; reset != 0 zeroes the counter */
