@@ -28,6 +28,7 @@ struct RdDriver {
     CUresult (*MemcpyHtoDAsync)(CUdeviceptr, const void*, size_t, CUstream);
     CUresult (*GetErrorString)(CUresult, const char**);
     CUresult (*OccupancyMaxActiveBlocksPerMultiprocessor)(int*, CUfunction, int, size_t);
+    CUresult (*FuncSetAttribute)(CUfunction, CUfunction_attribute, int);
     bool ok;
 };
 static RdDriver g_drv;
@@ -40,7 +41,8 @@ static int rd_driver_init()
         {"cuModuleGetFunction", (void**)&g_drv.ModuleGetFunction}, {"cuModuleGetGlobal", (void**)&g_drv.ModuleGetGlobal},
         {"cuFuncGetAttribute", (void**)&g_drv.FuncGetAttribute}, {"cuLaunchKernel", (void**)&g_drv.LaunchKernel},
         {"cuMemcpyHtoDAsync", (void**)&g_drv.MemcpyHtoDAsync}, {"cuGetErrorString", (void**)&g_drv.GetErrorString},
-        {"cuOccupancyMaxActiveBlocksPerMultiprocessor", (void**)&g_drv.OccupancyMaxActiveBlocksPerMultiprocessor}};
+        {"cuOccupancyMaxActiveBlocksPerMultiprocessor", (void**)&g_drv.OccupancyMaxActiveBlocksPerMultiprocessor},
+        {"cuFuncSetAttribute", (void**)&g_drv.FuncSetAttribute}};
     for (auto& e : tab) {
         cudaDriverEntryPointQueryResult q;
         cudaError_t err = cudaGetDriverEntryPoint(e.name, e.slot, cudaEnableDefault, &q);
@@ -63,6 +65,7 @@ static int rd_driver_init()
 #define cuMemcpyHtoDAsync g_drv.MemcpyHtoDAsync
 #define cuGetErrorString g_drv.GetErrorString
 #define cuOccupancyMaxActiveBlocksPerMultiprocessor g_drv.OccupancyMaxActiveBlocksPerMultiprocessor
+#define cuFuncSetAttribute g_drv.FuncSetAttribute
 
 // ---- sbt.json ---------------------------------------------------------------------------------
 struct SbtRow { std::string raygen, closestHit, anyHit, miss; };
@@ -679,6 +682,8 @@ extern "C" int rd_shader_module_create(rd_platform* p, const char* code, unsigne
         for (int i = 0; i < 4; ++i) m->wfRay[i] = hq[1 + i];
         if (!m->wfPayloadSize) m->wfGenerate = 0;
     } else m->wfGenerate = 0;
+    if (const char* e = getenv("RD_L1_CARVEOUT"))   // developer knob: preferred shared-memory carve-out of the raygen kernel in percent (0 = all L1)
+        cuFuncSetAttribute(m->raygen, CU_FUNC_ATTRIBUTE_PREFERRED_SHARED_MEMORY_CARVEOUT, atoi(e));
     cuFuncGetAttribute(&m->numRegs, CU_FUNC_ATTRIBUTE_NUM_REGS, m->raygen);
     cuFuncGetAttribute(&m->localBytes, CU_FUNC_ATTRIBUTE_LOCAL_SIZE_BYTES, m->raygen);
     *out = m;
