@@ -297,12 +297,11 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "    wavefrontPrimary(&pl, &sd, frameID, wf.totalSamples);\n"
          "    pl.hit = false;\n"
          "    *(struct Payload*)(wf.payload + (size_t)slot * wf.payloadStride) = pl;\n"
-         "    RdF4 a, b, one, zero;\n"
+         "    RdF4 a, b;\n"
          "    a.x = pl.nextRayOrigin.x; a.y = pl.nextRayOrigin.y; a.z = pl.nextRayOrigin.z; a.w = wf.tmin;\n"
          "    b.x = pl.nextRayDirection.x; b.y = pl.nextRayDirection.y; b.z = pl.nextRayDirection.z; b.w = wf.tmax;\n"
-         "    one.x = one.y = one.z = one.w = 1.0f; zero.x = zero.y = zero.z = zero.w = 0.0f;\n"
          "    wf.rayA[wf.cur][slot] = a; wf.rayB[wf.cur][slot] = b; wf.pathOf[wf.cur][slot] = slot;\n"
-         "    wf.color[slot] = zero; wf.contrib[slot] = one;\n"
+         "    // color = 0 and contribution = 1 (shader.cl:231-232) are not stored: the first shade stage starts from them\n"
          "    if (slot == 0) { wf.counts[wf.cur] = wf.count * wf.samples; wf.counts[wf.cur ^ 1u] = 0u; }\n"
          "}\n\n";
     // The shade stage carries the inline shadow traversal: 6 resident 128-thread blocks per SM (80 registers) measured
@@ -336,7 +335,9 @@ static std::string generate_wavefront_kernels(const std::vector<RaygenParam>& P,
          "        rd_l1::callMiss(wf.missIndex, (rd_l1::Payload*)&pl, (rd_l1::SceneData*)&sd, " + image + ", " + sampler + ");\n"
          "    }\n"
          "    // bounce loop body of samples/shader.cl:238-260\n"
-         "    RdF4 col = wf.color[slot], con = wf.contrib[slot];\n"
+         "    RdF4 col, con;\n"
+         "    if (wf.depth == 0u) { col.x = col.y = col.z = col.w = 0.0f; con.x = con.y = con.z = con.w = 1.0f; }\n"
+         "    else { col = wf.color[slot]; con = wf.contrib[slot]; }\n"
          "    bool more = false;\n"
          "    if (pl.hit) {\n"
          "        col.x += con.x * pl.color.x; col.y += con.y * pl.color.y; col.z += con.z * pl.color.z;\n"
