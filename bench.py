@@ -258,7 +258,13 @@ def primary_config(torch, pkg, plt, stream, flush, name, grid_n, key):
     t0 = time.perf_counter()
     tlas, blas = scenes.build_scene(plt, bundle)
     plt.sync()
-    build_ms = (time.perf_counter() - t0) * 1e3
+    build_ms = (time.perf_counter() - t0) * 1e3   # first build of this size in the process: pool growth, first pageable upload
+    for hnd in [tlas] + list(blas):
+        hnd.free()
+    t0 = time.perf_counter()
+    tlas, blas = scenes.build_scene(plt, bundle)
+    plt.sync()
+    build_warm_ms = (time.perf_counter() - t0) * 1e3
     ds = scenes.DeviceScene(plt, bundle, tlas, WIDTH, HEIGHT, scenes.rtprop(0, 1, 1, 0))
     pipe, module = scenes.make_pipeline(plt, "primary")
     rd.BindPipeline(plt, pipe)
@@ -279,7 +285,7 @@ def primary_config(torch, pkg, plt, stream, flush, name, grid_n, key):
     achieved = n * bytes_per_ray / (ms * 1e-3) / 1e9
     ncu = ncu_reference(key) or {}
     out = {"workload": name, "triangles": bundle.triangle_count(), "value": n / ms / 1e3, "unit": "Mrays/s", "ms_per_frame": ms,
-           "build_ms_incl_upload": build_ms, "bvh": blas[0].stats(), "raygen": module.info(),
+           "build_ms_incl_upload": build_ms, "build_ms_incl_upload_warm": build_warm_ms, "bvh": blas[0].stats(), "raygen": module.info(),
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": ncu.get("dram_bytes_per_launch"), "traffic_source": ncu.get("source"),
                         "algorithmic_bytes_per_launch": n * bytes_per_ray, "peak_kind": peak_kind,
