@@ -244,7 +244,7 @@ def extra_config(torch, pkg, plt, stream, flush, name, bundle, program, spp, dep
     finally:
         plt.set_option("wavefront", 0)
         plt.set_option("wf_sort", 1)
-        plt.set_option("wf_paths", 1 << 25)
+        plt.set_option("wf_paths", 1 << 26)
     for h in [tlas] + list(blas):
         h.free()
     return out
@@ -702,7 +702,7 @@ def main():
         if world == 1 and want:
             for h in [tlas] + list(blas):   # the extras build their own scenes
                 h.free()
-            inflight = 1 << 25   # paths in flight per wavefront pass (all 16 samples of a 1080p frame)
+            inflight = int(os.environ.get("RD_BENCH_WF_PATHS", 1 << 26))   # paths in flight per wavefront frame over both lanes (the library default: all 16 samples of a 1080p frame, 8 of a 4K frame); developer knob for A/B runs
             modes = (("inline", 0, 1, inflight), ("wavefront_sorted", 1, 1, inflight), ("wavefront_unsorted", 1, 0, inflight))
             out["extra"] = {}
             todo = [

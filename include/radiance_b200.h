@@ -238,9 +238,9 @@ int rd_generate_primary_rays(rd_platform* p, rd_handle camera, unsigned frameID,
  * "wf_ray_sort" (0/1, default 0: re-sort bounce rays by direction octant and origin cell before tracing them;
  * measured slower on C3 -- the pass costs more than the trace stage gains),
  * "wf_sort" (0/1, default 1: reorder each bounce's rays by hit-group row and material key before shading),
- * "wf_paths" (default 2^25: paths in flight per wavefront pass -- RTProp.batchSize samples of every work-item are
- * generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path; 1 = one sample
- * per pass. Images do not depend on it: finished samples are folded into imageScratch in frame order),
+ * "wf_paths" (default 2^26: paths in flight per wavefront frame, shared by the lanes -- RTProp.batchSize samples of every
+ * work-item are generated, traced and shaded together, as many as fit under this cap at ~200 B of HBM per path (13 GB at the
+ * default); 1 = one sample per pass. 4K 64 spp: 2^25 426 ms, 2^26 419 ms, 2^27 419 ms. Images do not depend on it: finished samples are folded into imageScratch in frame order),
  * "wf_lanes" (1..4, default 2: the sample passes of a wavefront frame go round robin over that many queue sets, each on its own
  * stream, so the tail of one pass's stage -- its longest rays -- overlaps the other passes' stages; same image bit for bit, same
  * HBM; 3 and 4 lanes measured no faster than 2),

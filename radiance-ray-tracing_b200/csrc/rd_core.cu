@@ -36,7 +36,7 @@ extern "C" int rd_platform_create(int device, rd_platform** out)
     rd_platform* p = new rd_platform();
     p->device = device;
     p->boundModule = 0;
-    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 25; p->optWfLanes = 2;
+    p->optFmad = 1; p->optTile = 1; p->optBlock = 128; p->optCountRays = 0; p->optMaxDepth = 2; p->optWavefront = 0; p->optWfSort = 1; p->optSteal = 0; p->optWfDynamic = 1; p->optWfRaySort = 0; p->optWfPaths = 1l << 26; p->optWfLanes = 2;
     p->ilWorld = p->ilRank = p->ilBandRows = 0;
     p->optStreamImage = 0;
     p->mirrorObj = 0; p->mirrorHost = 0; p->mirrorItemBytes = 0; p->mirrorBands = 0; p->mirrorValidBytes = 0; p->mirrorFresh = 0; p->copyPending = 0;

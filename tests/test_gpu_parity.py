@@ -566,7 +566,7 @@ def test_wavefront_two_lanes_render_the_single_lane_frame(pkg, plt):
     finally:
         plt.set_option("wavefront", 0)
         plt.set_option("wf_lanes", 2)   # the default
-        plt.set_option("wf_paths", 1 << 25)
+        plt.set_option("wf_paths", 1 << 26)
         plt.set_option("wf_sort", 1)
 
 
@@ -597,7 +597,7 @@ def test_wavefront_samples_in_flight_do_not_change_the_image(pkg, plt):
     finally:
         plt.set_option("wavefront", 0)
         plt.set_option("wf_lanes", 2)
-        plt.set_option("wf_paths", 1 << 25)
+        plt.set_option("wf_paths", 1 << 26)
     for first, second, image, _ in out[1:]:
         assert np.array_equal(first, out[0][0]) and np.array_equal(second, out[0][1]) and np.array_equal(image, out[0][2])
     assert out[0][3] > out[1][3] > out[2][3]            # 5, 3 and 1 passes per call
