@@ -24,6 +24,7 @@ rd.BindPipeline(plt, pipe)
 rd.BindDescriptorSet(plt, ds.descriptors)
 plt.set_option("wavefront", 1)
 plt.set_option("wf_timeline", 1)
+plt.set_option("wf_dynamic", int(os.environ.get("RD_WF_DYNAMIC", "1")))
 for rep in range(3):
     ds.set_rtprop(0, spp, depth)
     if world == 1:
