@@ -104,8 +104,8 @@ __global__ void __launch_bounds__(128, MINB) rd_k_wf_trace_dyn(const RdScene* __
 
 // ---- sort stage ---------------------------------------------------------------------------------
 // Counting sort of the queue entries by key (RD_WF_KEY_BINS bins): block-local histograms in shared
-// memory, one scan block, then a scatter in which every warp ranks its entries with match_any and
-// claims a run of output positions per distinct key with one atomic (warp-level compaction).
+// memory, one scan block, then a scatter in which every warp ranks its entries with match_any and the
+// block claims a run of output positions per distinct key with one atomic (rd_k_wf_scatter).
 __global__ void rd_k_wf_hist(const RdWfState* __restrict__ wfp)
 {
     __shared__ unsigned bins[RD_WF_KEY_BINS];
