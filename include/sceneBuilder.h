@@ -519,28 +519,67 @@ inline Mat4x4 nodeTransform(const Json& node)
     return m;
 }
 
-// aiProcess_GenSmoothNormals for meshes without NORMAL: area-weighted face normals summed over vertices that share a position
-inline std::vector<Vec3> smoothNormals(const std::vector<Vec3>& v, const std::vector<Triangle>& t)
+// aiProcess_GenSmoothNormals as assimp runs it on the importer's INDEXED mesh (GenVertexNormalsProcess.cpp:104-235, default
+// smoothing angle 175 degrees): every face writes its unit normal ((v1 - v0) x (v2 - v0), NormalizeSafe) to its three vertices
+// -- for a vertex shared by several faces the LAST face in index order wins -- and vertices at the same position then share the
+// normalised sum of those per-vertex normals (assimp groups positions within 1e-4 of the mesh's extent; exact equality here).
+inline std::vector<Vec3> importerNormals(const std::vector<Vec3>& v, const std::vector<Triangle>& t)
 {
+    std::vector<Vec3> perVertex(v.size(), Vec3(0.0f, 0.0f, 0.0f));
+    for (const Triangle& f : t) {
+        const Vec3 &a = v[f.idx0], &b = v[f.idx1], &c = v[f.idx2];
+        const float e1[3] = {b.x - a.x, b.y - a.y, b.z - a.z}, e2[3] = {c.x - a.x, c.y - a.y, c.z - a.z};
+        float n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
+        const float len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        if (len > 0.0f) { n[0] /= len; n[1] /= len; n[2] /= len; }
+        for (unsigned idx : {f.idx0, f.idx1, f.idx2}) perVertex[idx] = Vec3(n[0], n[1], n[2]);
+    }
     struct Key { float x, y, z; bool operator<(const Key& o) const { return x != o.x ? x < o.x : (y != o.y ? y < o.y : z < o.z); } };
     std::map<Key, size_t> groupOf;
     std::vector<size_t> group(v.size());
     for (size_t i = 0; i < v.size(); ++i) group[i] = groupOf.emplace(Key{v[i].x, v[i].y, v[i].z}, groupOf.size()).first->second;
-    std::vector<double> acc(groupOf.size() * 3, 0.0);
-    for (const Triangle& f : t) {
-        const Vec3 &a = v[f.idx0], &b = v[f.idx1], &c = v[f.idx2];
-        const double e1[3] = {(double)b.x - a.x, (double)b.y - a.y, (double)b.z - a.z}, e2[3] = {(double)c.x - a.x, (double)c.y - a.y, (double)c.z - a.z};
-        const double n[3] = {e1[1] * e2[2] - e1[2] * e2[1], e1[2] * e2[0] - e1[0] * e2[2], e1[0] * e2[1] - e1[1] * e2[0]};
-        for (unsigned idx : {f.idx0, f.idx1, f.idx2}) for (int k = 0; k < 3; ++k) acc[group[idx] * 3 + k] += n[k];
-    }
+    std::vector<float> acc(groupOf.size() * 3, 0.0f);
+    for (size_t i = 0; i < v.size(); ++i) { acc[group[i] * 3] += perVertex[i].x; acc[group[i] * 3 + 1] += perVertex[i].y; acc[group[i] * 3 + 2] += perVertex[i].z; }
     std::vector<Vec3> out(v.size());
     for (size_t i = 0; i < v.size(); ++i) {
-        const double* n = &acc[group[i] * 3];
-        double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
-        if (len == 0) len = 1;
-        out[i] = Vec3((float)(n[0] / len), (float)(n[1] / len), (float)(n[2] / len));
+        const float* n = &acc[group[i] * 3];
+        const float len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+        out[i] = len > 0.0f ? Vec3(n[0] / len, n[1] / len, n[2] / len) : Vec3(n[0], n[1], n[2]);
     }
     return out;
+}
+
+// The vertex numbering assimp hands to sceneBuilder.cpp: the glTF2 importer keeps only the vertices the index list uses and
+// numbers them in the order the index list first mentions them (glTF2Importer.cpp ImportMeshes, vertexRemappingTable); missing
+// normals are generated on that mesh; then aiProcess_JoinIdenticalVertices merges vertices whose position, normal and uv are
+// identical, keeping the first (JoinVerticesProcess.cpp:258-381; its comparison has a 1e-5 tolerance, exact equality is used
+// here). Triangles keep their order. `normals` empty = generate them.
+inline void importerVertexOrder(std::vector<Vec3>& v, std::vector<Triangle>& t, std::vector<Vec3>& normals, std::vector<Vec3>& uv)
+{
+    const unsigned none = 0xffffffffu;
+    std::vector<unsigned> remap(v.size(), none), order;
+    for (Triangle& f : t)
+        for (unsigned* idx : {&f.idx0, &f.idx1, &f.idx2}) {
+            if (remap[*idx] == none) { remap[*idx] = (unsigned)order.size(); order.push_back(*idx); }
+            *idx = remap[*idx];
+        }
+    std::vector<Vec3> v2(order.size()), uv2(order.size()), n2;
+    for (size_t i = 0; i < order.size(); ++i) { v2[i] = v[order[i]]; uv2[i] = uv[order[i]]; }
+    if (!normals.empty()) { n2.resize(order.size()); for (size_t i = 0; i < order.size(); ++i) n2[i] = normals[order[i]]; }
+    else n2 = importerNormals(v2, t);
+    struct Key { float a[9]; bool operator<(const Key& o) const { return memcmp(a, o.a, sizeof(a)) < 0; } };
+    std::map<Key, unsigned> firstOf;
+    std::vector<unsigned> joined(order.size());
+    std::vector<Vec3> v3, n3, uv3;
+    for (size_t i = 0; i < order.size(); ++i) {
+        Key k = {{v2[i].x, v2[i].y, v2[i].z, n2[i].x, n2[i].y, n2[i].z, uv2[i].x, uv2[i].y, uv2[i].z}};
+        for (float& x : k.a) if (x == 0.0f) x = 0.0f;   // -0 and +0 are one value
+        auto it = firstOf.find(k);
+        if (it == firstOf.end()) { it = firstOf.emplace(k, (unsigned)v3.size()).first; v3.push_back(v2[i]); n3.push_back(n2[i]); uv3.push_back(uv2[i]); }
+        joined[i] = it->second;
+    }
+    for (Triangle& f : t) { f.idx0 = joined[f.idx0]; f.idx1 = joined[f.idx1]; f.idx2 = joined[f.idx2]; }
+    v.swap(v3); normals.swap(n3); uv.swap(uv3);
 }
 
 inline int textureImage(const Json& doc, const std::vector<int>& embedded, const Json* info)
@@ -558,28 +597,91 @@ inline Parsed parse(const std::string& path)
     const Document D = readContainer(path);
     const Json& doc = D.doc;
     Parsed S;
-    // embedded images in image order -> "*N"
-    std::vector<int> embedded;
-    if (const Json* images = doc.find("images"))
-        for (size_t k = 0; k < images->size(); ++k) {
-            const Json& img = images->at(k);
-            if (img.has("bufferView")) {
-                const Json& view = doc.at("bufferViews").at((size_t)img.integer("bufferView", 0));
-                const std::vector<unsigned char>& buf = D.buffers.at((size_t)view.integer("buffer", 0));
-                const size_t at = (size_t)view.integer("byteOffset", 0), len = (size_t)view.integer("byteLength", 0);
-                if (at + len > buf.size()) fail("image " + std::to_string(k) + ": buffer view outside its buffer");
-                S.images.emplace_back(buf.begin() + at, buf.begin() + at + len);
-            } else if (img.has("uri") && img.at("uri").text.compare(0, 5, "data:") == 0) {
-                S.images.push_back(base64(img.at("uri").text, img.at("uri").text.find(',') + 1));
-            } else { embedded.push_back(-1); continue; }
-            embedded.push_back((int)S.images.size() - 1);
+    // assimp's glTF2 importer loads only what the default scene references, in the order it first meets it (LazyDict::Retrieve):
+    // Node::Read (glTF2Asset.inl:1692-1760) retrieves a node's children -- depth first -- BEFORE the node's own mesh, Mesh::Read
+    // retrieves each primitive's material, Material::Read (:1283-1300) the baseColor, metallicRoughness, normal, occlusion and
+    // emissive textures and through them the images. aiMesh / aiMaterial / "*N" numbering follows that order, not the file's
+    // (pinned against the reference's own loader on the reference's assimp by tests/test_scene_loader.py).
+    std::vector<size_t> meshOrder, materialOrder, imageOrder;
+    {
+        const Json* nodesJ = doc.find("nodes");
+        const Json* meshesJ = doc.find("meshes");
+        const Json* matsJ = doc.find("materials");
+        const Json* texJ = doc.find("textures");
+        std::vector<char> seen(nodesJ ? nodesJ->size() : 0, 0);
+        auto listed = [](const std::vector<size_t>& v, size_t x) { for (size_t y : v) if (y == x) return true; return false; };
+        struct Loader
+        {
+            const Json *nodesJ, *meshesJ, *matsJ, *texJ; std::vector<char>& seen;
+            std::vector<size_t>&meshOrder, &materialOrder, &imageOrder;
+            bool (*listed)(const std::vector<size_t>&, size_t);
+            void texture(const Json* info)
+            {
+                if (!info || !texJ) return;
+                const long source = texJ->at((size_t)info->integer("index", 0)).integer("source", -1);
+                if (source >= 0 && !listed(imageOrder, (size_t)source)) imageOrder.push_back((size_t)source);
+            }
+            void material(size_t k)
+            {
+                if (listed(materialOrder, k)) return;
+                materialOrder.push_back(k);
+                const Json& m = matsJ->at(k);
+                const Json* pbr = m.find("pbrMetallicRoughness");
+                texture(pbr ? pbr->find("baseColorTexture") : nullptr);
+                texture(pbr ? pbr->find("metallicRoughnessTexture") : nullptr);
+                texture(m.find("normalTexture")); texture(m.find("occlusionTexture")); texture(m.find("emissiveTexture"));
+            }
+            void node(size_t i)
+            {
+                if (i >= seen.size()) fail("node " + std::to_string(i) + ": index out of range");
+                if (seen[i]) return;
+                seen[i] = 1;
+                const Json& n = nodesJ->at(i);
+                if (const Json* ch = n.find("children")) for (size_t k = 0; k < ch->size(); ++k) node((size_t)ch->at(k).number);
+                if (n.has("mesh")) {
+                    const size_t mi = (size_t)n.integer("mesh", 0);
+                    if (!meshesJ || mi >= meshesJ->size()) fail("node " + std::to_string(i) + ": mesh index out of range");
+                    if (!listed(meshOrder, mi)) {
+                        meshOrder.push_back(mi);
+                        const Json& prims = meshesJ->at(mi).at("primitives");
+                        for (size_t pi = 0; pi < prims.size(); ++pi) if (prims.at(pi).has("material")) material((size_t)prims.at(pi).integer("material", 0));
+                    }
+                }
+            }
+        } loader{nodesJ, meshesJ, matsJ, texJ, seen, meshOrder, materialOrder, imageOrder, +listed};
+        const Json* scenesJ = doc.find("scenes");
+        if (scenesJ && scenesJ->size() && nodesJ)
+            if (const Json* roots = scenesJ->at((size_t)doc.integer("scene", 0)).find("nodes"))
+                for (size_t k = 0; k < roots->size(); ++k) loader.node((size_t)roots->at(k).number);
+    }
+    // embedded images, in the order the importer meets them -> "*N"
+    std::vector<int> embedded(doc.find("images") ? doc.find("images")->size() : 0, -1);
+    for (size_t k : imageOrder) {
+        const Json& img = doc.at("images").at(k);
+        if (img.has("bufferView")) {
+            const Json& view = doc.at("bufferViews").at((size_t)img.integer("bufferView", 0));
+            const std::vector<unsigned char>& buf = D.buffers.at((size_t)view.integer("buffer", 0));
+            const size_t at = (size_t)view.integer("byteOffset", 0), len = (size_t)view.integer("byteLength", 0);
+            if (at + len > buf.size()) fail("image " + std::to_string(k) + ": buffer view outside its buffer");
+            S.images.emplace_back(buf.begin() + at, buf.begin() + at + len);
+        } else if (img.has("uri") && img.at("uri").text.compare(0, 5, "data:") == 0) {
+            S.images.push_back(base64(img.at("uri").text, img.at("uri").text.find(',') + 1));
+        } else continue;
+        embedded[k] = (int)S.images.size() - 1;
+    }
+    // the materials the scene references + the importer's default material; the transmission / ior extensions count only when
+    // the asset declares them in extensionsUsed (glTF2Asset.inl:1360, :1384)
+    bool useTransmission = false, useIor = false;
+    if (const Json* used = doc.find("extensionsUsed"))
+        for (size_t k = 0; k < used->size(); ++k) {
+            if (used->at(k).text == "KHR_materials_transmission") useTransmission = true;
+            if (used->at(k).text == "KHR_materials_ior") useIor = true;
         }
-    // materials + the importer's default material
     const Json* mats = doc.find("materials");
-    const size_t nm = mats ? mats->size() : 0;
+    const size_t nm = materialOrder.size();
     static const Json empty;
     for (size_t k = 0; k <= nm; ++k) {
-        const Json& m = k < nm ? mats->at(k) : empty;
+        const Json& m = k < nm ? mats->at(materialOrder[k]) : empty;
         const Json* pbr = m.find("pbrMetallicRoughness");
         const Json* ext = m.find("extensions");
         Material M;
@@ -589,8 +691,8 @@ inline Parsed parse(const std::string& path)
         M.metallic = (float)(pbr ? pbr->num("metallicFactor", 1.0) : 1.0);
         M.roughness = (float)(pbr ? pbr->num("roughnessFactor", 1.0) : 1.0);
         M.metallicTexIdx = M.roughnessTexIdx = textureImage(doc, embedded, pbr ? pbr->find("metallicRoughnessTexture") : nullptr);
-        const Json* tr = ext ? ext->find("KHR_materials_transmission") : nullptr;
-        const Json* ior = ext ? ext->find("KHR_materials_ior") : nullptr;
+        const Json* tr = (ext && useTransmission) ? ext->find("KHR_materials_transmission") : nullptr;
+        const Json* ior = (ext && useIor) ? ext->find("KHR_materials_ior") : nullptr;
         M.transmission = (float)(tr ? tr->num("transmissionFactor", 0.0) : 0.0);
         M.ior = (float)(ior ? ior->num("ior", 1.45) : 1.45);
         M.normalTexIdx = textureImage(doc, embedded, m.find("normalTexture"));
@@ -598,10 +700,10 @@ inline Parsed parse(const std::string& path)
     }
     const int defaultMaterial = (int)nm;
     // one mesh per primitive
-    std::vector<size_t> meshOffsets;
     const Json* meshes = doc.find("meshes");
-    for (size_t mi = 0; meshes && mi < meshes->size(); ++mi) {
-        meshOffsets.push_back(S.meshes.size());
+    std::vector<size_t> meshFirst(meshes ? meshes->size() : 0, 0), meshEnd(meshes ? meshes->size() : 0, 0);   // per glTF mesh: its run of primitives
+    for (size_t mi : meshOrder) {
+        meshFirst[mi] = S.meshes.size();
         const Json& prims = meshes->at(mi).at("primitives");
         for (size_t pi = 0; pi < prims.size(); ++pi) {
             const Json& prim = prims.at(pi);
@@ -621,15 +723,16 @@ inline Parsed parse(const std::string& path)
                 if (idx[i] >= P.count || idx[i + 1] >= P.count || idx[i + 2] >= P.count) fail(where + ": index out of range");
                 M.triangles.push_back(Triangle{idx[i], idx[i + 1], idx[i + 2]});
             }
-            std::vector<Vec3> normals;
-            if (attr.has("NORMAL")) { const Accessor N = readAccessor(D, attr.integer("NORMAL", 0)); for (size_t i = 0; i < N.count; ++i) normals.emplace_back((float)N.v[3 * i], (float)N.v[3 * i + 1], (float)N.v[3 * i + 2]); }
-            else normals = smoothNormals(M.vertices, M.triangles);
+            std::vector<Vec3> normals;   // empty = generated by importerVertexOrder
+            if (attr.has("NORMAL")) { const Accessor N = readAccessor(D, attr.integer("NORMAL", 0)); for (size_t i = 0; i < N.count; ++i) normals.emplace_back((float)N.v[3 * i], (float)N.v[3 * i + 1], (float)N.v[3 * i + 2]); if (normals.size() != P.count) fail(where + ": NORMAL count differs from POSITION"); }
             std::vector<Vec3> uv(P.count);
             if (attr.has("TEXCOORD_0")) { const Accessor T = readAccessor(D, attr.integer("TEXCOORD_0", 0)); for (size_t i = 0; i < T.count && i < P.count; ++i) uv[i] = Vec3((float)T.v[T.width * i], 1.0f - (float)T.v[T.width * i + 1], 0.0f); }
+            importerVertexOrder(M.vertices, M.triangles, normals, uv);
             MeshInfo info{};
             info.vertexOffset = info.uvOffset = info.normalOffset = (int)(S.vertices.size() * 3);
             info.indexOffset = (int)(S.triangles.size() * 3);
-            info.materialIndex = (int)prim.integer("material", defaultMaterial);
+            info.materialIndex = defaultMaterial;
+            if (prim.has("material")) for (size_t r = 0; r < materialOrder.size(); ++r) if (materialOrder[r] == (size_t)prim.integer("material", 0)) info.materialIndex = (int)r;
             S.meshInfoPerMesh.push_back(info);
             S.vertices.insert(S.vertices.end(), M.vertices.begin(), M.vertices.end());
             S.triangles.insert(S.triangles.end(), M.triangles.begin(), M.triangles.end());
@@ -637,14 +740,14 @@ inline Parsed parse(const std::string& path)
             S.uvs.insert(S.uvs.end(), uv.begin(), uv.end());
             S.meshes.push_back(std::move(M));
         }
+        meshEnd[mi] = S.meshes.size();
     }
-    meshOffsets.push_back(S.meshes.size());
     if (S.meshes.empty()) fail(path + ": no meshes");
     // instances: depth-first, a node's primitives before its children
     const Json* nodes = doc.find("nodes");
     struct Walker
     {
-        Parsed& S; const Json* nodes; const std::vector<size_t>& meshOffsets;
+        Parsed& S; const Json* nodes; const std::vector<size_t>& meshFirst; const std::vector<size_t>& meshEnd;
         void visit(size_t index, const Mat4x4& parent, std::vector<size_t>& trail)
         {
             for (size_t t : trail) if (t == index) fail("node " + std::to_string(index) + ": cycle in the node hierarchy");
@@ -652,15 +755,15 @@ inline Parsed parse(const std::string& path)
             const Mat4x4 current = multiply(parent, nodeTransform(node));
             if (node.has("mesh")) {
                 const size_t m = (size_t)node.integer("mesh", 0);
-                if (m + 1 >= meshOffsets.size()) fail("node " + std::to_string(index) + ": mesh index out of range");
-                for (size_t k = meshOffsets[m]; k < meshOffsets[m + 1]; ++k)
+                if (m >= meshFirst.size()) fail("node " + std::to_string(index) + ": mesh index out of range");
+                for (size_t k = meshFirst[m]; k < meshEnd[m]; ++k)
                     S.instances.push_back(Parsed::InstanceData{(unsigned)k, current, 0u, (unsigned)S.meshInfoPerMesh[k].materialIndex});
             }
             trail.push_back(index);
             if (const Json* ch = node.find("children")) for (size_t k = 0; k < ch->size(); ++k) visit((size_t)ch->at(k).number, current, trail);
             trail.pop_back();
         }
-    } walker{S, nodes, meshOffsets};
+    } walker{S, nodes, meshFirst, meshEnd};
     const Json* scenes = doc.find("scenes");
     if (scenes && scenes->size() && nodes) {
         const Json& scene = scenes->at((size_t)doc.integer("scene", 0));

@@ -107,23 +107,6 @@ def _accessor(doc, buffers, index):
     return out
 
 
-def _smooth_normals(verts, tris):
-    """aiProcess_GenSmoothNormals for meshes without NORMAL: area-weighted face normals summed over all vertices that
-    share a position, then normalised."""
-    v = verts.astype(np.float64)
-    fn = np.cross(v[tris[:, 1]] - v[tris[:, 0]], v[tris[:, 2]] - v[tris[:, 0]])
-    _, group = np.unique(verts, axis=0, return_inverse=True)
-    group = group.reshape(-1)
-    acc = np.zeros((group.max() + 1, 3))
-    for k in range(3):
-        for c in range(3):
-            acc[:, c] += np.bincount(group[tris[:, k]], weights=fn[:, c], minlength=acc.shape[0])
-    n = acc[group]
-    ln = np.linalg.norm(n, axis=1, keepdims=True)
-    ln[ln == 0] = 1.0
-    return (n / ln).astype(np.float32)
-
-
 def _quat_matrix(q):
     x, y, z, w = (float(c) for c in q)
     return np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w), 0],
@@ -169,20 +152,117 @@ def _texture_image(doc, embedded, tex_info):
     return embedded[image]
 
 
-def _materials(doc, embedded):
-    """One row per glTF material plus the importer's default material (sceneBuilder.cpp:111-197)."""
-    out = np.zeros(len(doc.get("materials", [])) + 1, MATERIAL_DTYPE)
-    for k, m in enumerate(list(doc.get("materials", [])) + [{}]):
+def _materials(doc, embedded, order):
+    """One row per glTF material the scene references, in the order the importer first meets them, plus the importer's
+    default material (sceneBuilder.cpp:111-197). The transmission / ior extensions count only when the asset declares them in
+    extensionsUsed (glTF2Asset.inl:1360, :1384)."""
+    used = set(doc.get("extensionsUsed", []))
+    listed = [doc["materials"][k] for k in order]
+    out = np.zeros(len(listed) + 1, MATERIAL_DTYPE)
+    for k, m in enumerate(listed + [{}]):
         pbr, ext, row = m.get("pbrMetallicRoughness", {}), m.get("extensions", {}), out[k]
         row["albedo"] = pbr.get("baseColorFactor", [1.0, 1.0, 1.0, 1.0])
         row["albedoTex"] = _texture_image(doc, embedded, pbr.get("baseColorTexture"))
         row["metallic"] = pbr.get("metallicFactor", 1.0)
         row["roughness"] = pbr.get("roughnessFactor", 1.0)
         row["metallicTex"] = row["roughnessTex"] = _texture_image(doc, embedded, pbr.get("metallicRoughnessTexture"))
-        row["transmission"] = ext.get("KHR_materials_transmission", {}).get("transmissionFactor", 0.0)
-        row["ior"] = ext.get("KHR_materials_ior", {}).get("ior", 1.45)
+        row["transmission"] = (ext.get("KHR_materials_transmission", {}).get("transmissionFactor", 0.0)
+                               if "KHR_materials_transmission" in used else 0.0)
+        row["ior"] = ext.get("KHR_materials_ior", {}).get("ior", 1.45) if "KHR_materials_ior" in used else 1.45
         row["normalTex"] = _texture_image(doc, embedded, m.get("normalTexture"))
     return out
+
+
+def _importer_normals(v, t):
+    """aiProcess_GenSmoothNormals as assimp runs it on the importer's INDEXED mesh (GenVertexNormalsProcess.cpp:104-235, default
+    smoothing angle 175 degrees): every face writes its unit normal ((v1 - v0) x (v2 - v0), NormalizeSafe) to its three vertices --
+    for a vertex shared by several faces the LAST face in index order wins -- and vertices at the same position then share the
+    normalised sum of those per-vertex normals. (assimp groups positions within 1e-4 of the mesh's extent; exact equality here.)"""
+    p0, p1, p2 = v[t[:, 0]].astype(np.float32), v[t[:, 1]].astype(np.float32), v[t[:, 2]].astype(np.float32)
+    fn = np.cross(p1 - p0, p2 - p0).astype(np.float32)
+    length = np.sqrt((fn * fn).sum(1, dtype=np.float32)).astype(np.float32)
+    fn = np.where(length[:, None] > 0, fn / np.where(length > 0, length, 1)[:, None], fn).astype(np.float32)
+    per_vertex = np.zeros((v.shape[0], 3), np.float32)
+    flat = t.reshape(-1)
+    per_vertex[flat] = np.repeat(fn, 3, axis=0)            # numpy keeps the last assignment of a repeated index: the last face wins
+    keys = np.ascontiguousarray(v, np.float32).view([("", np.float32)] * 3).reshape(-1)
+    _, inverse = np.unique(keys, return_inverse=True)
+    inverse = inverse.reshape(-1)
+    sums = np.zeros((inverse.max() + 1, 3), np.float32)
+    np.add.at(sums, inverse, per_vertex)
+    length = np.sqrt((sums * sums).sum(1, dtype=np.float32)).astype(np.float32)
+    sums = np.where(length[:, None] > 0, sums / np.where(length > 0, length, 1)[:, None], sums).astype(np.float32)
+    return np.ascontiguousarray(sums[inverse], np.float32)
+
+
+def _importer_vertex_order(v, t, n, uv):
+    """The vertex numbering assimp hands to sceneBuilder.cpp: the glTF2 importer keeps only the vertices the index list uses and
+    numbers them in the order the index list first mentions them (glTF2Importer.cpp ImportMeshes, vertexRemappingTable); missing
+    normals are generated on that mesh (_importer_normals; pass n = None); then aiProcess_JoinIdenticalVertices merges vertices
+    whose position, normal and uv are identical, keeping the first (JoinVerticesProcess.cpp:258-381; its comparison has a 1e-5
+    tolerance, exact equality is used here). Triangles keep their order."""
+    flat = t.reshape(-1).astype(np.int64)
+    if flat.size == 0:
+        return v[:0], t, (n if n is not None else v)[:0], uv[:0]
+    order = flat[np.sort(np.unique(flat, return_index=True)[1])]                 # vertex ids by first appearance
+    remap = np.full(v.shape[0], -1, np.int64)
+    remap[order] = np.arange(len(order))
+    v, uv, t = v[order], uv[order], remap[t]
+    n = n[order] if n is not None else _importer_normals(v, t)
+    attr = np.ascontiguousarray(np.concatenate([v, n, uv], 1), np.float32) + np.float32(0.0)   # -0 and +0 are one value
+    rows = attr.view([("", attr.dtype)] * attr.shape[1]).reshape(-1)
+    _, first, inverse = np.unique(rows, return_index=True, return_inverse=True)
+    keep = np.sort(first)                                                        # first occurrence of every distinct vertex
+    rank = np.empty(len(first), np.int64)
+    rank[np.argsort(first)] = np.arange(len(first))
+    joined = rank[inverse.reshape(-1)]
+    return (np.ascontiguousarray(v[keep]), np.ascontiguousarray(joined[t].astype(np.uint32)),
+            np.ascontiguousarray(n[keep]), np.ascontiguousarray(uv[keep]))
+
+
+def _retrieval_order(doc):
+    """assimp's glTF2 importer loads only what the default scene references, in the order it first meets it (LazyDict::Retrieve):
+    Node::Read (glTF2Asset.inl:1692-1760) retrieves a node's children -- depth first -- BEFORE the node's own mesh, Mesh::Read
+    retrieves each primitive's material, Material::Read (:1283-1300) the baseColor, metallicRoughness, normal, occlusion and
+    emissive textures and through them the images. aiMesh / aiMaterial / "*N" numbering follows that order, not the file's
+    (pinned against the reference's own loader by tests/test_scene_loader.py). Returns (meshes, materials, images)."""
+    nodes, meshes_d, materials_d, textures_d = doc.get("nodes", []), doc.get("meshes", []), doc.get("materials", []), doc.get("textures", [])
+    meshes, materials, images, seen = [], [], [], set()
+
+    def texture(info):
+        if info is None:
+            return
+        source = textures_d[info["index"]].get("source")
+        if source is not None and source not in images:
+            images.append(source)
+
+    def material(k):
+        if k in materials:
+            return
+        materials.append(k)
+        m = materials_d[k]
+        pbr = m.get("pbrMetallicRoughness", {})
+        for info in (pbr.get("baseColorTexture"), pbr.get("metallicRoughnessTexture"), m.get("normalTexture"),
+                     m.get("occlusionTexture"), m.get("emissiveTexture")):
+            texture(info)
+
+    def node(i):
+        if i in seen:
+            return
+        seen.add(i)
+        for c in nodes[i].get("children", []):
+            node(c)
+        mi = nodes[i].get("mesh")
+        if mi is not None and mi not in meshes:
+            meshes.append(mi)
+            for prim in meshes_d[mi]["primitives"]:
+                if "material" in prim:
+                    material(prim["material"])
+
+    scenes = doc.get("scenes", [])
+    for r in (scenes[doc.get("scene", 0)].get("nodes", []) if scenes else []):
+        node(r)
+    return meshes, materials, images
 
 
 def parse_gltf(path):
@@ -191,9 +271,11 @@ def parse_gltf(path):
         raise SceneFormatError(f"{path}: glTF asset version {doc['asset'].get('version')} (2.x expected)")
     s = ParsedScene()
 
-    # embedded images in image order -> "*N"
-    embedded, s.images = [], []
-    for img in doc.get("images", []):
+    mesh_order, material_order, image_order = _retrieval_order(doc)
+    # embedded images, in the order the importer meets them -> "*N"
+    embedded, s.images = [-1] * len(doc.get("images", [])), []
+    for k in image_order:
+        img = doc["images"][k]
         if "bufferView" in img:
             view = doc["bufferViews"][img["bufferView"]]
             at = view.get("byteOffset", 0)
@@ -201,17 +283,18 @@ def parse_gltf(path):
         elif str(img.get("uri", "")).startswith("data:"):
             s.images.append(base64.b64decode(img["uri"].split(",", 1)[1]))
         else:
-            embedded.append(-1)
             continue
-        embedded.append(len(s.images) - 1)
-    s.materials = _materials(doc, embedded)
+        embedded[k] = len(s.images) - 1
+    s.materials = _materials(doc, embedded, material_order)
     default_material = len(s.materials) - 1
+    material_row = {k: row for row, k in enumerate(material_order)}
 
     # one mesh per primitive
-    s.meshes, mesh_offsets, info, uvs, normals = [], [], [], [], []
+    s.meshes, mesh_offsets, info, uvs, normals = [], {}, [], [], []
     vo = io_ = 0
-    for mi, mesh in enumerate(doc.get("meshes", [])):
-        mesh_offsets.append(len(s.meshes))
+    for mi in mesh_order:
+        mesh = doc["meshes"][mi]
+        first = len(s.meshes)
         for pi, prim in enumerate(mesh["primitives"]):
             if prim.get("mode", 4) != 4:
                 raise SceneFormatError(f"mesh {mi} primitive {pi}: mode {prim['mode']}; only triangle lists (4) reach "
@@ -229,22 +312,20 @@ def parse_gltf(path):
             t = idx.reshape(-1, 3)
             if t.size and int(t.max()) >= v.shape[0]:
                 raise SceneFormatError(f"mesh {mi} primitive {pi}: index {int(t.max())} >= {v.shape[0]} vertices")
-            if "NORMAL" in attr:
-                n = np.ascontiguousarray(_accessor(doc, buffers, attr["NORMAL"]), np.float32)
-            else:
-                n = _smooth_normals(v, t)
+            n = np.ascontiguousarray(_accessor(doc, buffers, attr["NORMAL"]), np.float32) if "NORMAL" in attr else None
             uv = np.zeros((v.shape[0], 3), np.float32)
             if "TEXCOORD_0" in attr:
                 tc = _accessor(doc, buffers, attr["TEXCOORD_0"]).astype(np.float32)
                 uv[:, 0], uv[:, 1] = tc[:, 0], np.float32(1.0) - tc[:, 1]
-            material = prim.get("material", default_material)
+            v, t, n, uv = _importer_vertex_order(v, t, n, uv)
+            material = material_row[prim["material"]] if "material" in prim else default_material
             info.append((vo * 3, io_ * 3, vo * 3, vo * 3, material))
             s.meshes.append((v, np.ascontiguousarray(t)))
             uvs.append(uv)
             normals.append(n)
             vo += v.shape[0]
             io_ += t.shape[0]
-    mesh_offsets.append(len(s.meshes))
+        mesh_offsets[mi] = (first, len(s.meshes))
     if not s.meshes:
         raise SceneFormatError(f"{path}: no meshes")
     s.meshInfoPerMesh = np.zeros(len(info), MESHINFO_DTYPE)
@@ -265,7 +346,7 @@ def parse_gltf(path):
         node = nodes[index]
         current = (parent @ _node_transform(node)).astype(np.float32)
         if "mesh" in node:
-            for m in range(mesh_offsets[node["mesh"]], mesh_offsets[node["mesh"] + 1]):
+            for m in range(*mesh_offsets[node["mesh"]]):
                 s.instances.append((m, current, 0, int(s.meshInfoPerMesh[m]["materialIndex"])))
         for child in node.get("children", []):
             visit(child, current, trail | {index})

@@ -100,6 +100,8 @@ def build_asset(scenes):
              {"name": "C", "mesh": 0, "children": [3]},
              {"name": "D", "translation": [-0.6, 0.5, 0.3], "mesh": 1}]
     doc = {"asset": {"version": "2.0"}, "scene": 0, "scenes": [{"nodes": [0, 2]}], "nodes": nodes,
+           # the specification requires used extensions to be declared; assimp ignores undeclared ones (glTF2Asset.inl:1360, :1384)
+           "extensionsUsed": ["KHR_materials_transmission", "KHR_materials_ior"],
            "meshes": [{"primitives": [p_floor, p_box]}, {"primitives": [p_sphere]}],
            "materials": [{"pbrMetallicRoughness": {"baseColorTexture": {"index": 0}, "metallicFactor": 0.0, "roughnessFactor": 0.7}},
                          {"pbrMetallicRoughness": {"baseColorFactor": [0.9, 0.3, 0.2, 1.0], "metallicFactor": 0.2, "roughnessFactor": 0.4},
@@ -113,15 +115,39 @@ def build_asset(scenes):
     td = np.eye(4)
     td[:3, 3] = [-0.6, 0.5, 0.3]
     bsm = bv.copy()  # box normals: per-position area-weighted average (every corner position is unique in this mesh)
+    # Order of the importer's meshes and materials = the order in which assimp first MEETS them while it loads the default scene
+    # (LazyDict::Retrieve; a node's children are read before the node's own mesh, glTF2Asset.inl:1692-1760), not the order of the
+    # file: root A has no mesh, its child B retrieves glTF mesh 1 (sphere, material 1) first; root C's child D uses mesh 1 again,
+    # then C's own mesh 0 (floor with material 0, box without material) follows. Pinned against the reference's own loader on
+    # the reference's vendored assimp by tests/test_scene_loader.py::test_loader_equals_reference_scenebuilder_on_assimp.
+    # Vertices: the importer numbers them in the order the index list first mentions them (vertexRemappingTable in ImportMeshes).
+    def first_use(v, t, *attrs):
+        flat = t.reshape(-1)
+        order = flat[np.sort(np.unique(flat, return_index=True)[1])]
+        remap = np.zeros(len(v), np.uint32)
+        remap[order] = np.arange(len(order), dtype=np.uint32)
+        return (v[order], remap[t]) + tuple(a[order] for a in attrs)
+
+    # generated normals (the box has no NORMAL): assimp's GenSmoothNormals on the importer's indexed mesh gives every vertex the
+    # unit normal of the LAST face that uses it, then averages over vertices at the same position (GenVertexNormalsProcess.cpp:
+    # 125-185) -- every corner position of this box is one vertex, so no averaging happens
+    bn = np.zeros((len(bv), 3), np.float32)
+    for tri in bt:
+        a, b, c = bv[tri[0]], bv[tri[1]], bv[tri[2]]
+        fn_ = np.cross(b - a, c - a).astype(np.float32)
+        bn[tri] = fn_ / np.float32(np.sqrt((fn_ * fn_).sum(dtype=np.float32)))
+    fuv3 = np.stack([fuv[:, 0], 1.0 - fuv[:, 1], np.zeros(len(fuv))], -1).astype(np.float32)
+    sv_o, st_o, sn_o = first_use(sv, st, sn)
+    fv_o, ft_o, fn_o, fuv_o = first_use(fv, ft, fn, fuv3)
+    bv_o, bt_o, bn_o = first_use(bv, bt, bn)
     expected = {
-        "meshes": [(fv, ft), (bv, bt), (sv, st)],
-        "normals": [fn, scenes.vertex_normals(bsm, bt), sn],
-        "uv": [np.stack([fuv[:, 0], 1.0 - fuv[:, 1], np.zeros(len(fuv))], -1).astype(np.float32),
-               np.zeros((len(bv), 3), np.float32), np.zeros((len(sv), 3), np.float32)],
-        "mesh_material": [0, 2, 1],             # the box gets the importer's default material (index 2)
-        # depth-first, a node's primitives before its children: A (no mesh) -> B; C -> floor, box; D
-        "instances": [(2, (tf_a @ m_b.astype(np.float64)).astype(np.float32), 1), (0, np.eye(4, dtype=np.float32), 0),
-                      (1, np.eye(4, dtype=np.float32), 2), (2, td.astype(np.float32), 1)],
+        "meshes": [(sv_o, st_o), (fv_o, ft_o), (bv_o, bt_o)],
+        "normals": [sn_o, fn_o, bn_o],
+        "uv": [np.zeros((len(sv_o), 3), np.float32), fuv_o, np.zeros((len(bv_o), 3), np.float32)],
+        "mesh_material": [0, 1, 2],             # sphere -> glTF material 1 = row 0, floor -> glTF material 0 = row 1, box -> default (row 2)
+        # instances: depth-first, a node's primitives before its children (sceneBuilder.cpp:285-315): A (no mesh) -> B; C -> floor, box; D
+        "instances": [(0, (tf_a @ m_b.astype(np.float64)).astype(np.float32), 0), (1, np.eye(4, dtype=np.float32), 1),
+                      (2, np.eye(4, dtype=np.float32), 2), (0, td.astype(np.float32), 0)],
         "pixels": pixels,
     }
     return doc, bytes(blob), expected
