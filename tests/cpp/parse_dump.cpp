@@ -1,7 +1,8 @@
 // tests/cpp/parse_dump.cpp -- CPU-only check of the C++ scene parser (include/sceneBuilder.h, RD::gltf::parse): writes the arrays
 // behind the nine descriptors in the format of sample_scene's <prefix>.arrays, without creating a platform (no GPU needed).
-// usage: parse_dump <scene.glb|gltf> <out.arrays>
+// usage: parse_dump <scene.glb|gltf> <out.arrays> [texture dim: also appends embedded image 0 decoded and resized to dim x dim]
 #include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <vector>
 #include "sceneBuilder.h"
@@ -26,6 +27,11 @@ int main(int argc, char** argv)
     std::vector<unsigned> imageSizes;
     for (auto& im : P.images) imageSizes.push_back((unsigned)im.size());
     dump(f, imageSizes);
+    if (argc > 3 && !P.images.empty()) {
+        std::vector<unsigned char> rgba; int w = 0, h = 0;
+        if (!RD::gltf::decodePng(P.images[0].data(), P.images[0].size(), rgba, w, h)) { fprintf(stderr, "parse_dump: image 0 is not a PNG\n"); return 5; }
+        dump(f, RD::gltf::resizeRgba(rgba, w, h, atoi(argv[3])));
+    }
     fclose(f);
     printf("parse_dump: %zu meshes, %zu materials, %zu instances, %zu images\n", P.meshes.size(), P.materials.size(), P.instances.size(), P.images.size());
     return 0;

@@ -79,7 +79,7 @@ def _reference_scene(path):
     return mod.load(path)
 
 
-def _cpp_arrays(path, tmpdir):
+def _cpp_arrays(path, tmpdir, dim=None):
     """the arrays of the C++ parser (include/sceneBuilder.h) through tests/cpp/parse_dump (no GPU needed)"""
     import subprocess
     here = os.path.dirname(os.path.abspath(__file__))
@@ -88,7 +88,7 @@ def _cpp_arrays(path, tmpdir):
         r = subprocess.run(["make", "-C", os.path.join(here, "cpp"), "parse_dump"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, r.stdout
     out = os.path.join(str(tmpdir), "cpp.arrays")
-    r = subprocess.run([exe, path, out], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    r = subprocess.run([exe, path, out] + ([str(dim)] if dim else []), stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     assert r.returncode == 0, r.stdout
     raw = open(out, "rb").read()
     at, arrays = 0, []
@@ -142,12 +142,12 @@ def test_loader_equals_reference_scenebuilder_on_assimp(pkg, asset):
             assert got[0] == mesh and got[2] == sbt == 0 and got[3] == custom
             assert np.abs(np.asarray(got[1]).reshape(4, 4) - tf).max() <= 1e-6
         assert ref["sampler"] == (0x1133, 0x1141)          # CL_ADDRESS_REPEAT, CL_FILTER_LINEAR (sceneBuilder.cpp:40)
-        # the texture: the fixture's 16x16 PNG, resized to 4096^2 by the reference's stb code -- every 256x256 block of the
-        # reference layer is one texel of the PNG away from the block edges, and the loader's embedded image is that PNG
+        # the texture layer: the fixture's 16x16 PNG decoded and resized to 4096^2 -- by the reference with its stb code
+        # (stb_image_resize2 defaults: Catmull-Rom enlargement), by the Python loader and by the C++ header loader: identical
         assert len(s.images) == ref["textureData"].shape[0] == 1
         layer = ref["textureData"][0]
-        centres = layer[128::256, 128::256]
-        assert np.abs(centres.astype(int) - asset["expected"]["pixels"].astype(int)).max() <= 1
+        assert np.array_equal(sl.decode_texture(s.images[0], 4096), layer)
+        assert np.array_equal(np.frombuffer(_cpp_arrays(path, asset["dir"], 4096)[8], np.uint8).reshape(4096, 4096, 4), layer)
         dec = sl.decode_texture(s.images[0], 16)
         assert np.array_equal(np.asarray(dec).reshape(16, 16, 4), asset["expected"]["pixels"])
         # the C++ header loader produces the Python loader's arrays byte for byte (normals to 2e-6)
@@ -160,6 +160,33 @@ def test_loader_equals_reference_scenebuilder_on_assimp(pkg, asset):
         for row, (mesh, tf, sbt, custom) in zip(inst, s.instances):
             assert int(row[0]) == mesh and int(row[1]) == custom and np.allclose(row[2:].reshape(4, 4), tf, atol=1e-6)
         assert np.frombuffer(image_sizes, np.uint32).tolist() == [len(b) for b in s.images]
+
+
+def test_texture_reduction_equals_reference_stb_resize(pkg, tmp_path):
+    """A texture wider than the 4096 layer (8192 x 24 random texels): the reference's stbir_resize_uint8_linear shrinks it with the
+    Mitchell filter widened by the scale and enlarges the 24 rows with Catmull-Rom; both product loaders reproduce the layer
+    within one level on <= 1e-4 of the texels (float32 summation order)."""
+    import io
+    from PIL import Image
+    sl = loader(pkg)
+    rng = np.random.default_rng(5)
+    px = rng.integers(0, 256, (24, 8192, 4), dtype=np.uint8)
+    px[..., 3] = 255
+    buf = io.BytesIO()
+    Image.fromarray(px, "RGBA").save(buf, format="PNG")
+    saved = gltf_fixture.checker_png
+    gltf_fixture.checker_png = lambda size=16: (buf.getvalue(), px)
+    try:
+        doc, binary, _ = gltf_fixture.build_asset(pkg.scenes)
+    finally:
+        gltf_fixture.checker_png = saved
+    path = str(tmp_path / "wide.glb")
+    gltf_fixture.write_glb(path, doc, binary)
+    layer = _reference_scene(path)["textureData"][0]
+    for got in (sl.decode_texture(sl.parse_gltf(path).images[0], 4096),
+                np.frombuffer(_cpp_arrays(path, tmp_path, 4096)[8], np.uint8).reshape(4096, 4096, 4)):
+        d = np.abs(got.astype(int) - layer.astype(int))
+        assert d.max() <= 1 and (d > 0).mean() <= 1e-4, (d.max(), (d > 0).mean())
 
 
 def test_malformed_assets_fail_loudly(pkg, asset):
