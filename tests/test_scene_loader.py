@@ -1,6 +1,8 @@
 """glTF / GLB ingestion (`scene_loader.Scene.Load`, the mirror of RD::Scene::Load, tools/sceneBuilder.cpp:27-315).
 
-CPU: the parsed descriptor arrays against arrays computed by the fixture writer; malformed containers fail loudly.
+CPU: the parsed descriptor arrays against arrays computed by the fixture writer AND against the reference's own loader
+(tools/sceneBuilder.cpp compiled unchanged) running on the reference's vendored assimp (oracle/_ref/libscene_ref.so), for the
+Python loader and the C++ header loader; the texture layers against the reference's stb resize; malformed containers fail loudly.
 GPU: the loaded scene rendered by programs/textured.cl against the same program on the reference runtime fed with
 the SAME parsed arrays, and the `<path>.cache` blob written in the reference's format read back."""
 import ctypes as C
