@@ -168,6 +168,20 @@ def test_reference_shader_cl_compiles_unmodified(pkg):
     assert size > 100000 and "raygen" in log
 
 
+def test_reference_shader_cl_with_wavefront_hooks_compiles(pkg):
+    """samples/shader.cl + programs/shader_wavefront_hooks.cl (the two functions a host appends): the raygen AND the generated
+    wavefront stage kernels compile for sm_100a (the GPU test test_c1_shader_cl_in_wavefront_mode runs them)."""
+    path = "/root/reference/samples/shader.cl"
+    if not os.path.exists(path):
+        pytest.skip("reference sources not present on this machine")
+    hooks = open(os.path.join(os.path.dirname(pkg.scenes.__file__), "programs", "shader_wavefront_hooks.cl")).read()
+    size, log = pkg.rd.CompileCheck(open(path).read() + "\n" + hooks, None)
+    for kernel in ("raygen", "rd_wf_generate", "rd_wf_shade", "rd_wf_accumulate", "rd_wf_resolve"):
+        assert kernel in log, kernel
+    plain, _ = pkg.rd.CompileCheck(open(path).read(), None)
+    assert size > plain
+
+
 def test_compile_errors_and_bad_sbt_are_reported(pkg):
     rd = pkg.rd
     with pytest.raises(rd.RadianceError, match="compilation failed"):
