@@ -13,6 +13,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
+#include <ctime>
+#include <string>
 #include <vector>
 #include "radiance_b200.h"
 
@@ -24,6 +27,46 @@
 #define CL_ADDRESS_MIRRORED_REPEAT 0x1134
 #define CL_FILTER_NEAREST 0x1140
 #define CL_FILTER_LINEAR 0x1141
+#endif
+
+// The reference's radiance.h hands assimp's math types to every host through core.h (Vec3 = aiVector3D, Mat4x4 = aiMatrix4x4), and
+// samples/sample1.cpp:74-81 builds its light direction with two more of them. Stand-ins for exactly what that host uses, so that
+// the reference's own sample1.cpp compiles against this header unchanged (tests/test_cpp_shim.py); a host that includes assimp
+// itself keeps assimp's types.
+#ifndef AI_VECTOR3D_H_INC
+struct aiVector3f
+{
+    float x = 0, y = 0, z = 0;
+    aiVector3f() = default;
+    aiVector3f(float X, float Y, float Z) : x(X), y(Y), z(Z) {}
+    float operator[](unsigned i) const { return (&x)[i]; }
+    float& operator[](unsigned i) { return (&x)[i]; }
+};
+struct aiMatrix3x3   // row major, identity by default
+{
+    float a1 = 1, a2 = 0, a3 = 0, b1 = 0, b2 = 1, b3 = 0, c1 = 0, c2 = 0, c3 = 1;
+    // rotation by `a` radians about the unit axis (x, y, z), written into `out`
+    static aiMatrix3x3& Rotation(float a, const aiVector3f& axis, aiMatrix3x3& out)
+    {
+        const float c = std::cos(a), s = std::sin(a), t = 1.0f - c, x = axis.x, y = axis.y, z = axis.z;
+        out.a1 = t * x * x + c;     out.a2 = t * x * y - s * z; out.a3 = t * x * z + s * y;
+        out.b1 = t * x * y + s * z; out.b2 = t * y * y + c;     out.b3 = t * y * z - s * x;
+        out.c1 = t * x * z - s * y; out.c2 = t * y * z + s * x; out.c3 = t * z * z + c;
+        return out;
+    }
+    aiMatrix3x3 operator*(const aiMatrix3x3& m) const
+    {
+        aiMatrix3x3 r;
+        r.a1 = a1 * m.a1 + a2 * m.b1 + a3 * m.c1; r.a2 = a1 * m.a2 + a2 * m.b2 + a3 * m.c2; r.a3 = a1 * m.a3 + a2 * m.b3 + a3 * m.c3;
+        r.b1 = b1 * m.a1 + b2 * m.b1 + b3 * m.c1; r.b2 = b1 * m.a2 + b2 * m.b2 + b3 * m.c2; r.b3 = b1 * m.a3 + b2 * m.b3 + b3 * m.c3;
+        r.c1 = c1 * m.a1 + c2 * m.b1 + c3 * m.c1; r.c2 = c1 * m.a2 + c2 * m.b2 + c3 * m.c2; r.c3 = c1 * m.a3 + c2 * m.b3 + c3 * m.c3;
+        return r;
+    }
+};
+inline aiVector3f operator*(const aiMatrix3x3& m, const aiVector3f& v)
+{
+    return aiVector3f(m.a1 * v.x + m.a2 * v.y + m.a3 * v.z, m.b1 * v.x + m.b2 * v.y + m.b3 * v.z, m.c1 * v.x + m.c2 * v.y + m.c3 * v.z);
+}
 #endif
 
 namespace RD

@@ -28,6 +28,39 @@ def test_shim_compiles_and_has_no_cpu_path(pkg):
     assert r.returncode != 0 and "no CPU path" in r.stdout   # aborts like CL_CHECK, never falls back
 
 
+def test_reference_sample1_cpp_builds_unchanged_against_the_shim(pkg, tmp_path):
+    """the reference's OWN host program, samples/sample1.cpp (scene load, pipeline set-up, descriptor binding,
+    TraceRays / ReadBuffer render loop, :363-548), compiled UNCHANGED against include/radiance.h + include/sceneBuilder.h +
+    include/inspector.h (they carry the names of the headers it includes) and linked to libradiance_b200.so -- with the
+    reference's vendored Dear ImGui core for its UI panel, which needs no graphics. Without a GPU the program stops at the
+    platform ("no CPU path"); its asset paths are the author's, so it is a build test, not a run test."""
+    ref = "/root/reference"
+    src = os.path.join(ref, "samples", "sample1.cpp")
+    if not os.path.exists(src):
+        pytest.skip("reference sources not present on this machine")
+    pkg.rd.lib()   # the library exists
+    inc = ["-I", os.path.join(ROOT, "include"), "-I", os.path.join(ref, "external"), "-I", os.path.join(ref, "external", "imgui")]
+    objs = []
+    jobs = []
+    for f, flags in [(src, ["-O1"])] + [(os.path.join(ref, "external", "imgui", n + ".cpp"), ["-O0"])
+                                        for n in ("imgui", "imgui_draw", "imgui_tables", "imgui_widgets")]:
+        o = str(tmp_path / (os.path.basename(f) + ".o"))
+        objs.append(o)
+        jobs.append(subprocess.Popen(["g++", "-std=c++17", "-w"] + flags + inc + ["-c", f, "-o", o], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    for j in jobs:
+        out, _ = j.communicate()
+        assert j.returncode == 0, out
+    exe = str(tmp_path / "sample1")
+    lib_dir = os.path.join(ROOT, "radiance-ray-tracing_b200")
+    r = subprocess.run(["g++"] + objs + ["-o", exe, "-L", lib_dir, "-lradiance_b200", "-Wl,-rpath," + lib_dir],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    import torch
+    if not torch.cuda.is_available():
+        r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, cwd=str(tmp_path))
+        assert "no CPU path" in r.stdout
+
+
 def test_shim_declares_the_reference_api():
     text = open(os.path.join(ROOT, "include", "radiance.h")).read()
     for name in ("BuildAccelStruct", "TopAccelStructToFile", "FileToTopAccelStruct", "CreateBuffer", "CreateImage", "CreateImageArray",
